@@ -1,0 +1,285 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the IndexFlatL2 search path (BASELINE.json `metric`).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c3|c2|c1|c5|smoke] [--impl reference]
+
+Workload (default c3 = BASELINE.json configs[2], the configuration the metric is quoted on):
+10M x 384 fp32 database, batches of nq=1024 queries, k=100.  One "step" = one search batch.
+  value  queries/s with database, queries and results resident in HBM (CUDA events);
+  e2e    the same through the public API with HOST numpy buffers (H2D of the queries and D2H of
+         (D, I) inside the timed region);
+  roofline / cpu_baseline as described in DESIGN.md section "Measurement".
+With N > 1 (torchrun, one rank per GPU) the 10M rows are row-sharded over the ranks (strong
+scaling: total work fixed), each step ends with one NCCL all-gather of the local top-k and the
+merge kernel; time is the max over ranks.
+
+`--impl reference` times the CPU restatement of faiss's IndexFlatL2.search (oracle/) on the
+host cores on a bounded sample of the same workload.  faiss-cpu itself is not installable here.
+"""
+import argparse
+import json
+import os
+import statistics
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "rag-llm-k8s_b200"))
+
+WORKLOADS = {
+    # name: (N, d, nq, k)
+    "c1": (2048, 384, 1, 5),
+    "c2": (1_000_000, 384, 1, 10),
+    "c3": (10_000_000, 384, 1024, 100),
+    "c3q1": (10_000_000, 384, 1, 100),
+    "c5": (10_000_000, 1024, 4096, 1024),
+    "smoke": (200_000, 384, 64, 10),
+}
+SEED_DB, SEED_Q = 1234, 5678
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        j = json.load(open(p))
+        return dict(hbm=j["hbm_gbs"], bf16=j["bf16_tflops"], bf16_sus=j.get("bf16_tflops_sustained", j["bf16_tflops"]),
+                    source="measured")
+    return dict(hbm=6650.0, bf16=1590.0, bf16_sus=1400.0, source="fallback")
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons while the timed region runs (NVML)."""
+
+    def __init__(self, dev):
+        super().__init__(daemon=True)
+        self.dev, self.stop_flag, self.sm, self.reasons, self.sm_max = dev, False, [], set(), None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(dev)
+            self.sm_max = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if not self.nv:
+            return
+        nv = self.nv
+        names = {
+            getattr(nv, "nvmlClocksThrottleReasonHwSlowdown", 0x8): "hw_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0x4): "sw_power_cap",
+        }
+        while not self.stop_flag:
+            try:
+                self.sm.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.02)
+
+    def result(self):
+        return {"sm_mhz": statistics.median(self.sm) if self.sm else None, "sm_max_mhz": self.sm_max,
+                "reasons": sorted(self.reasons), "samples": len(self.sm)}
+
+
+def cpu_reference(N, d, nq, k, steps, warmup, budget_s=15.0):
+    """Times the oracle (faiss-cpu-equivalent restatement) on a bounded sample: all nq queries
+    against the first S rows; QPS is scaled linearly in N (the scan is linear in rows)."""
+    import numpy as np
+    from oracle import oracle as O
+    threads = O.num_threads()
+    mode = O.MODE_FAISS if nq >= 20 else O.MODE_DIRECT_ROWPAR
+    q = O.synth(SEED_Q, 0, nq, d)
+    S = min(N, 4096)
+    x = O.synth(SEED_DB, 0, S, d)
+    t0 = time.perf_counter()
+    O.search(x, q, k, mode)
+    t_cal = max(time.perf_counter() - t0, 1e-4)
+    per_step = budget_s / max(steps + warmup, 1)
+    S = int(min(N, max(S, S * per_step / t_cal)))
+    S = max(min(S, int(8e9 / (4 * d))), 1)
+    x = O.synth(SEED_DB, 0, S, d)
+    for _ in range(min(warmup, 1)):
+        O.search(x, q, k, mode)
+    times = []
+    for _ in range(steps):
+        t0 = time.perf_counter()
+        O.search(x, q, k, mode)
+        times.append(time.perf_counter() - t0)
+    t = sum(times) / len(times) * (N / S)
+    return {"value": nq / t, "unit": "queries/s", "cores": threads, "kind": "port",
+            "sample": "all %d queries x first %d of %d rows, %d timed passes, time scaled x%.1f (linear in rows); "
+                      "oracle/flat_l2_oracle.c, OpenMP %d threads%s" % (
+                          nq, S, N, steps, N / S, threads,
+                          "" if nq >= 20 else " (row-parallel scan; faiss itself would use 1 thread at nq=1)")}, t * 1e3
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--rows", type=int, default=0, help="override N (debug)")
+    args = ap.parse_args()
+
+    N, d, nq, k = WORKLOADS[args.workload]
+    if args.rows:
+        N = args.rows
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    metric = "QPS at %s k=%d nq=%d" % (("%dMx%d" % (N // 1_000_000, d)) if N % 1_000_000 == 0 else "%dx%d" % (N, d), k, nq)
+    config = {"workload": "%s: IndexFlatL2 %dx%d fp32, nq=%d, k=%d" % (args.workload, N, d, nq, k),
+              "N": N, "d": d, "nq": nq, "k": k, "parallelism": "row-shard x%d" % world if world > 1 else "1 gpu",
+              "l2": "database (%.1f GB) is larger than L2, no flush needed" % (N * d * 4 / 1e9),
+              "db_seed": SEED_DB, "query_seed": SEED_Q}
+
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        cb, ms = cpu_reference(N, d, nq, k, args.steps, args.warmup, budget_s=60.0)
+        line = {"impl": "reference", "metric": metric, "value": cb["value"], "unit": "queries/s", "n_gpus": args.gpus,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config,
+                "cpu_baseline": cb,
+                "e2e": {"value": cb["value"], "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                "note": "faiss-cpu-equivalent restatement (not faiss-cpu): the wheel cannot be installed here"}
+        print(json.dumps(line))
+        return
+
+    import numpy as np
+    import torch
+    import b200knn
+    from b200knn import _lib
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; b200knn has no CPU path (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    # ---- build the (shard of the) index on the device -----------------------------------
+    if world > 1:
+        from b200knn.sharded import ShardedIndexFlatL2
+        index = ShardedIndexFlatL2(d, device=local_rank)
+        index.add_synthetic_global(N, SEED_DB)
+    else:
+        index = b200knn.IndexFlatL2(d, device=local_rank)
+        index.reserve(N)
+        index.add_synthetic(N, SEED_DB, 0)
+    q_dev = b200knn.synth(SEED_Q, 0, nq, d, device=local_rank)
+    q_host = q_dev.cpu().numpy()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        barrier()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0 = b200knn.launch_count()
+        t0 = time.perf_counter()
+        ev0.record()
+        for _ in range(steps):
+            fn()
+        ev1.record()
+        barrier()
+        wall = time.perf_counter() - t0
+        ms = ev0.elapsed_time(ev1)
+        launches = b200knn.launch_count() - l0
+        if dist is not None:
+            t = torch.tensor([ms], device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms, wall * 1e3, launches
+
+    # device-resident arm (value) and host-buffer arm (e2e)
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    ms_dev, _, launches = timed(lambda: index.search(q_dev, k), args.steps, args.warmup)
+    sampler.stop_flag = True
+    sampler.join()
+    _, wall_e2e, _ = timed(lambda: index.search(q_host, k), args.steps, max(args.warmup, 1))
+    if dist is not None:
+        t = torch.tensor([wall_e2e], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        wall_e2e = float(t.item())
+
+    # p50 single-query latency on the same index (second half of BASELINE.json's metric)
+    q1 = q_dev[:1].contiguous()
+    lat = []
+    for i in range(30):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        index.search(q1, k)
+        e1.record()
+        torch.cuda.synchronize()
+        if i >= 5:
+            lat.append(e0.elapsed_time(e1))
+    p50_nq1 = statistics.median(lat)
+
+    ms_step = ms_dev / args.steps
+    qps = nq / (ms_step * 1e-3)
+    qps_e2e = nq / (wall_e2e / args.steps * 1e-3)
+
+    # ---- roofline of the dominant kernel ----------------------------------------------
+    pk = peaks()
+    stats = index.stats() if hasattr(index, "stats") else {}
+    n_local = N // world if world > 1 else N
+    if stats.get("path") == "tensor":
+        k_ms = stats["main_kernel_ms"]
+        flops = 3 * 2.0 * nq * n_local * d
+        peak = pk["bf16_sus"] / 2.0
+        roof = {"bound": "tensor", "kernel": "k3_tf32x3_topk", "achieved": flops / (k_ms * 1e-3) / 1e12, "peak": peak,
+                "unit": "TFLOP/s", "traffic": None, "launch_ms": k_ms,
+                "peak_source": "%s bf16 sustained / 2 (TF32 dense; derived, MEASURED_PEAKS.json has no TF32 row)" % pk["source"],
+                "algorithmic": "executed tensor flops = 3 (3xTF32) * 2*nq*N*d per launch"}
+    else:
+        per_launch_ms = ms_dev / max(launches, 1)
+        gbs = n_local * d * 4 / (per_launch_ms * 1e-3) / 1e9
+        roof = {"bound": "hbm", "kernel": "scan_l2_topk_kernel", "achieved": gbs, "peak": pk["hbm"], "unit": "GB/s",
+                "traffic": None, "launch_ms": per_launch_ms, "peak_source": "%s copy bandwidth" % pk["source"],
+                "algorithmic": "N*d*4 bytes per launch (one pass over the rows per group of <= 8 queries)"}
+    roof["frac"] = roof["achieved"] / roof["peak"]
+    # single-query scan (the HBM-bound path) on the same index
+    roof_nq1 = {"bound": "hbm", "achieved": n_local * d * 4 / (p50_nq1 * 1e-3) / 1e9, "peak": pk["hbm"], "unit": "GB/s"}
+    roof_nq1["frac"] = roof_nq1["achieved"] / roof_nq1["peak"]
+
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+    cb = None
+    if world == 1 and not args.no_cpu_baseline:
+        cb, _ = cpu_reference(N, d, nq, k, 2, 1, budget_s=15.0)
+    line = {"metric": metric, "value": qps, "unit": "queries/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config,
+            "e2e": {"value": qps_e2e, "unit": "queries/s", "h2d_bytes_per_step": nq * d * 4,
+                    "d2h_bytes_per_step": nq * k * 12},
+            "gpu_launches": launches, "clocks": sampler.result(), "roofline": roof,
+            "p50_nq1_ms": p50_nq1, "roofline_nq1": roof_nq1, "cpu_baseline": cb}
+    print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,118 @@
+/*
+ * b200knn.h -- C ABI of libb200knn.so: an exact (brute-force) squared-L2 k-NN index for
+ * NVIDIA B200 (sm_100a).  It is the drop-in boundary for the `faiss.IndexFlatL2` object
+ * used by the retrieval path of oscka/rag-llm-k8s (`llm/rag.py`).  Each entry point cites
+ * the reference call it stands in for (file:line under /root/reference).
+ *
+ * Conventions
+ *   - plain C types only; no exception crosses the boundary;
+ *   - every function returns 0 on success or a negative B2K_E* code; the message for the
+ *     calling thread's last failure is b2k_last_error();
+ *   - vectors are float32, row-major, C-contiguous; ids are int64 (row position, 0-based,
+ *     sequential across adds); distances are SQUARED L2 in float32;
+ *   - `on_device != 0` means the data pointers of that call are device pointers on the
+ *     index's GPU and `stream` is the cudaStream_t to enqueue on (NULL = the index's own
+ *     stream); the call then returns after enqueueing.  With `on_device == 0` the pointers
+ *     are host memory and the call returns when the results are in the caller's buffers;
+ *   - the handle owns all device memory; the library never keeps a caller pointer past
+ *     return;
+ *   - different handles are independent across threads; calls on ONE handle are
+ *     serialised internally (search included: it uses the handle's workspace).
+ *   - there is no CPU fallback: without a usable sm_100 GPU every compute call fails with
+ *     B2K_ECUDA.
+ */
+#ifndef B200KNN_H_
+#define B200KNN_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2K_OK 0
+#define B2K_EINVAL (-1)  /* bad argument (shape, k <= 0, null pointer)              */
+#define B2K_ECUDA (-2)   /* CUDA error or no usable device (sticky on the handle)   */
+#define B2K_EIO (-3)     /* file missing / short / not an IxF2 file                 */
+#define B2K_ENOMEM (-4)  /* device or host allocation failed                        */
+#define B2K_ELIMIT (-5)  /* size beyond a documented limit (k > B2K_MAX_K, ...)     */
+
+#define B2K_MAX_K 1024   /* largest k of one search call (north_star: k <= 1024)     */
+
+#if defined(__GNUC__)
+#define B2K_API __attribute__((visibility("default")))
+#else
+#define B2K_API
+#endif
+
+typedef struct b2k_index b2k_index;
+
+/* faiss.IndexFlatL2(dimension) -- llm/rag.py:61, :71.  Empty index, d fixed for life. */
+B2K_API int b2k_create(int d, int device, b2k_index** out);
+B2K_API int b2k_destroy(b2k_index* h);
+
+/* index.add(vectors_np) -- llm/rag.py:80.  Appends n rows; also computes ||x||^2 per row
+ * (kernel K1) and, once a batched search has been made, the TF32 residual rows. */
+B2K_API int b2k_add(b2k_index* h, int64_t n, const float* x, int on_device, void* stream);
+
+/* D, I = index.search(xq, k) -- llm/rag.py:116.  For each of nq queries the k smallest
+ * squared distances ascending with their row ids; if ntotal < k the tail is I = -1,
+ * D = FLT_MAX (3.4028235e38), which is what rag.py:118-119 then indexes metadata with. */
+B2K_API int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, int64_t* I,
+               int on_device, void* stream);
+
+/* index.ntotal, index.d -- llm/rag.py:86, :190-191. */
+B2K_API int64_t b2k_ntotal(const b2k_index* h);
+B2K_API int b2k_d(const b2k_index* h);
+
+/* index.reset() -- named by the north_star; never called in llm/rag.py.  Drops all rows. */
+B2K_API int b2k_reset(b2k_index* h);
+
+/* faiss.write_index(index, path) -- llm/rag.py:62, :82.  Byte-exact "IxF2" file
+ * (45-byte header + ntotal*d float32), written to path.tmp then renamed. */
+B2K_API int b2k_write(const b2k_index* h, const char* path);
+
+/* faiss.read_index(path) -- llm/rag.py:74, :153, :186.  Missing file -> B2K_EIO. */
+B2K_API int b2k_read(const char* path, int device, b2k_index** out);
+
+/* Message of the calling thread's last failed call ("" if none). */
+B2K_API const char* b2k_last_error(void);
+
+/* ---- additions with no faiss call site in llm/rag.py (benchmarks, sharding, tests) ---- */
+
+/* Pre-size the row storage so later adds do not reallocate (std::vector::reserve). */
+B2K_API int b2k_reserve(b2k_index* h, int64_t nrows);
+
+/* Copy rows [i0, i0+n) back out (faiss `reconstruct_n`; used by write_index and tests). */
+B2K_API int b2k_get_rows(const b2k_index* h, int64_t i0, int64_t n, float* out, int on_device);
+
+/* Counter-based synthetic rows generated on the GPU, bit-identical to oracle `orc_synth`:
+ * value(seed, row, col) ~ unit-variance sum of four 16-bit uniforms.  b2k_add_synthetic
+ * appends rows first_row .. first_row+n-1 of that stream without touching host memory
+ * (100M x 768 does not fit in host RAM; SURVEY.md section 7, hard part 5). */
+B2K_API int b2k_synth(int device, uint64_t seed, int64_t row0, int64_t nrows, int d, float* out_dev,
+              void* stream);
+B2K_API int b2k_add_synthetic(b2k_index* h, int64_t n, uint64_t seed, int64_t first_row);
+
+/* Combine step of the row-sharded search: Din/Iin hold nlists
+ * result sets [nlists][nq][k] (e.g. the all-gathered per-GPU top-k); writes the k
+ * smallest (distance, id) per query.  id_offset (nullable, host array of nlists values)
+ * is added to the non-negative ids of each list.  nlists * k <= 8192. */
+B2K_API int b2k_merge_topk(int device, int nlists, int64_t nq, int64_t k, const float* Din,
+                   const int64_t* Iin, const int64_t* id_offset, float* D, int64_t* I,
+                   int on_device, void* stream);
+
+/* Tuning / test hooks.  Keys: "path" (0 auto, 1 force the scan kernel, 2 force the
+ * tensor-core kernel), "scan_ctas_per_sm".  Unknown key -> B2K_EINVAL. */
+B2K_API int b2k_set_option(b2k_index* h, const char* key, int64_t value);
+
+/* Number of kernels this library has launched in this process (bench `gpu_launches`). */
+B2K_API int64_t b2k_launch_count(void);
+
+/* Library version: major*10000 + minor*100 + patch. */
+B2K_API int b2k_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200KNN_H_ */

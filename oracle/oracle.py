@@ -1,0 +1,175 @@
+"""CPU oracle for the IndexFlatL2 path -- TEST INFRASTRUCTURE, NOT PRODUCT CODE.
+
+PARITY UNPINNED (see flat_l2_oracle.c): faiss-cpu is absent and the reference holds no
+golden vectors, so this restates faiss's published behaviour for the calls in
+/root/reference/llm/rag.py:61-86,114-120 and is cross-checked against an independent
+float64 brute force (`truth_f64`) plus hand-derived known answers (tests/golden/).
+
+Only tests/, __graft_entry__.smoke() and bench.py's CPU-baseline legs import this.
+"""
+import ctypes
+import os
+import struct
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_lib = None
+
+FLT_MAX = np.float32(3.4028234663852886e38)
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        path = os.path.join(_HERE, "liboracle.so")
+        if not os.path.exists(path):
+            import importlib.util
+            spec = importlib.util.spec_from_file_location("_oracle_build", os.path.join(_HERE, "build.py"))
+            mod = importlib.util.module_from_spec(spec)
+            spec.loader.exec_module(mod)
+            mod.build()
+        L = ctypes.CDLL(path)
+        fp = ctypes.POINTER(ctypes.c_float)
+        ip = ctypes.POINTER(ctypes.c_int64)
+        L.orc_search.argtypes = [fp, ctypes.c_int64, ctypes.c_int, fp, ctypes.c_int64, ctypes.c_int64, fp, ip, ctypes.c_int]
+        L.orc_search.restype = ctypes.c_int
+        L.orc_merge.argtypes = [ctypes.c_int, ctypes.c_int64, ctypes.c_int64, fp, ip, fp, ip]
+        L.orc_merge.restype = ctypes.c_int
+        L.orc_synth.argtypes = [ctypes.c_uint64, ctypes.c_int64, ctypes.c_int64, ctypes.c_int, fp]
+        L.orc_synth.restype = None
+        L.orc_num_threads.restype = ctypes.c_int
+        _lib = L
+    return _lib
+
+
+def _f(a):
+    return a.ctypes.data_as(ctypes.POINTER(ctypes.c_float))
+
+
+def _i(a):
+    return a.ctypes.data_as(ctypes.POINTER(ctypes.c_int64))
+
+
+MODE_FAISS, MODE_DIRECT, MODE_EXPAND, MODE_DIRECT_ROWPAR = 0, 1, 2, 3
+
+
+def search(x, q, k, mode=MODE_FAISS):
+    """faiss `IndexFlatL2.search` restated (rag.py:116): returns (D float32 [nq,k], I int64 [nq,k])."""
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    q = np.ascontiguousarray(q, dtype=np.float32)
+    assert x.ndim == 2 and q.ndim == 2 and (x.shape[0] == 0 or x.shape[1] == q.shape[1])
+    assert k > 0
+    nq, d = q.shape
+    D = np.empty((nq, k), np.float32)
+    I = np.empty((nq, k), np.int64)
+    rc = lib().orc_search(_f(x), x.shape[0], d, _f(q), nq, k, _f(D), _i(I), mode)
+    assert rc == 0
+    return D, I
+
+
+def merge(Dl, Il):
+    """Combine per-shard results [nlists,nq,k] into the global top-k (row-sharded search)."""
+    Dl = np.ascontiguousarray(Dl, dtype=np.float32)
+    Il = np.ascontiguousarray(Il, dtype=np.int64)
+    nl, nq, k = Dl.shape
+    D = np.empty((nq, k), np.float32)
+    I = np.empty((nq, k), np.int64)
+    lib().orc_merge(nl, nq, k, _f(Dl), _i(Il), _f(D), _i(I))
+    return D, I
+
+
+def synth(seed, row0, nrows, d):
+    """Counter-based synthetic rows, bit-identical to the CUDA generator (b2k_synth)."""
+    out = np.empty((nrows, d), np.float32)
+    if nrows:
+        lib().orc_synth(seed, row0, nrows, d, _f(out))
+    return out
+
+
+def num_threads():
+    return lib().orc_num_threads()
+
+
+def truth_f64(x, q, k, chunk=262144):
+    """Independent ground truth: float64 brute force, (distance, id) lexicographic top-k.
+
+    Returns (D float64 [nq,k] padded with +inf, I int64 padded with -1, Dall-less)."""
+    x = np.asarray(x, dtype=np.float64)
+    q = np.asarray(q, dtype=np.float64)
+    nq = q.shape[0]
+    n = x.shape[0]
+    bestD = np.full((nq, 0), np.inf)
+    bestI = np.full((nq, 0), -1, np.int64)
+    qn = (q * q).sum(1)[:, None]
+    for j0 in range(0, n, chunk):
+        xb = x[j0:j0 + chunk]
+        dist = qn + (xb * xb).sum(1)[None, :] - 2.0 * (q @ xb.T)
+        # the expansion in float64 keeps ~1e-13 relative accuracy at these magnitudes
+        np.maximum(dist, 0.0, out=dist)
+        ids = np.arange(j0, j0 + xb.shape[0], dtype=np.int64)[None, :].repeat(nq, 0)
+        D = np.concatenate([bestD, dist], 1)
+        I = np.concatenate([bestI, ids], 1)
+        order = np.lexsort((I, D), axis=1)[:, :k]
+        bestD = np.take_along_axis(D, order, 1)
+        bestI = np.take_along_axis(I, order, 1)
+    if bestD.shape[1] < k:
+        pad = k - bestD.shape[1]
+        bestD = np.concatenate([bestD, np.full((nq, pad), np.inf)], 1)
+        bestI = np.concatenate([bestI, np.full((nq, pad), -1, np.int64)], 1)
+    return bestD, bestI
+
+
+def dist_f64(x, q, ids):
+    """float64 squared distances from each query to the rows named in ids [nq,k] (-1 -> inf)."""
+    x = np.asarray(x, dtype=np.float64)
+    q = np.asarray(q, dtype=np.float64)
+    out = np.full(ids.shape, np.inf)
+    for i in range(ids.shape[0]):
+        m = ids[i] >= 0
+        diff = x[ids[i][m]] - q[i][None, :]
+        out[i][m] = (diff * diff).sum(1)
+    return out
+
+
+# --------------------------------------------------------------------------------------
+# IxF2: the file faiss.write_index / read_index produce for an IndexFlatL2
+# (rag.py:62,74,82,153,186).  Little-endian, no padding [faiss-upstream, SURVEY.md 8a-a5]:
+#   "IxF2" | d:int32 | ntotal:int64 | 1<<20:int64 | 1<<20:int64 | is_trained:uint8 |
+#   metric_type:int32 (1 = L2) | count:uint64 (= ntotal*d) | count float32 values
+
+_HDR = struct.Struct("<4siqqqBiQ")
+assert _HDR.size == 45
+
+
+def write_ixf2(path, x, d=None):
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    if d is None:
+        d = x.shape[1]
+    n = x.shape[0] if x.size else 0
+    with open(path, "wb") as f:
+        f.write(_HDR.pack(b"IxF2", d, n, 1 << 20, 1 << 20, 1, 1, n * d))
+        if n:
+            f.write(x.tobytes())
+
+
+def read_ixf2(path):
+    with open(path, "rb") as f:
+        hdr = f.read(45)
+        if len(hdr) != 45:
+            raise RuntimeError("short IxF2 header")
+        four, d, n, _d0, _d1, trained, metric, count = _HDR.unpack(hdr)
+        if four != b"IxF2":
+            raise RuntimeError("not an IxF2 file: %r" % four)
+        if metric != 1 or count != n * d:
+            raise RuntimeError("inconsistent IxF2 header")
+        data = np.frombuffer(f.read(4 * count), dtype=np.float32)
+        if data.size != count:
+            raise RuntimeError("truncated IxF2 payload")
+    return d, data.reshape(n, d).copy()
+
+
+def empty_ixf2_bytes(d):
+    """The 45 bytes SURVEY.md 8c lists for an empty index of dimension d."""
+    return (b"IxF2" + struct.pack("<i", d) + b"\x00" * 8 + b"\x00\x00\x10\x00\x00\x00\x00\x00" * 2
+            + b"\x01" + b"\x01\x00\x00\x00" + b"\x00" * 8)

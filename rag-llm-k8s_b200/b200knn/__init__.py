@@ -1,0 +1,206 @@
+"""b200knn -- drop-in for the `faiss` names used by oscka/rag-llm-k8s `llm/rag.py`.
+
+    import b200knn as faiss                      # the one edit to llm/rag.py (line 6)
+    index = faiss.IndexFlatL2(d)                 # rag.py:61, :71
+    index.add(vectors_np)                        # rag.py:80
+    D, I = index.search(q.reshape(1, -1), 5)     # rag.py:116
+    index.ntotal, index.d                        # rag.py:86, :190-191
+    faiss.write_index(index, path)               # rag.py:62, :82
+    index = faiss.read_index(path)               # rag.py:74, :153, :186
+
+Every call goes through the C ABI of libb200knn.so (include/b200knn.h) onto a B200; there
+is no CPU path.  numpy inputs are host buffers (results are fresh numpy arrays, as faiss
+returns); torch CUDA tensors are used in place (results are torch tensors on that device,
+enqueued on torch's current stream).
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import _lib
+from ._lib import MAX_K
+
+__all__ = ["IndexFlatL2", "write_index", "read_index", "METRIC_L2", "default_device", "launch_count"]
+
+METRIC_L2 = 1
+__version__ = "0.1.0"
+
+
+def default_device():
+    """GPU used by new indexes: $B200KNN_DEVICE, else $LOCAL_RANK (torchrun), else 0."""
+    for var in ("B200KNN_DEVICE", "LOCAL_RANK"):
+        v = os.environ.get(var)
+        if v not in (None, ""):
+            return int(v)
+    return 0
+
+
+def launch_count():
+    return int(_lib.lib().b2k_launch_count())
+
+
+def _is_torch(x):
+    return type(x).__module__.split(".")[0] == "torch"
+
+
+def _as_host_f32(x, d, what):
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    assert x.ndim == 2, "%s: expected a 2-D array, got shape %s" % (what, x.shape)
+    assert x.shape[1] == d, "%s: dimension mismatch, index has d=%d, got %d" % (what, d, x.shape[1])
+    return x
+
+
+def _as_dev_f32(x, d, device, what):
+    import torch
+    assert x.is_cuda and x.device.index == device, "%s: tensor must live on cuda:%d" % (what, device)
+    assert x.dim() == 2 and x.shape[1] == d, "%s: expected shape (n, %d), got %s" % (what, d, tuple(x.shape))
+    if x.dtype != torch.float32 or not x.is_contiguous():
+        x = x.to(torch.float32).contiguous()
+    return x
+
+
+class IndexFlatL2:
+    """Exact squared-L2 index on one B200; the surface of `faiss.IndexFlatL2` that rag.py uses."""
+
+    is_trained = True
+    metric_type = METRIC_L2
+
+    def __init__(self, d, device=None, _handle=None):
+        self._h = None
+        self.device = default_device() if device is None else int(device)
+        if _handle is not None:
+            self._h = _handle
+            return
+        h = C.c_void_p()
+        _lib.check(_lib.lib().b2k_create(int(d), self.device, C.byref(h)))
+        self._h = h
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            try:
+                _lib.lib().b2k_destroy(h)
+            except Exception:
+                pass
+
+    @property
+    def d(self):
+        return int(_lib.lib().b2k_d(self._h))
+
+    @property
+    def ntotal(self):
+        return int(_lib.lib().b2k_ntotal(self._h))
+
+    def _stream(self):
+        import torch
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def add(self, x):
+        """Append rows (rag.py:80).  Ids are row positions, sequential across adds."""
+        L = _lib.lib()
+        if _is_torch(x) and x.is_cuda:
+            x = _as_dev_f32(x, self.d, self.device, "add")
+            _lib.check(L.b2k_add(self._h, x.shape[0], C.c_void_p(x.data_ptr()), 1, self._stream()))
+            return
+        if _is_torch(x):
+            x = x.detach().cpu().numpy()
+        x = _as_host_f32(x, self.d, "add")
+        _lib.check(L.b2k_add(self._h, x.shape[0], x.ctypes.data_as(C.c_void_p), 0, None))
+
+    def search(self, x, k):
+        """(D, I) = k nearest stored rows of each query row (rag.py:116)."""
+        L = _lib.lib()
+        k = int(k)
+        assert k > 0, "search: k must be positive"
+        if _is_torch(x) and x.is_cuda:
+            import torch
+            x = _as_dev_f32(x, self.d, self.device, "search")
+            nq = x.shape[0]
+            D = torch.empty((nq, k), dtype=torch.float32, device=x.device)
+            I = torch.empty((nq, k), dtype=torch.int64, device=x.device)
+            _lib.check(L.b2k_search(self._h, nq, C.c_void_p(x.data_ptr()), k, C.c_void_p(D.data_ptr()),
+                                    C.c_void_p(I.data_ptr()), 1, self._stream()))
+            return D, I
+        if _is_torch(x):
+            x = x.detach().cpu().numpy()
+        x = _as_host_f32(x, self.d, "search")
+        nq = x.shape[0]
+        D = np.empty((nq, k), dtype=np.float32)
+        I = np.empty((nq, k), dtype=np.int64)
+        _lib.check(L.b2k_search(self._h, nq, x.ctypes.data_as(C.c_void_p), k, D.ctypes.data_as(C.c_void_p),
+                                I.ctypes.data_as(C.c_void_p), 0, None))
+        return D, I
+
+    def reset(self):
+        _lib.check(_lib.lib().b2k_reset(self._h))
+
+    def reserve(self, nrows):
+        _lib.check(_lib.lib().b2k_reserve(self._h, int(nrows)))
+
+    def reconstruct_n(self, i0=0, n=-1):
+        if n < 0:
+            n = self.ntotal - i0
+        out = np.empty((n, self.d), dtype=np.float32)
+        _lib.check(_lib.lib().b2k_get_rows(self._h, int(i0), int(n), out.ctypes.data_as(C.c_void_p), 0))
+        return out
+
+    def add_synthetic(self, n, seed, first_row=0):
+        """Append n rows of the counter-based synthetic stream, generated on the GPU."""
+        _lib.check(_lib.lib().b2k_add_synthetic(self._h, int(n), int(seed), int(first_row)))
+
+    def set_option(self, key, value):
+        _lib.check(_lib.lib().b2k_set_option(self._h, key.encode(), int(value)))
+
+
+def write_index(index, path):
+    """faiss.write_index (rag.py:62, :82): byte-exact IxF2 file, written atomically."""
+    _lib.check(_lib.lib().b2k_write(index._h, os.fsencode(path)))
+
+
+def read_index(path, device=None):
+    """faiss.read_index (rag.py:74, :153, :186); a missing file raises RuntimeError."""
+    dev = default_device() if device is None else int(device)
+    h = C.c_void_p()
+    _lib.check(_lib.lib().b2k_read(os.fsencode(path), dev, C.byref(h)))
+    return IndexFlatL2(0, device=dev, _handle=h)
+
+
+def synth(seed, row0, nrows, d, device=None):
+    """Synthetic rows as a torch CUDA tensor (same stream as oracle.synth on the CPU)."""
+    import torch
+    dev = default_device() if device is None else int(device)
+    out = torch.empty((nrows, d), dtype=torch.float32, device="cuda:%d" % dev)
+    st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+    _lib.check(_lib.lib().b2k_synth(dev, int(seed), int(row0), int(nrows), int(d), C.c_void_p(out.data_ptr()), st))
+    return out
+
+
+def merge_topk(Dl, Il, id_offset=None, device=None):
+    """Combine [nlists, nq, k] result sets into the global (D, I) -- the sharded search's last step."""
+    L = _lib.lib()
+    off = None
+    if id_offset is not None:
+        off_arr = np.ascontiguousarray(id_offset, dtype=np.int64)
+        off = off_arr.ctypes.data_as(C.c_void_p)
+    if _is_torch(Dl):
+        import torch
+        dev = Dl.device.index
+        Dl = Dl.contiguous()
+        Il = Il.contiguous()
+        nl, nq, k = Dl.shape
+        D = torch.empty((nq, k), dtype=torch.float32, device=Dl.device)
+        I = torch.empty((nq, k), dtype=torch.int64, device=Dl.device)
+        st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        _lib.check(L.b2k_merge_topk(dev, nl, nq, k, C.c_void_p(Dl.data_ptr()), C.c_void_p(Il.data_ptr()), off,
+                                    C.c_void_p(D.data_ptr()), C.c_void_p(I.data_ptr()), 1, st))
+        return D, I
+    dev = default_device() if device is None else int(device)
+    Dl = np.ascontiguousarray(Dl, dtype=np.float32)
+    Il = np.ascontiguousarray(Il, dtype=np.int64)
+    nl, nq, k = Dl.shape
+    D = np.empty((nq, k), np.float32)
+    I = np.empty((nq, k), np.int64)
+    _lib.check(L.b2k_merge_topk(dev, nl, nq, k, Dl.ctypes.data_as(C.c_void_p), Il.ctypes.data_as(C.c_void_p), off,
+                                D.ctypes.data_as(C.c_void_p), I.ctypes.data_as(C.c_void_p), 0, None))
+    return D, I

@@ -1,0 +1,564 @@
+// index.cu -- the C ABI of libb200knn.so (declared in include/b200knn.h): index lifecycle,
+// row storage in HBM, IxF2 persistence and the search dispatch.
+//
+// Mirrors the `faiss.IndexFlatL2` surface used by /root/reference/llm/rag.py
+// (:61/:71 construct, :80 add, :116 search, :86/:190-191 ntotal/d, :62/:82 write_index,
+// :74/:153/:186 read_index).  HBM layout per handle:
+//     x     [capacity][d] float32  row-major, the rows as given            (K2, K3 "hi" operand)
+//     norms [capacity]    float32  ||x||^2, written by K1 at add()         (K3 epilogue)
+//     xlo   [capacity][d] float32  TF32 residual rows, only once a batched (K3 "lo" operand)
+//                                  search has been made on this handle
+//     ws    scratch: device copies of queries / results for host callers, per-CTA partial
+//           top-k lists, K3 candidate lists.
+#include <errno.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+#include <mutex>
+#include <new>
+#include <string>
+
+#include "common.cuh"
+#include "kernels.h"
+#include "k3_api.h"
+
+namespace b2k {
+
+static thread_local std::string t_err;
+std::atomic<int64_t> g_launches{0};
+
+void set_error(const char* fmt, ...) {
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    t_err = buf;
+}
+
+}  // namespace b2k
+
+using namespace b2k;
+
+struct b2k_index {
+    int d = 0, device = 0, sm_count = 148;
+    int64_t ntotal = 0, capacity = 0;
+    float* x = nullptr;
+    float* norms = nullptr;
+    float* xlo = nullptr;
+    bool lo_enabled = false;
+    cudaStream_t stream = nullptr;
+    mutable std::mutex mu;
+    void* ws = nullptr;
+    size_t ws_bytes = 0;
+    void* pin = nullptr;
+    size_t pin_bytes = 0;
+    unsigned int* done = nullptr;
+    int opt_path = 0;
+    int opt_scan_ctas_per_sm = 2;
+    int sticky = 0;
+    K3State* k3 = nullptr;
+};
+
+static constexpr int64_t MAX_ROWS = 0xFFFFFFFEll;  // row index lives in the low 32 bits of a key
+static constexpr size_t IO_CHUNK = (size_t)64 << 20;
+
+namespace {
+
+struct DeviceGuard {
+    int prev = -1;
+    bool ok = false;
+    explicit DeviceGuard(int dev) {
+        if (cudaGetDevice(&prev) != cudaSuccess) { prev = -1; }
+        ok = (cudaSetDevice(dev) == cudaSuccess);
+    }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+int check_device(int device, int* sm_count) {
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) {
+        set_error("no usable CUDA device (%s); libb200knn has no CPU fallback",
+                  e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+        return B2K_ECUDA;
+    }
+    if (device < 0 || device >= count) {
+        set_error("device %d out of range (0..%d)", device, count - 1);
+        return B2K_EINVAL;
+    }
+    cudaDeviceProp prop;
+    B2K_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10) {
+        set_error("device %d is sm_%d%d; libb200knn is built for sm_100a (B200) only", device, prop.major, prop.minor);
+        return B2K_ECUDA;
+    }
+    if (sm_count) *sm_count = prop.multiProcessorCount;
+    return B2K_OK;
+}
+
+int ensure_ws(b2k_index* h, size_t bytes) {
+    if (bytes <= h->ws_bytes) return B2K_OK;
+    if (h->ws) { B2K_CUDA(cudaFree(h->ws)); h->ws = nullptr; h->ws_bytes = 0; }  // cudaFree synchronises
+    size_t want = bytes + bytes / 4 + 4096;
+    cudaError_t e = cudaMalloc(&h->ws, want);
+    if (e != cudaSuccess) { cudaGetLastError(); set_error("workspace cudaMalloc(%zu) failed: %s", want, cudaGetErrorString(e)); return B2K_ENOMEM; }
+    h->ws_bytes = want;
+    return B2K_OK;
+}
+
+int ensure_pin(b2k_index* h, size_t bytes) {
+    if (bytes <= h->pin_bytes) return B2K_OK;
+    if (h->pin) { B2K_CUDA(cudaStreamSynchronize(h->stream)); B2K_CUDA(cudaFreeHost(h->pin)); h->pin = nullptr; h->pin_bytes = 0; }
+    size_t want = bytes + bytes / 4 + 4096;
+    cudaError_t e = cudaMallocHost(&h->pin, want);
+    if (e != cudaSuccess) { cudaGetLastError(); set_error("cudaMallocHost(%zu) failed: %s", want, cudaGetErrorString(e)); return B2K_ENOMEM; }
+    h->pin_bytes = want;
+    return B2K_OK;
+}
+
+int grow(b2k_index* h, int64_t need_rows) {
+    if (need_rows <= h->capacity) return B2K_OK;
+    if (need_rows > MAX_ROWS) { set_error("index limited to %lld rows per GPU", (long long)MAX_ROWS); return B2K_ELIMIT; }
+    int64_t cap = h->capacity * 2;
+    if (cap < need_rows) cap = need_rows;
+    if (cap < 1024) cap = 1024;
+    if (cap > MAX_ROWS) cap = MAX_ROWS;
+    float *nx = nullptr, *nn = nullptr, *nl = nullptr;
+    size_t row_bytes = (size_t)h->d * sizeof(float);
+    cudaError_t e = cudaMalloc(&nx, (size_t)cap * row_bytes);
+    if (e != cudaSuccess && cap > need_rows) {  // doubling did not fit: take exactly what is needed
+        cudaGetLastError();
+        cap = need_rows;
+        e = cudaMalloc(&nx, (size_t)cap * row_bytes);
+    }
+    if (e == cudaSuccess) e = cudaMalloc(&nn, (size_t)cap * sizeof(float));
+    if (e == cudaSuccess && h->lo_enabled) e = cudaMalloc(&nl, (size_t)cap * row_bytes);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        cudaFree(nx); cudaFree(nn); cudaFree(nl);
+        set_error("cudaMalloc for %lld rows x %d failed: %s", (long long)cap, h->d, cudaGetErrorString(e));
+        return B2K_ENOMEM;
+    }
+    if (h->ntotal > 0) {
+        B2K_CUDA(cudaMemcpyAsync(nx, h->x, (size_t)h->ntotal * row_bytes, cudaMemcpyDeviceToDevice, h->stream));
+        B2K_CUDA(cudaMemcpyAsync(nn, h->norms, (size_t)h->ntotal * sizeof(float), cudaMemcpyDeviceToDevice, h->stream));
+        if (nl) B2K_CUDA(cudaMemcpyAsync(nl, h->xlo, (size_t)h->ntotal * row_bytes, cudaMemcpyDeviceToDevice, h->stream));
+        B2K_CUDA(cudaStreamSynchronize(h->stream));
+    }
+    cudaFree(h->x); cudaFree(h->norms); cudaFree(h->xlo);
+    h->x = nx; h->norms = nn; h->xlo = nl; h->capacity = cap;
+    if (h->k3) k3_invalidate_maps(h->k3);
+    return B2K_OK;
+}
+
+// Rows [first, first+n) of h->x are in place: compute their norms (and residual rows).
+int prep_new_rows(b2k_index* h, int64_t first, int64_t n, cudaStream_t st) {
+    return launch_row_prep(h->x + first * (int64_t)h->d, n, h->d, h->norms + first,
+                           h->lo_enabled ? h->xlo + first * (int64_t)h->d : nullptr, st);
+}
+
+int enable_lo(b2k_index* h, cudaStream_t st) {
+    if (h->lo_enabled) return B2K_OK;
+    if (h->capacity > 0) {
+        cudaError_t e = cudaMalloc(&h->xlo, (size_t)h->capacity * h->d * sizeof(float));
+        if (e != cudaSuccess) { cudaGetLastError(); set_error("cudaMalloc for TF32 residual rows failed: %s", cudaGetErrorString(e)); return B2K_ENOMEM; }
+    }
+    h->lo_enabled = true;
+    if (h->k3) k3_invalidate_maps(h->k3);
+    if (h->ntotal > 0) return launch_row_prep(h->x, h->ntotal, h->d, h->norms, h->xlo, st);
+    return B2K_OK;
+}
+
+int scan_search(b2k_index* h, int64_t nq, const float* qd, int k, float* Dd, int64_t* Id, unsigned char* ws_tail,
+                cudaStream_t st) {
+    const int grid = scan_grid(h->ntotal, h->sm_count, h->opt_scan_ctas_per_sm);
+    u64* partial = reinterpret_cast<u64*>(ws_tail);
+    for (int64_t q0 = 0; q0 < nq;) {
+        int qt = scan_pick_qt(nq - q0, k);
+        int rc = launch_scan(h->x, qd + q0 * (int64_t)h->d, h->ntotal, h->d, qt, k, grid, partial, h->done,
+                             Dd + q0 * k, Id + q0 * k, st);
+        if (rc) return rc;
+        q0 += qt;
+    }
+    return B2K_OK;
+}
+
+size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
+
+}  // namespace
+
+extern "C" {
+
+int b2k_version(void) { return 100; }
+
+const char* b2k_last_error(void) { return t_err.c_str(); }
+
+int64_t b2k_launch_count(void) { return g_launches.load(); }
+
+int b2k_create(int d, int device, b2k_index** out) {
+    if (!out) { set_error("b2k_create: out is null"); return B2K_EINVAL; }
+    *out = nullptr;
+    if (d <= 0) { set_error("b2k_create: d must be positive, got %d", d); return B2K_EINVAL; }
+    int sm = 148;
+    int rc = check_device(device, &sm);
+    if (rc) return rc;
+    DeviceGuard g(device);
+    b2k_index* h = new (std::nothrow) b2k_index();
+    if (!h) { set_error("out of host memory"); return B2K_ENOMEM; }
+    h->d = d; h->device = device; h->sm_count = sm;
+    cudaError_t e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaMalloc(&h->done, 256);
+    if (e == cudaSuccess) e = cudaMemset(h->done, 0, 256);
+    if (e != cudaSuccess) {
+        set_error("b2k_create: %s", cudaGetErrorString(e));
+        if (h->stream) cudaStreamDestroy(h->stream);
+        cudaFree(h->done);
+        delete h;
+        return B2K_ECUDA;
+    }
+    *out = h;
+    return B2K_OK;
+}
+
+int b2k_destroy(b2k_index* h) {
+    if (!h) return B2K_OK;
+    DeviceGuard g(h->device);
+    cudaDeviceSynchronize();
+    if (h->k3) k3_destroy(h->k3);
+    cudaFree(h->x); cudaFree(h->norms); cudaFree(h->xlo); cudaFree(h->ws); cudaFree(h->done);
+    if (h->pin) cudaFreeHost(h->pin);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+    return B2K_OK;
+}
+
+int64_t b2k_ntotal(const b2k_index* h) { return h ? h->ntotal : -1; }
+int b2k_d(const b2k_index* h) { return h ? h->d : -1; }
+
+int b2k_set_option(b2k_index* h, const char* key, int64_t value) {
+    if (!h || !key) { set_error("b2k_set_option: null argument"); return B2K_EINVAL; }
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (!strcmp(key, "path")) {
+        if (value < 0 || value > 2) { set_error("option path must be 0, 1 or 2"); return B2K_EINVAL; }
+        h->opt_path = (int)value;
+    } else if (!strcmp(key, "scan_ctas_per_sm")) {
+        if (value < 1 || value > 8) { set_error("option scan_ctas_per_sm must be 1..8"); return B2K_EINVAL; }
+        h->opt_scan_ctas_per_sm = (int)value;
+    } else {
+        set_error("unknown option '%s'", key);
+        return B2K_EINVAL;
+    }
+    return B2K_OK;
+}
+
+int b2k_reserve(b2k_index* h, int64_t nrows) {
+    if (!h || nrows < 0) { set_error("b2k_reserve: bad argument"); return B2K_EINVAL; }
+    std::lock_guard<std::mutex> lk(h->mu);
+    DeviceGuard g(h->device);
+    return grow(h, nrows);
+}
+
+int b2k_reset(b2k_index* h) {
+    if (!h) { set_error("b2k_reset: null handle"); return B2K_EINVAL; }
+    std::lock_guard<std::mutex> lk(h->mu);
+    DeviceGuard g(h->device);
+    B2K_CUDA(cudaDeviceSynchronize());
+    cudaFree(h->x); cudaFree(h->norms); cudaFree(h->xlo);
+    h->x = h->norms = h->xlo = nullptr;
+    h->ntotal = h->capacity = 0;
+    if (h->k3) k3_invalidate_maps(h->k3);
+    return B2K_OK;
+}
+
+int b2k_add(b2k_index* h, int64_t n, const float* x, int on_device, void* stream) {
+    if (!h) { set_error("b2k_add: null handle"); return B2K_EINVAL; }
+    if (n < 0 || (n > 0 && !x)) { set_error("b2k_add: bad argument (n=%lld)", (long long)n); return B2K_EINVAL; }
+    if (n == 0) return B2K_OK;
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (h->sticky) { set_error("handle has a sticky CUDA error (%d)", h->sticky); return B2K_ECUDA; }
+    DeviceGuard g(h->device);
+    int rc = grow(h, h->ntotal + n);
+    if (rc) return rc;
+    cudaStream_t st = (on_device && stream) ? (cudaStream_t)stream : h->stream;
+    float* dst = h->x + h->ntotal * (int64_t)h->d;
+    size_t bytes = (size_t)n * h->d * sizeof(float);
+    B2K_CUDA(cudaMemcpyAsync(dst, x, bytes, on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, st));
+    rc = prep_new_rows(h, h->ntotal, n, st);
+    if (rc) return rc;
+    h->ntotal += n;
+    if (!on_device) {
+        cudaError_t e = cudaStreamSynchronize(st);
+        if (e != cudaSuccess) { h->sticky = (int)e; set_error("b2k_add: %s", cudaGetErrorString(e)); return B2K_ECUDA; }
+    }
+    return B2K_OK;
+}
+
+int b2k_add_synthetic(b2k_index* h, int64_t n, uint64_t seed, int64_t first_row) {
+    if (!h || n < 0) { set_error("b2k_add_synthetic: bad argument"); return B2K_EINVAL; }
+    if (n == 0) return B2K_OK;
+    std::lock_guard<std::mutex> lk(h->mu);
+    DeviceGuard g(h->device);
+    int rc = grow(h, h->ntotal + n);
+    if (rc) return rc;
+    rc = launch_synth(seed, first_row, n, h->d, h->x + h->ntotal * (int64_t)h->d, h->stream);
+    if (rc) return rc;
+    rc = prep_new_rows(h, h->ntotal, n, h->stream);
+    if (rc) return rc;
+    h->ntotal += n;
+    B2K_CUDA(cudaStreamSynchronize(h->stream));
+    return B2K_OK;
+}
+
+int b2k_synth(int device, uint64_t seed, int64_t row0, int64_t nrows, int d, float* out_dev, void* stream) {
+    if (nrows < 0 || d <= 0 || (nrows > 0 && !out_dev)) { set_error("b2k_synth: bad argument"); return B2K_EINVAL; }
+    int rc = check_device(device, nullptr);
+    if (rc) return rc;
+    DeviceGuard g(device);
+    rc = launch_synth(seed, row0, nrows, d, out_dev, (cudaStream_t)stream);
+    if (rc) return rc;
+    if (!stream) B2K_CUDA(cudaStreamSynchronize(nullptr));
+    return B2K_OK;
+}
+
+int b2k_get_rows(const b2k_index* h, int64_t i0, int64_t n, float* out, int on_device) {
+    if (!h || i0 < 0 || n < 0 || (n > 0 && !out)) { set_error("b2k_get_rows: bad argument"); return B2K_EINVAL; }
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (i0 + n > h->ntotal) { set_error("b2k_get_rows: rows [%lld,%lld) out of range (ntotal=%lld)", (long long)i0, (long long)(i0 + n), (long long)h->ntotal); return B2K_EINVAL; }
+    if (n == 0) return B2K_OK;
+    DeviceGuard g(h->device);
+    B2K_CUDA(cudaMemcpyAsync(out, h->x + i0 * (int64_t)h->d, (size_t)n * h->d * sizeof(float),
+                             on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, h->stream));
+    B2K_CUDA(cudaStreamSynchronize(h->stream));
+    return B2K_OK;
+}
+
+int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, int64_t* I, int on_device,
+               void* stream) {
+    if (!h) { set_error("b2k_search: null handle"); return B2K_EINVAL; }
+    if (k <= 0) { set_error("b2k_search: k must be positive, got %lld", (long long)k); return B2K_EINVAL; }
+    if (nq < 0 || (nq > 0 && (!xq || !D || !I))) { set_error("b2k_search: bad argument"); return B2K_EINVAL; }
+    if (k > B2K_MAX_K) { set_error("b2k_search: k=%lld exceeds B2K_MAX_K=%d", (long long)k, B2K_MAX_K); return B2K_ELIMIT; }
+    if (nq == 0) return B2K_OK;
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (h->sticky) { set_error("handle has a sticky CUDA error (%d)", h->sticky); return B2K_ECUDA; }
+    DeviceGuard g(h->device);
+    const int kk = (int)k;
+    cudaStream_t st = (on_device && stream) ? (cudaStream_t)stream : h->stream;
+
+    const bool want_tc = h->ntotal > 0 && (h->opt_path == 2 || (h->opt_path == 0 && nq >= 20)) && k3_supported(h->d, kk);
+
+    // workspace: [queries][D][I] for host callers, then the kernels' scratch
+    size_t q_bytes = align256((size_t)nq * h->d * sizeof(float));
+    size_t d_bytes = align256((size_t)nq * kk * sizeof(float));
+    size_t i_bytes = align256((size_t)nq * kk * sizeof(int64_t));
+    size_t io_bytes = on_device ? 0 : q_bytes + d_bytes + i_bytes;
+    size_t scratch = 0;
+    if (h->ntotal > 0) {
+        if (want_tc) scratch = k3_scratch_bytes(h->sm_count, h->d, nq, kk);
+        else scratch = scan_partial_bytes(scan_grid(h->ntotal, h->sm_count, h->opt_scan_ctas_per_sm), 8, kk);
+    }
+    int rc = ensure_ws(h, io_bytes + align256(scratch));
+    if (rc) return rc;
+    unsigned char* wsb = static_cast<unsigned char*>(h->ws);
+    const float* qd = xq;
+    float* Dd = D;
+    int64_t* Id = I;
+    if (!on_device) {
+        rc = ensure_pin(h, io_bytes);
+        if (rc) return rc;
+        memcpy(h->pin, xq, (size_t)nq * h->d * sizeof(float));
+        B2K_CUDA(cudaMemcpyAsync(wsb, h->pin, (size_t)nq * h->d * sizeof(float), cudaMemcpyHostToDevice, st));
+        qd = reinterpret_cast<const float*>(wsb);
+        Dd = reinterpret_cast<float*>(wsb + q_bytes);
+        Id = reinterpret_cast<int64_t*>(wsb + q_bytes + d_bytes);
+    }
+    unsigned char* ws_tail = wsb + io_bytes;
+
+    if (h->ntotal == 0) {
+        rc = launch_fill_empty(Dd, Id, nq * kk, st);
+    } else if (want_tc) {
+        rc = enable_lo(h, st);
+        if (!rc) {
+            if (!h->k3) rc = k3_create(&h->k3, h->device, h->sm_count);
+            if (!rc) rc = k3_search(h->k3, h->x, h->xlo, h->norms, h->ntotal, h->capacity, h->d, qd, nq, kk, Dd, Id,
+                                    ws_tail, st);
+        }
+    } else {
+        rc = scan_search(h, nq, qd, kk, Dd, Id, ws_tail, st);
+    }
+    if (rc) return rc;
+
+    if (!on_device) {
+        unsigned char* pb = static_cast<unsigned char*>(h->pin);
+        B2K_CUDA(cudaMemcpyAsync(pb + q_bytes, Dd, (size_t)nq * kk * sizeof(float), cudaMemcpyDeviceToHost, st));
+        B2K_CUDA(cudaMemcpyAsync(pb + q_bytes + d_bytes, Id, (size_t)nq * kk * sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+        cudaError_t e = cudaStreamSynchronize(st);
+        if (e != cudaSuccess) { h->sticky = (int)e; set_error("b2k_search: %s", cudaGetErrorString(e)); return B2K_ECUDA; }
+        memcpy(D, pb + q_bytes, (size_t)nq * kk * sizeof(float));
+        memcpy(I, pb + q_bytes + d_bytes, (size_t)nq * kk * sizeof(int64_t));
+    }
+    return B2K_OK;
+}
+
+int b2k_merge_topk(int device, int nlists, int64_t nq, int64_t k, const float* Din, const int64_t* Iin,
+                   const int64_t* id_offset, float* D, int64_t* I, int on_device, void* stream) {
+    if (nlists <= 0 || nq < 0 || k <= 0 || (nq > 0 && (!Din || !Iin || !D || !I))) {
+        set_error("b2k_merge_topk: bad argument");
+        return B2K_EINVAL;
+    }
+    if ((int64_t)nlists * k > 8192) { set_error("b2k_merge_topk: nlists*k = %lld exceeds 8192", (long long)nlists * k); return B2K_ELIMIT; }
+    if (nq == 0) return B2K_OK;
+    int rc = check_device(device, nullptr);
+    if (rc) return rc;
+    DeviceGuard g(device);
+    cudaStream_t st = (cudaStream_t)stream;
+    size_t in_n = (size_t)nlists * nq * k, out_n = (size_t)nq * k;
+    int64_t* off_d = nullptr;
+    float *Din_d = const_cast<float*>(Din), *D_d = D;
+    int64_t *Iin_d = const_cast<int64_t*>(Iin), *I_d = I;
+    unsigned char* tmp = nullptr;
+    size_t off_bytes = align256(id_offset ? (size_t)nlists * 8 : 0);
+    size_t a = align256(in_n * 4), b = align256(in_n * 8), c = align256(out_n * 4), e2 = align256(out_n * 8);
+    size_t need = off_bytes + (on_device ? 0 : a + b + c + e2);
+    if (need) {
+        cudaError_t e = cudaMalloc(&tmp, need);
+        if (e != cudaSuccess) { cudaGetLastError(); set_error("b2k_merge_topk: cudaMalloc failed: %s", cudaGetErrorString(e)); return B2K_ENOMEM; }
+    }
+    rc = B2K_OK;
+    do {
+        cudaError_t e = cudaSuccess;
+        if (id_offset) {
+            off_d = reinterpret_cast<int64_t*>(tmp);
+            e = cudaMemcpyAsync(off_d, id_offset, (size_t)nlists * 8, cudaMemcpyHostToDevice, st);
+        }
+        if (e == cudaSuccess && !on_device) {
+            Din_d = reinterpret_cast<float*>(tmp + off_bytes);
+            Iin_d = reinterpret_cast<int64_t*>(tmp + off_bytes + a);
+            D_d = reinterpret_cast<float*>(tmp + off_bytes + a + b);
+            I_d = reinterpret_cast<int64_t*>(tmp + off_bytes + a + b + c);
+            e = cudaMemcpyAsync(Din_d, Din, in_n * 4, cudaMemcpyHostToDevice, st);
+            if (e == cudaSuccess) e = cudaMemcpyAsync(Iin_d, Iin, in_n * 8, cudaMemcpyHostToDevice, st);
+        }
+        if (e != cudaSuccess) { set_error("b2k_merge_topk: %s", cudaGetErrorString(e)); rc = B2K_ECUDA; break; }
+        rc = launch_merge_lists(nlists, nq, (int)k, Din_d, Iin_d, off_d, D_d, I_d, st);
+        if (rc) break;
+        if (!on_device) {
+            e = cudaMemcpyAsync(D, D_d, out_n * 4, cudaMemcpyDeviceToHost, st);
+            if (e == cudaSuccess) e = cudaMemcpyAsync(I, I_d, out_n * 8, cudaMemcpyDeviceToHost, st);
+        }
+        if (e == cudaSuccess && tmp) e = cudaStreamSynchronize(st);  // tmp is freed below
+        if (e != cudaSuccess) { set_error("b2k_merge_topk: %s", cudaGetErrorString(e)); rc = B2K_ECUDA; }
+    } while (0);
+    if (tmp) cudaFree(tmp);
+    return rc;
+}
+
+// ---- IxF2 persistence ------------------------------------------------------------------
+// Layout (little-endian, packed) [faiss-upstream index_write.cpp, SURVEY.md 8a-a5]:
+//   "IxF2" | d int32 | ntotal int64 | 1<<20 int64 | 1<<20 int64 | is_trained u8 (1) |
+//   metric_type int32 (1 = L2) | count u64 (= ntotal*d) | count float32
+
+static const size_t IXF2_HEADER = 45;
+
+static void put_header(unsigned char* b, int d, int64_t n) {
+    memcpy(b, "IxF2", 4);
+    int32_t d32 = d; memcpy(b + 4, &d32, 4);
+    memcpy(b + 8, &n, 8);
+    int64_t dummy = 1 << 20; memcpy(b + 16, &dummy, 8); memcpy(b + 24, &dummy, 8);
+    b[32] = 1;
+    int32_t metric = 1; memcpy(b + 33, &metric, 4);
+    uint64_t count = (uint64_t)n * (uint64_t)d; memcpy(b + 37, &count, 8);
+}
+
+int b2k_write(const b2k_index* hc, const char* path) {
+    b2k_index* h = const_cast<b2k_index*>(hc);
+    if (!h || !path) { set_error("b2k_write: null argument"); return B2K_EINVAL; }
+    std::lock_guard<std::mutex> lk(h->mu);
+    DeviceGuard g(h->device);
+    std::string tmp = std::string(path) + ".tmp";
+    FILE* f = fopen(tmp.c_str(), "wb");
+    if (!f) { set_error("could not open %s for writing: %s", tmp.c_str(), strerror(errno)); return B2K_EIO; }
+    unsigned char hdr[IXF2_HEADER];
+    put_header(hdr, h->d, h->ntotal);
+    int rc = B2K_OK;
+    if (fwrite(hdr, 1, IXF2_HEADER, f) != IXF2_HEADER) rc = B2K_EIO;
+    size_t total = (size_t)h->ntotal * h->d * sizeof(float), done = 0;
+    if (!rc && total) {
+        rc = ensure_pin(h, total < IO_CHUNK ? total : IO_CHUNK);
+        while (!rc && done < total) {
+            size_t n = total - done < IO_CHUNK ? total - done : IO_CHUNK;
+            cudaError_t e = cudaMemcpyAsync(h->pin, reinterpret_cast<unsigned char*>(h->x) + done, n, cudaMemcpyDeviceToHost, h->stream);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+            if (e != cudaSuccess) { set_error("b2k_write: %s", cudaGetErrorString(e)); rc = B2K_ECUDA; break; }
+            if (fwrite(h->pin, 1, n, f) != n) { rc = B2K_EIO; break; }
+            done += n;
+        }
+    }
+    if (fclose(f) != 0 && !rc) rc = B2K_EIO;
+    if (rc == B2K_EIO) set_error("error writing %s: %s", tmp.c_str(), strerror(errno));
+    if (!rc && rename(tmp.c_str(), path) != 0) { set_error("could not rename %s to %s: %s", tmp.c_str(), path, strerror(errno)); rc = B2K_EIO; }
+    if (rc) remove(tmp.c_str());
+    return rc;
+}
+
+int b2k_read(const char* path, int device, b2k_index** out) {
+    if (!path || !out) { set_error("b2k_read: null argument"); return B2K_EINVAL; }
+    *out = nullptr;
+    FILE* f = fopen(path, "rb");
+    if (!f) { set_error("could not open %s for reading: %s", path, strerror(errno)); return B2K_EIO; }
+    unsigned char hdr[IXF2_HEADER];
+    if (fread(hdr, 1, IXF2_HEADER, f) != IXF2_HEADER) { fclose(f); set_error("%s: short read of the index header", path); return B2K_EIO; }
+    if (memcmp(hdr, "IxF2", 4) != 0) {
+        fclose(f);
+        set_error("%s: index type '%.4s' not supported (only IxF2 = IndexFlatL2)", path, (const char*)hdr);
+        return B2K_EIO;
+    }
+    int32_t d32, metric; int64_t n; uint64_t count;
+    memcpy(&d32, hdr + 4, 4); memcpy(&n, hdr + 8, 8); memcpy(&metric, hdr + 33, 4); memcpy(&count, hdr + 37, 8);
+    if (d32 <= 0 || n < 0 || metric != 1 || count != (uint64_t)n * (uint64_t)d32) {
+        fclose(f);
+        set_error("%s: inconsistent IxF2 header (d=%d ntotal=%lld metric=%d count=%llu)", path, d32, (long long)n, metric, (unsigned long long)count);
+        return B2K_EIO;
+    }
+    b2k_index* h = nullptr;
+    int rc = b2k_create(d32, device, &h);
+    if (rc) { fclose(f); return rc; }
+    {
+        std::lock_guard<std::mutex> lk(h->mu);
+        DeviceGuard g(h->device);
+        size_t total = (size_t)n * d32 * sizeof(float), done = 0;
+        if (n > 0) rc = grow(h, n);
+        if (!rc && total) {
+            // two pinned halves: the H2D copy of one overlaps the fread of the other
+            size_t half = total < IO_CHUNK ? total : IO_CHUNK;
+            rc = ensure_pin(h, 2 * half);
+            int which = 0;
+            cudaEvent_t ev[2] = {nullptr, nullptr};
+            if (!rc) { cudaEventCreateWithFlags(&ev[0], cudaEventDisableTiming); cudaEventCreateWithFlags(&ev[1], cudaEventDisableTiming); }
+            while (!rc && done < total) {
+                size_t nb = total - done < half ? total - done : half;
+                unsigned char* buf = static_cast<unsigned char*>(h->pin) + (size_t)which * half;
+                cudaEventSynchronize(ev[which]);
+                if (fread(buf, 1, nb, f) != nb) { set_error("%s: truncated IxF2 payload", path); rc = B2K_EIO; break; }
+                cudaError_t e = cudaMemcpyAsync(reinterpret_cast<unsigned char*>(h->x) + done, buf, nb, cudaMemcpyHostToDevice, h->stream);
+                if (e == cudaSuccess) e = cudaEventRecord(ev[which], h->stream);
+                if (e != cudaSuccess) { set_error("b2k_read: %s", cudaGetErrorString(e)); rc = B2K_ECUDA; break; }
+                done += nb;
+                which ^= 1;
+            }
+            if (!rc) rc = prep_new_rows(h, 0, n, h->stream);
+            cudaError_t e = cudaStreamSynchronize(h->stream);
+            if (!rc && e != cudaSuccess) { set_error("b2k_read: %s", cudaGetErrorString(e)); rc = B2K_ECUDA; }
+            if (ev[0]) cudaEventDestroy(ev[0]);
+            if (ev[1]) cudaEventDestroy(ev[1]);
+        }
+        if (!rc) h->ntotal = n;
+    }
+    fclose(f);
+    if (rc) { b2k_destroy(h); return rc; }
+    *out = h;
+    return B2K_OK;
+}
+
+}  // extern "C"

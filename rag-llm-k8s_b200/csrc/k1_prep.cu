@@ -1,0 +1,119 @@
+// k1_prep.cu -- K1: per-row preparation done once at add() time, plus the synthetic-row
+// generator used by the benchmarks.
+//
+// Stands in for the `fvec_norms_L2sqr` pass that faiss repeats over the whole database on
+// EVERY batched search behind `index.search` (/root/reference/llm/rag.py:116): here the
+// squared norms are computed when rows arrive (`index.add`, rag.py:80) and kept in HBM.
+// The same pass can also emit the TF32 residual rows the tensor-core kernel (K3) needs:
+//     x = hi + lo,  hi = x with the low 13 mantissa bits cleared (what a kind::tf32 MMA
+//     reads from a raw fp32 operand), lo = x - hi (exact in fp32).
+// Roofline: HBM; algorithmic bytes per row = d*4 read (+ d*4 written when lo is emitted).
+#include "common.cuh"
+#include "kernels.h"
+
+namespace b2k {
+
+__device__ __forceinline__ float tf32_residual(float x) {
+    float hi = __uint_as_float(__float_as_uint(x) & 0xffffe000u);
+    return x - hi;  // exact: at most 13 significant bits
+}
+
+// 8 lanes per row (128 B per request), 4 rows per warp; d % 4 == 0 path.
+__global__ void __launch_bounds__(256)
+row_prep_vec_kernel(const float* __restrict__ X, int64_t n, int d, float* __restrict__ norms,
+                    float* __restrict__ xlo) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const int g = lane >> 3, cl = (lane & 7) * 4;
+    for (int64_t r0 = warp * 4; r0 < n; r0 += nwarps * 4) {
+        const int64_t row = r0 + g;
+        float acc = 0.f;
+        if (row < n) {
+            const float* xr = X + row * (int64_t)d;
+            for (int c = cl; c < d; c += 32) {
+                float4 v = ldg_stream(reinterpret_cast<const float4*>(xr + c));
+                acc = fmaf(v.x, v.x, acc); acc = fmaf(v.y, v.y, acc);
+                acc = fmaf(v.z, v.z, acc); acc = fmaf(v.w, v.w, acc);
+                if (xlo) {
+                    float4 l = make_float4(tf32_residual(v.x), tf32_residual(v.y), tf32_residual(v.z), tf32_residual(v.w));
+                    *reinterpret_cast<float4*>(xlo + row * (int64_t)d + c) = l;
+                }
+            }
+        }
+        acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+        acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+        acc += __shfl_xor_sync(0xffffffffu, acc, 4);
+        if (row < n && (lane & 7) == 0) norms[row] = acc;
+    }
+}
+
+// any d: one warp per row.
+__global__ void __launch_bounds__(256)
+row_prep_any_kernel(const float* __restrict__ X, int64_t n, int d, float* __restrict__ norms,
+                    float* __restrict__ xlo) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t row = warp; row < n; row += nwarps) {
+        const float* xr = X + row * (int64_t)d;
+        float acc = 0.f;
+        for (int c = lane; c < d; c += 32) {
+            float v = __ldg(xr + c);
+            acc = fmaf(v, v, acc);
+            if (xlo) xlo[row * (int64_t)d + c] = tf32_residual(v);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        if (lane == 0) norms[row] = acc;
+    }
+}
+
+int launch_row_prep(const float* X, int64_t n, int d, float* norms, float* xlo, cudaStream_t st) {
+    if (n <= 0) return B2K_OK;
+    const bool vec = (d % 4 == 0) && ((reinterpret_cast<uintptr_t>(X) & 15) == 0) &&
+                     (xlo == nullptr || (reinterpret_cast<uintptr_t>(xlo) & 15) == 0);
+    int64_t rows_per_block = vec ? 32 : 8;
+    int64_t blocks = (n + rows_per_block - 1) / rows_per_block;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    if (vec) row_prep_vec_kernel<<<(unsigned)blocks, 256, 0, st>>>(X, n, d, norms, xlo);
+    else row_prep_any_kernel<<<(unsigned)blocks, 256, 0, st>>>(X, n, d, norms, xlo);
+    count_launch();
+    B2K_CUDA(cudaGetLastError());
+    return B2K_OK;
+}
+
+// ---- synthetic rows (must stay bit-identical to oracle/flat_l2_oracle.c orc_synth_value) ----
+__host__ __device__ __forceinline__ uint64_t mix64(uint64_t z) {
+    z ^= z >> 30; z *= 0xBF58476D1CE4E5B9ull;
+    z ^= z >> 27; z *= 0x94D049BB133111EBull;
+    z ^= z >> 31;
+    return z;
+}
+
+__global__ void __launch_bounds__(256)
+synth_kernel(uint64_t seed, int64_t row0, int64_t nrows, int d, float* __restrict__ out) {
+    const int64_t total = nrows * (int64_t)d;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+        int64_t r = i / d;
+        int c = (int)(i - r * d);
+        uint64_t hr = mix64(seed * 0x9E3779B97F4A7C15ull + (uint64_t)(row0 + r) + 0x632BE59BD9B4E019ull);
+        uint64_t h = mix64(hr + (uint64_t)c * 0xD1342543DE82EF95ull);
+        int s = (int)(h & 0xFFFF) + (int)((h >> 16) & 0xFFFF) + (int)((h >> 32) & 0xFFFF) + (int)(h >> 48) - 131070;
+        out[i] = __fmul_rn((float)s, 2.6429e-5f);
+    }
+}
+
+int launch_synth(uint64_t seed, int64_t row0, int64_t nrows, int d, float* out, cudaStream_t st) {
+    if (nrows <= 0) return B2K_OK;
+    int64_t total = nrows * (int64_t)d;
+    int64_t blocks = (total + 255) / 256;
+    if (blocks > 148 * 32) blocks = 148 * 32;
+    synth_kernel<<<(unsigned)blocks, 256, 0, st>>>(seed, row0, nrows, d, out);
+    count_launch();
+    B2K_CUDA(cudaGetLastError());
+    return B2K_OK;
+}
+
+}  // namespace b2k

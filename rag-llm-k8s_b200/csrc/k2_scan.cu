@@ -1,0 +1,367 @@
+// k2_scan.cu -- K2: the HBM-bound exact scan with fused top-k (nq < 20, and the generic
+// fallback for any nq / any d).
+//
+// Stands in for faiss `exhaustive_L2sqr_seq` + heap result handler behind
+// `index.search(xq, k)` at /root/reference/llm/rag.py:116 (nq = 1, k = 5 there).
+// Numerics follow the oracle's rule (1): D = sum_t (q_t - x_t)^2 in fp32 (exact 0 for a
+// query equal to a stored row).
+//
+// Design (B200): the database is read exactly once per group of <= 8 queries with 128-bit
+// non-allocating loads, 8 lanes per row (one 128-byte line per row segment per request),
+// 16 rows in flight per warp.  Selection never leaves the SM: each CTA keeps, per query,
+// an append buffer of 64-bit (distance,row) keys in shared memory guarded by a running
+// threshold; a full buffer is compacted by a block-wide bitonic sort.  Each CTA writes its
+// k best keys, and the LAST CTA to finish (atomic ticket) merges all CTAs' lists and
+// writes D / I -- so the whole search is ONE launch per query group and no distance ever
+// reaches HBM.  Roofline: HBM; algorithmic bytes per launch = n * d * 4.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace b2k {
+
+static constexpr int SCAN_THREADS = 256;
+static constexpr int SCAN_ROWS_PER_ITER = 128;  // 8 warps x 16 rows
+static constexpr int SCAN_FINAL_P = 4096;       // final-merge buffer (keys)
+
+struct ScanSmem {
+    float* qs;   // [QT][dq]
+    u64* buf;    // [max(QT*P, SCAN_FINAL_P)]
+    u64* kth;    // [QT]  current k-th best key (strict upper bound for new keys)
+    float* tau;  // [QT]  its distance
+    int* cnt;    // [QT]
+    u64* red;    // [2 * 8] block-reduction scratch
+};
+
+__device__ __forceinline__ ScanSmem carve(unsigned char* base, int QT, int dq, int P) {
+    ScanSmem s;
+    size_t off = 0;
+    s.qs = (float*)(base + off); off += (size_t)QT * dq * 4;  // multiple of 16 bytes
+    s.buf = (u64*)(base + off);
+    size_t nbuf = (size_t)QT * P > (size_t)SCAN_FINAL_P ? (size_t)QT * P : (size_t)SCAN_FINAL_P;
+    off += nbuf * 8;
+    s.kth = (u64*)(base + off); off += (size_t)QT * 8;
+    s.red = (u64*)(base + off); off += 16 * 8;
+    s.tau = (float*)(base + off); off += (size_t)QT * 4;
+    s.cnt = (int*)(base + off);
+    return s;
+}
+
+size_t scan_smem_bytes(int QT, int d, int P) {
+    int dq = (d + 3) & ~3;
+    size_t nbuf = (size_t)QT * P > (size_t)SCAN_FINAL_P ? (size_t)QT * P : (size_t)SCAN_FINAL_P;
+    return (size_t)QT * dq * 4 + nbuf * 8 + (size_t)QT * 8 + 16 * 8 + (size_t)QT * 4 + (size_t)QT * 4 + 16;
+}
+
+// Sort the first *cnt keys of buf (capacity P, power of two), keep the best k, refresh the
+// threshold.  Block-wide; *cnt must be stable (call after a barrier).
+__device__ __forceinline__ void compact(u64* buf, int P, int* cnt, u64* kth, float* tau, int k) {
+    const int tid = threadIdx.x, nt = blockDim.x;
+    const int c = *cnt;
+    int Ps = 2;
+    while (Ps < c) Ps <<= 1;
+    if (Ps > P) Ps = P;
+    for (int i = c + tid; i < Ps; i += nt) buf[i] = KEY_EMPTY;
+    __syncthreads();
+    block_bitonic_sort(buf, Ps);
+    if (tid == 0) {
+        int nc = c < k ? c : k;
+        *cnt = nc;
+        if (nc >= k) { *kth = buf[k - 1]; *tau = key_dist(buf[k - 1]); }
+    }
+    __syncthreads();
+}
+
+template <int QT, bool VEC>
+__global__ void __launch_bounds__(SCAN_THREADS)
+scan_l2_topk_kernel(const float* __restrict__ X, const float* __restrict__ Q, int64_t n, int d,
+                    int k, int P, int64_t rows_per_cta, u64* __restrict__ partial,
+                    unsigned int* __restrict__ done, float* __restrict__ D, int64_t* __restrict__ I) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int dq = (d + 3) & ~3;
+    ScanSmem s = carve(smem_raw, QT, dq, P);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    __shared__ int s_is_last;
+
+    for (int i = tid; i < QT * dq; i += SCAN_THREADS) {
+        int q = i / dq, c = i - q * dq;
+        s.qs[i] = c < d ? Q[(int64_t)q * d + c] : 0.f;
+    }
+    if (tid < QT) {
+        s.cnt[tid] = 0;
+        s.kth[tid] = ((u64)FLT_MAX_BITS << 32);  // only distances < FLT_MAX are ever selected
+        s.tau[tid] = FLT_MAX;
+    }
+    __syncthreads();
+
+    const int64_t row_begin = (int64_t)blockIdx.x * rows_per_cta;
+    int64_t row_end = row_begin + rows_per_cta;
+    if (row_end > n) row_end = n;
+
+    for (int64_t base = row_begin; base < row_end; base += SCAN_ROWS_PER_ITER) {
+        float tau_r[QT];
+#pragma unroll
+        for (int q = 0; q < QT; ++q) tau_r[q] = s.tau[q];
+        int flag = 0;
+
+        if (VEC) {
+            // 8 lanes per row, 4 rows per warp request, 4 requests (u) in flight.
+            const int g = lane >> 3, cl = (lane & 7) * 4;
+            float acc[4][QT];
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+#pragma unroll
+                for (int q = 0; q < QT; ++q) acc[u][q] = 0.f;
+            int64_t rows[4];
+            const float* rp[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                rows[u] = base + warp * 16 + u * 4 + g;
+                int64_t rr = rows[u] < row_end ? rows[u] : row_begin;  // clamp: load something valid
+                rp[u] = X + rr * (int64_t)d + cl;
+            }
+#pragma unroll 2
+            for (int c0 = 0; c0 < d; c0 += 32) {
+                const bool cok = (c0 + cl) < d;
+                float4 xv[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                    xv[u] = cok ? ldg_stream(reinterpret_cast<const float4*>(rp[u] + c0)) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                for (int q = 0; q < QT; ++q) {
+                    float4 qv = cok ? *reinterpret_cast<const float4*>(s.qs + q * dq + c0 + cl)
+                                    : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        float a = qv.x - xv[u].x, b = qv.y - xv[u].y, c = qv.z - xv[u].z, e = qv.w - xv[u].w;
+                        acc[u][q] = fmaf(a, a, acc[u][q]);
+                        acc[u][q] = fmaf(b, b, acc[u][q]);
+                        acc[u][q] = fmaf(c, c, acc[u][q]);
+                        acc[u][q] = fmaf(e, e, acc[u][q]);
+                    }
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+#pragma unroll
+                for (int q = 0; q < QT; ++q) {
+                    float v = acc[u][q];
+                    v += __shfl_xor_sync(0xffffffffu, v, 1);
+                    v += __shfl_xor_sync(0xffffffffu, v, 2);
+                    v += __shfl_xor_sync(0xffffffffu, v, 4);
+                    acc[u][q] = v;
+                }
+            if ((lane & 7) == 0) {
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    if (rows[u] < row_end) {
+#pragma unroll
+                        for (int q = 0; q < QT; ++q) {
+                            float dv = acc[u][q];
+                            if (dv <= tau_r[q]) {
+                                u64 key = make_key(dv, (uint32_t)rows[u]);
+                                if (key < s.kth[q]) {
+                                    int pos = atomicAdd(&s.cnt[q], 1);
+                                    s.buf[q * P + pos] = key;
+                                    if (pos + 1 > P - SCAN_ROWS_PER_ITER) flag = 1;
+                                }
+                            }
+                        }
+                    }
+                }
+            }
+        } else {
+            // any d: one row per warp at a time, 32 lanes stride the columns.
+            for (int u = 0; u < 16; ++u) {
+                const int64_t row = base + warp * 16 + u;
+                if (row >= row_end) break;  // warp-uniform
+                const float* xr = X + row * (int64_t)d;
+                float acc[QT];
+#pragma unroll
+                for (int q = 0; q < QT; ++q) acc[q] = 0.f;
+                for (int c = lane; c < d; c += 32) {
+                    float xv = __ldg(xr + c);
+#pragma unroll
+                    for (int q = 0; q < QT; ++q) {
+                        float a = s.qs[q * dq + c] - xv;
+                        acc[q] = fmaf(a, a, acc[q]);
+                    }
+                }
+#pragma unroll
+                for (int q = 0; q < QT; ++q) {
+                    float v = acc[q];
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                    if (lane == 0 && v <= tau_r[q]) {
+                        u64 key = make_key(v, (uint32_t)row);
+                        if (key < s.kth[q]) {
+                            int pos = atomicAdd(&s.cnt[q], 1);
+                            s.buf[q * P + pos] = key;
+                            if (pos + 1 > P - SCAN_ROWS_PER_ITER) flag = 1;
+                        }
+                    }
+                }
+            }
+        }
+
+        if (__syncthreads_or(flag)) {
+#pragma unroll 1
+            for (int q = 0; q < QT; ++q)
+                if (s.cnt[q] > k) compact(s.buf + q * P, P, &s.cnt[q], &s.kth[q], &s.tau[q], k);
+        }
+    }
+
+    // ---- this CTA's k best per query -> global partial list -------------------------
+    __syncthreads();
+#pragma unroll 1
+    for (int q = 0; q < QT; ++q) {
+        compact(s.buf + q * P, P, &s.cnt[q], &s.kth[q], &s.tau[q], k);
+        const int c = s.cnt[q];
+        u64* out = partial + ((int64_t)blockIdx.x * QT + q) * k;
+        for (int j = tid; j < k; j += SCAN_THREADS) out[j] = j < c ? s.buf[q * P + j] : KEY_EMPTY;
+    }
+
+    // ---- last CTA merges -------------------------------------------------------------
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) {
+        unsigned int t = atomicAdd(done, 1u);
+        s_is_last = (t == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!s_is_last) return;
+    __threadfence();
+
+    const int G = gridDim.x;
+    const int64_t total = (int64_t)G * k;
+    const int jsel = (k + G - 1) / G - 1;  // G * (jsel + 1) >= k
+#pragma unroll 1
+    for (int q = 0; q < QT; ++q) {
+        // Two valid upper bounds for the global k-th key: the smallest of the lists' k-th
+        // keys, and the largest of the lists' jsel-th keys.
+        u64 T = KEY_EMPTY, B1 = 0;
+        for (int b = tid; b < G; b += SCAN_THREADS) {
+            const volatile u64* l = partial + ((int64_t)b * QT + q) * k;
+            u64 a = l[k - 1], c = l[jsel];
+            T = a < T ? a : T;
+            B1 = c > B1 ? c : B1;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            u64 a = __shfl_xor_sync(0xffffffffu, T, o), c = __shfl_xor_sync(0xffffffffu, B1, o);
+            T = a < T ? a : T;
+            B1 = c > B1 ? c : B1;
+        }
+        if (lane == 0) { s.red[warp] = T; s.red[8 + warp] = B1; }
+        __syncthreads();
+        u64 bound = KEY_EMPTY, b1 = 0;
+        for (int w = 0; w < SCAN_THREADS / 32; ++w) {
+            bound = s.red[w] < bound ? s.red[w] : bound;
+            b1 = s.red[8 + w] > b1 ? s.red[8 + w] : b1;
+        }
+        bound = b1 < bound ? b1 : bound;
+        if (tid == 0) { s.cnt[0] = 0; s.kth[0] = KEY_EMPTY; s.tau[0] = FLT_MAX; }
+        __syncthreads();
+
+        for (int64_t b0 = 0; b0 < total; b0 += SCAN_THREADS) {
+            int64_t idx = b0 + tid;
+            int flag = 0;
+            if (idx < total) {
+                int b = (int)(idx / k), j = (int)(idx - (int64_t)b * k);
+                u64 key = ((const volatile u64*)partial)[((int64_t)b * QT + q) * k + j];
+                if (key != KEY_EMPTY && key <= bound && key < s.kth[0]) {
+                    int pos = atomicAdd(&s.cnt[0], 1);
+                    s.buf[pos] = key;
+                    if (pos + 1 > SCAN_FINAL_P - SCAN_THREADS) flag = 1;
+                }
+            }
+            if (__syncthreads_or(flag)) compact(s.buf, SCAN_FINAL_P, &s.cnt[0], &s.kth[0], &s.tau[0], k);
+        }
+        compact(s.buf, SCAN_FINAL_P, &s.cnt[0], &s.kth[0], &s.tau[0], k);
+        const int c = s.cnt[0];
+        for (int j = tid; j < k; j += SCAN_THREADS) {
+            if (j < c) {
+                u64 key = s.buf[j];
+                D[(int64_t)q * k + j] = key_dist(key);
+                I[(int64_t)q * k + j] = (int64_t)key_row(key);
+            } else {
+                D[(int64_t)q * k + j] = FLT_MAX;
+                I[(int64_t)q * k + j] = -1;
+            }
+        }
+        __syncthreads();
+    }
+    if (tid == 0) *done = 0u;  // re-arm for the next launch on this stream
+}
+
+__global__ void fill_empty_kernel(float* D, int64_t* I, int64_t count) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < count) { D[i] = FLT_MAX; I[i] = -1; }
+}
+
+int launch_fill_empty(float* D, int64_t* I, int64_t count, cudaStream_t st) {
+    if (count <= 0) return B2K_OK;
+    fill_empty_kernel<<<(unsigned)((count + 255) / 256), 256, 0, st>>>(D, I, count);
+    count_launch();
+    B2K_CUDA(cudaGetLastError());
+    return B2K_OK;
+}
+
+int scan_pick_P(int k) { return next_pow2(k + SCAN_ROWS_PER_ITER); }
+
+int scan_pick_qt(int64_t nq_left, int k) {
+    int P = scan_pick_P(k);
+    int qt = 8;
+    while (qt > 1 && ((size_t)qt * P * 8 > 65536 || qt > nq_left)) qt >>= 1;
+    return qt;
+}
+
+int scan_grid(int64_t n, int sm_count, int ctas_per_sm) {
+    int64_t iters = (n + SCAN_ROWS_PER_ITER - 1) / SCAN_ROWS_PER_ITER;
+    int64_t g = (int64_t)sm_count * ctas_per_sm;
+    if (g > iters) g = iters;
+    if (g < 1) g = 1;
+    return (int)g;
+}
+
+size_t scan_partial_bytes(int grid, int qt, int k) { return (size_t)grid * qt * k * sizeof(u64); }
+
+template <int QT, bool VEC>
+static int launch_scan_t(const float* X, const float* Q, int64_t n, int d, int k, int P, int grid,
+                         u64* partial, unsigned int* done, float* D, int64_t* I, cudaStream_t st) {
+    size_t smem = scan_smem_bytes(QT, d, P);
+    if (smem > 48 * 1024)  // per-device attribute: set on every large launch (a handle may live on any GPU)
+        B2K_CUDA(cudaFuncSetAttribute(scan_l2_topk_kernel<QT, VEC>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int64_t per = (n + grid - 1) / grid;
+    per = (per + SCAN_ROWS_PER_ITER - 1) / SCAN_ROWS_PER_ITER * SCAN_ROWS_PER_ITER;
+    scan_l2_topk_kernel<QT, VEC><<<grid, SCAN_THREADS, smem, st>>>(X, Q, n, d, k, P, per, partial, done, D, I);
+    count_launch();
+    B2K_CUDA(cudaGetLastError());
+    return B2K_OK;
+}
+
+// One launch: QT (1,2,4,8) queries against rows [0,n).  Q, D, I already offset to the group.
+int launch_scan(const float* X, const float* Q, int64_t n, int d, int qt, int k, int grid,
+                u64* partial, unsigned int* done, float* D, int64_t* I, cudaStream_t st) {
+    const int P = scan_pick_P(k);
+    const bool vec = (d % 4 == 0) && ((reinterpret_cast<uintptr_t>(X) & 15) == 0);
+    if (scan_smem_bytes(qt, d, P) > 200 * 1024) {
+        set_error("scan kernel: d=%d too large for shared memory", d);
+        return B2K_ELIMIT;
+    }
+#define B2K_SCAN_CASE(QT_)                                                                          \
+    case QT_:                                                                                       \
+        return vec ? launch_scan_t<QT_, true>(X, Q, n, d, k, P, grid, partial, done, D, I, st)      \
+                   : launch_scan_t<QT_, false>(X, Q, n, d, k, P, grid, partial, done, D, I, st);
+    switch (qt) {
+        B2K_SCAN_CASE(1)
+        B2K_SCAN_CASE(2)
+        B2K_SCAN_CASE(4)
+        B2K_SCAN_CASE(8)
+    }
+#undef B2K_SCAN_CASE
+    set_error("scan kernel: bad query-group size %d", qt);
+    return B2K_EINVAL;
+}
+
+}  // namespace b2k

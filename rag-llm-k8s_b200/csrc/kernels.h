@@ -1,0 +1,24 @@
+// kernels.h -- host-callable launchers of the CUDA kernels (internal to libb200knn).
+#pragma once
+#include "common.cuh"
+
+namespace b2k {
+
+// K1 (k1_prep.cu): per-row squared norms (+ optional TF32 residual rows) for rows [0,n) of X.
+int launch_row_prep(const float* X, int64_t n, int d, float* norms, float* xlo, cudaStream_t st);
+int launch_synth(uint64_t seed, int64_t row0, int64_t nrows, int d, float* out, cudaStream_t st);
+
+// K2 (k2_scan.cu)
+int scan_pick_P(int k);
+int scan_pick_qt(int64_t nq_left, int k);
+int scan_grid(int64_t n, int sm_count, int ctas_per_sm);
+size_t scan_partial_bytes(int grid, int qt, int k);
+int launch_scan(const float* X, const float* Q, int64_t n, int d, int qt, int k, int grid,
+                u64* partial, unsigned int* done, float* D, int64_t* I, cudaStream_t st);
+int launch_fill_empty(float* D, int64_t* I, int64_t count, cudaStream_t st);
+
+// K5 (k5_merge.cu): per query, k smallest (distance,id) of nlists*k candidates.
+int launch_merge_lists(int nlists, int64_t nq, int k, const float* Din, const int64_t* Iin,
+                       const int64_t* id_offset_dev, float* D, int64_t* I, cudaStream_t st);
+
+}  // namespace b2k

@@ -1,0 +1,294 @@
+"""GPU parity tests: the CUDA path, called through the C ABI (via the ctypes shim), against the
+CPU oracle on identical inputs.  The reference has no tests; the cases
+follow SURVEY.md section 7 step 2 / section 8c and the call pattern of llm/rag.py.
+
+Tolerance (north_star): distances within 1e-5 relative; ids identical except where the
+competing distances agree within that tolerance.  Integer-lattice cases are bit-exact."""
+import os
+import pickle
+
+import numpy as np
+import pytest
+
+from oracle import oracle as O
+from util import RTOL, assert_knn_matches, unit_rows
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def faiss():
+    import b200knn
+    return b200knn
+
+
+def _build(faiss, x):
+    idx = faiss.IndexFlatL2(x.shape[1])
+    if x.shape[0]:
+        idx.add(x)
+    return idx
+
+
+def test_synth_generator_is_bit_identical_to_oracle(faiss):
+    for (seed, row0, n, d) in [(42, 7, 4, 8), (1234, 0, 1000, 384), (5678, 123456789, 33, 1027)]:
+        g = faiss.synth(seed, row0, n, d).cpu().numpy()
+        assert np.array_equal(g, O.synth(seed, row0, n, d))
+
+
+def test_config1_rag_default_2048x384_nq1_k5(faiss):
+    """BASELINE.json configs[0]: the reference's own CPU-runnable case."""
+    x = O.synth(1234, 0, 2048, 384)
+    q = O.synth(5678, 0, 1, 384)
+    idx = _build(faiss, x)
+    assert idx.ntotal == 2048 and idx.d == 384
+    D, I = idx.search(q, 5)
+    assert_knn_matches(D, I, x, q, 5, what="C1")
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "c1_2048x384_nq1_k5.npz"))
+    assert np.array_equal(I, g["I"]) and np.allclose(D, g["D"], rtol=1e-5)
+
+
+def test_real_app_shape_unit_norm_64x1024(faiss):
+    """What rag.py really feeds: bge-m3 d=1024, normalize_embeddings=True (rag.py:33,55), tens of rows."""
+    x = unit_rows(O.synth(1234, 0, 64, 1024))
+    q = unit_rows(O.synth(5678, 0, 1, 1024))
+    D, I = _build(faiss, x).search(q, 5)
+    assert_knn_matches(D, I, x, q, 5, what="app")
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "app_64x1024_unit_nq1_k5.npz"))
+    assert np.array_equal(I, g["I"]) and np.allclose(D, g["D"], rtol=1e-5)
+
+
+@pytest.mark.parametrize("d", [1, 3, 4, 100, 384, 768, 1024, 1027])
+def test_dimensions(faiss, d):
+    rng = np.random.default_rng(d)
+    x = rng.standard_normal((3001, d)).astype(np.float32)
+    q = rng.standard_normal((3, d)).astype(np.float32)
+    D, I = _build(faiss, x).search(q, 10)
+    assert_knn_matches(D, I, x, q, 10, what="d=%d" % d)
+
+
+@pytest.mark.parametrize("k", [1, 5, 10, 100, 129, 1024])
+def test_k_values(faiss, k):
+    rng = np.random.default_rng(k)
+    x = rng.standard_normal((5000, 64)).astype(np.float32)
+    q = rng.standard_normal((2, 64)).astype(np.float32)
+    D, I = _build(faiss, x).search(q, k)
+    assert_knn_matches(D, I, x, q, k, what="k=%d" % k)
+
+
+@pytest.mark.parametrize("nq", [1, 2, 7, 8, 9, 19])
+def test_small_query_batches_use_direct_numerics(faiss, nq):
+    rng = np.random.default_rng(nq)
+    x = rng.standard_normal((20000, 96)).astype(np.float32)
+    q = rng.standard_normal((nq, 96)).astype(np.float32)
+    D, I = _build(faiss, x).search(q, 10)
+    assert_knn_matches(D, I, x, q, 10, what="nq=%d" % nq)
+
+
+@pytest.mark.parametrize("nq", [20, 33, 130, 300])
+def test_query_batches(faiss, nq):
+    rng = np.random.default_rng(nq)
+    x = rng.standard_normal((20000, 128)).astype(np.float32)
+    q = rng.standard_normal((nq, 128)).astype(np.float32)
+    D, I = _build(faiss, x).search(q, 10)
+    assert_knn_matches(D, I, x, q, 10, expanded=True, what="nq=%d" % nq)
+
+
+@pytest.mark.parametrize("n", [0, 1, 3, 4, 5, 127, 128, 129])
+def test_fewer_rows_than_k_pads_with_minus_one(faiss, n):
+    """rag.py starts from an empty index (rag.py:61) and searches with k=5 (rag.py:114): the
+    -1 / FLT_MAX padding must be exact because rag.py:119 indexes metadata with it."""
+    x = O.synth(1, 0, n, 32)
+    q = O.synth(2, 0, 2, 32)
+    idx = _build(faiss, x)
+    assert idx.ntotal == n
+    D, I = idx.search(q, 5)
+    Dr, Ir = O.search(x, q, 5)
+    assert np.array_equal(I, Ir)
+    assert np.array_equal(D == O.FLT_MAX, Dr == O.FLT_MAX)
+    assert_knn_matches(D, I, x, q, 5, Dr, Ir, what="n=%d" % n)
+
+
+def test_integer_lattice_is_bit_exact(faiss):
+    rng = np.random.default_rng(7)
+    x = rng.integers(-8, 9, size=(30000, 48)).astype(np.float32)
+    for nq in (1, 5, 25, 140):
+        q = rng.integers(-8, 9, size=(nq, 48)).astype(np.float32)
+        D, I = _build(faiss, x).search(q, 20)
+        Dr, Ir = O.search(x, q, 20)
+        assert np.array_equal(D, Dr) and np.array_equal(I, Ir), nq
+
+
+def test_all_identical_rows_tie_break_by_id(faiss):
+    x = np.ones((5000, 8), np.float32)
+    for nq in (1, 24):
+        q = np.zeros((nq, 8), np.float32)
+        D, I = _build(faiss, x).search(q, 7)
+        assert np.all(I == np.arange(7)[None, :]) and np.all(D == 8.0)
+
+
+def test_duplicates_and_self_match(faiss):
+    rng = np.random.default_rng(5)
+    base = unit_rows(rng.standard_normal((500, 1024)))
+    x = np.concatenate([base, base[:100]], 0)          # rows 500..599 duplicate rows 0..99
+    q = base[[3, 42]].copy()
+    D, I = _build(faiss, x).search(q, 4)
+    assert I[:, :2].tolist() == [[3, 503], [42, 542]]
+    assert np.all(D[:, :2] == 0.0)                     # direct differences: exact zero
+    assert_knn_matches(D, I, x, q, 4, what="dups")
+    qb = np.repeat(q, 12, 0)                           # batched numerics: >= 0, never negative
+    D, I = _build(faiss, x).search(qb, 4)
+    assert np.all(D >= 0.0)
+    assert_knn_matches(D, I, x, qb, 4, expanded=True, what="dups-batched")
+
+
+def test_nonfinite_rows_are_never_selected(faiss):
+    x = np.array([[1.0, 0, 0, 0], [np.inf, 0, 0, 0], [np.nan, 0, 0, 0], [2.0, 0, 0, 0]], np.float32)
+    D, I = _build(faiss, x).search(np.zeros((1, 4), np.float32), 4)
+    assert I.tolist() == [[0, 3, -1, -1]]
+
+
+def test_incremental_adds_keep_sequential_ids(faiss):
+    x = O.synth(77, 0, 5000, 64)
+    idx = faiss.IndexFlatL2(64)
+    for a, b in ((0, 1), (1, 1500), (1500, 1501), (1501, 5000)):   # forces several regrowths
+        idx.add(x[a:b])
+    assert idx.ntotal == 5000
+    q = O.synth(78, 0, 4, 64)
+    D, I = idx.search(q, 10)
+    assert_knn_matches(D, I, x, q, 10, what="incremental")
+    assert np.array_equal(idx.reconstruct_n(0, 5000), x)
+    idx.reset()
+    assert idx.ntotal == 0 and idx.d == 64
+    D, I = idx.search(q, 3)
+    assert np.all(I == -1)
+    idx.add(x[:10])
+    assert idx.search(x[:1], 1)[1].tolist() == [[0]]
+
+
+def test_shape_and_k_errors_are_assertions(faiss):
+    idx = faiss.IndexFlatL2(16)
+    with pytest.raises(AssertionError):
+        idx.add(np.zeros((3, 8), np.float32))
+    with pytest.raises(AssertionError):
+        idx.search(np.zeros((1, 8), np.float32), 5)
+    with pytest.raises(AssertionError):
+        idx.search(np.zeros((1, 16), np.float32), 0)
+    with pytest.raises(RuntimeError):
+        idx.search(np.zeros((1, 16), np.float32), 1025)
+    idx.add(np.zeros((2, 16), np.float64))               # coerced to float32 like faiss
+
+
+def test_ixf2_bytes_and_round_trip(faiss, tmp_path):
+    p = str(tmp_path / "faiss_index")
+    faiss.write_index(faiss.IndexFlatL2(1024), p)
+    assert open(p, "rb").read() == O.empty_ixf2_bytes(1024)
+    back = faiss.read_index(p)
+    assert back.ntotal == 0 and back.d == 1024
+    x = O.synth(5, 0, 1234, 100)
+    idx = _build(faiss, x)
+    faiss.write_index(idx, p)
+    ref = str(tmp_path / "ref")
+    O.write_ixf2(ref, x)
+    assert open(p, "rb").read() == open(ref, "rb").read()  # byte-identical to the independent writer
+    assert not os.path.exists(p + ".tmp")
+    back = faiss.read_index(ref)
+    assert back.ntotal == 1234 and back.d == 100
+    q = O.synth(6, 0, 3, 100)
+    D, I = back.search(q, 5)
+    assert_knn_matches(D, I, x, q, 5, what="after read_index")
+
+
+def test_rag_py_call_pattern(faiss, tmp_path):
+    """ensure_index_exists / update_index / search_documents restated (rag.py:57-86,114-120) with
+    the encoder stubbed: row id == index into the metadata list, -1 padding reaches metadata[-1]."""
+    INDEX_PATH = str(tmp_path / "faiss_index")
+    d = 1024
+    enc = lambda i: unit_rows(O.synth(900, i, 1, d))[0]
+
+    def ensure_index_exists():
+        if not os.path.exists(INDEX_PATH):
+            faiss.write_index(faiss.IndexFlatL2(d), INDEX_PATH)
+            pickle.dump([], open(INDEX_PATH + ".metadata", "wb"))
+
+    def update_index(vectors, metadata):
+        index = faiss.read_index(INDEX_PATH)
+        existing = pickle.load(open(INDEX_PATH + ".metadata", "rb"))
+        vectors_np = np.array(vectors).astype("float32")
+        if vectors_np.shape[0] > 0:
+            index.add(vectors_np)
+            existing.extend(metadata)
+            faiss.write_index(index, INDEX_PATH)
+            pickle.dump(existing, open(INDEX_PATH + ".metadata", "wb"))
+        return index.ntotal, index.d
+
+    def search_documents(qv, k=5):
+        index = faiss.read_index(INDEX_PATH)
+        metadata = pickle.load(open(INDEX_PATH + ".metadata", "rb"))
+        D, I = index.search(qv.reshape(1, -1), k)
+        return [(metadata[idx], float(dist)) for idx, dist in zip(I[0], D[0])]
+
+    ensure_index_exists()
+    with pytest.raises(IndexError):                       # ntotal == 0 -> metadata[-1] on [] (rag.py:119)
+        search_documents(enc(0))
+    assert update_index([enc(i) for i in range(3)], [{"chunk_id": i} for i in range(3)]) == (3, d)
+    res = search_documents(enc(1))
+    assert res[0] == ({"chunk_id": 1}, 0.0)
+    assert res[3][0] == {"chunk_id": 2} and res[3][1] == float(O.FLT_MAX)   # idx -1 -> last chunk
+    assert update_index([enc(i) for i in range(3, 40)], [{"chunk_id": i} for i in range(3, 40)]) == (40, d)
+    res = search_documents(enc(17))
+    assert res[0][0] == {"chunk_id": 17} and res[0][1] == 0.0 and len(res) == 5
+    assert isinstance(faiss.read_index(INDEX_PATH).ntotal, int)
+
+
+def test_torch_device_tensors(faiss):
+    import torch
+    x = faiss.synth(1234, 0, 50000, 384)
+    q = faiss.synth(5678, 0, 4, 384)
+    idx = faiss.IndexFlatL2(384)
+    idx.add(x)
+    D, I = idx.search(q, 10)
+    assert D.is_cuda and I.dtype == torch.int64
+    xh, qh = x.cpu().numpy(), q.cpu().numpy()
+    assert_knn_matches(D.cpu().numpy(), I.cpu().numpy(), xh, qh, 10, what="torch")
+    idx2 = faiss.IndexFlatL2(384)
+    idx2.add_synthetic(50000, 1234, 0)
+    D2, I2 = idx2.search(qh, 10)
+    assert np.array_equal(I2, I.cpu().numpy()) and np.array_equal(D2, D.cpu().numpy())
+
+
+def test_merge_topk_matches_oracle(faiss):
+    rng = np.random.default_rng(2)
+    nl, nq, k = 8, 5, 100
+    Dl = np.sort(rng.random((nl, nq, k)).astype(np.float32), axis=2)
+    Dl[:, :, ::7] = Dl[:, :, 1::7][:, :, :Dl[:, :, ::7].shape[2]]      # inject exact ties
+    Dl = np.sort(Dl, axis=2)
+    Il = rng.permutation(nl * nq * k).reshape(nl, nq, k).astype(np.int64)
+    Il[3, :, 90:] = -1
+    Dl[3, :, 90:] = O.FLT_MAX
+    Dm, Im = faiss.merge_topk(Dl, Il)
+    Dr, Ir = O.merge(Dl, Il)
+    assert np.array_equal(Dm, Dr) and np.array_equal(Im, Ir)
+    off = np.arange(nl, dtype=np.int64) * 1000000
+    Dm, Im = faiss.merge_topk(Dl, Il, id_offset=off)
+    Dr, Ir = O.merge(Dl, np.where(Il >= 0, Il + off[:, None, None], -1))
+    assert np.array_equal(Dm, Dr) and np.array_equal(Im, Ir)
+
+
+def test_one_million_rows_nq1_k10(faiss):
+    """BASELINE.json configs[1] at full size: 1M x 384, nq=1, k=10, against the oracle (about a
+    second of CPU) and by a size-independent property: searching the two halves separately and
+    merging gives the same answer."""
+    idx = faiss.IndexFlatL2(384)
+    idx.add_synthetic(1_000_000, 1234, 0)
+    x = O.synth(1234, 0, 1_000_000, 384)
+    q = O.synth(5678, 0, 1, 384)
+    D, I = idx.search(q, 10)
+    assert_knn_matches(D, I, x, q, 10, what="C2")
+    halves = []
+    for a, b in ((0, 500_000), (500_000, 1_000_000)):
+        h = faiss.IndexFlatL2(384)
+        h.add(x[a:b])
+        halves.append(h.search(q, 10))
+    Dm, Im = faiss.merge_topk(np.stack([h[0] for h in halves]), np.stack([h[1] for h in halves]),
+                              id_offset=np.array([0, 500_000]))
+    assert np.array_equal(Im, I) and np.array_equal(Dm, D)
