@@ -11,8 +11,9 @@
  *   - vectors are float32, row-major, C-contiguous; ids are int64 (row position, 0-based,
  *     sequential across adds); distances are SQUARED L2 in float32;
  *   - `on_device != 0` means the data pointers of that call are device pointers on the
- *     index's GPU and `stream` is the cudaStream_t to enqueue on (NULL = the index's own
- *     stream); the call then returns after enqueueing.  With `on_device == 0` the pointers
+ *     index's GPU and `stream` is the cudaStream_t to enqueue on (NULL = the legacy
+ *     default stream, which is what torch calls its default stream); the call returns
+ *     after enqueueing.  With `on_device == 0` the pointers
  *     are host memory and the call returns when the results are in the caller's buffers;
  *   - the handle owns all device memory; the library never keeps a caller pointer past
  *     return;

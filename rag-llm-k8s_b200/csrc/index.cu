@@ -58,6 +58,8 @@ struct b2k_index {
     int opt_scan_ctas_per_sm = 2;
     int sticky = 0;
     K3State* k3 = nullptr;
+    // cross-stream ordering: rows written (add) -> later searches; workspace users -> next user
+    cudaEvent_t ev_rows = nullptr, ev_ws = nullptr;
 };
 
 static constexpr int64_t MAX_ROWS = 0xFFFFFFFEll;  // row index lives in the low 32 bits of a key
@@ -210,6 +212,8 @@ int b2k_create(int d, int device, b2k_index** out) {
     cudaError_t e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaMalloc(&h->done, 256);
     if (e == cudaSuccess) e = cudaMemset(h->done, 0, 256);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_rows, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_ws, cudaEventDisableTiming);
     if (e != cudaSuccess) {
         set_error("b2k_create: %s", cudaGetErrorString(e));
         if (h->stream) cudaStreamDestroy(h->stream);
@@ -228,6 +232,8 @@ int b2k_destroy(b2k_index* h) {
     if (h->k3) k3_destroy(h->k3);
     cudaFree(h->x); cudaFree(h->norms); cudaFree(h->xlo); cudaFree(h->ws); cudaFree(h->done);
     if (h->pin) cudaFreeHost(h->pin);
+    if (h->ev_rows) cudaEventDestroy(h->ev_rows);
+    if (h->ev_ws) cudaEventDestroy(h->ev_ws);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
     return B2K_OK;
@@ -280,12 +286,13 @@ int b2k_add(b2k_index* h, int64_t n, const float* x, int on_device, void* stream
     DeviceGuard g(h->device);
     int rc = grow(h, h->ntotal + n);
     if (rc) return rc;
-    cudaStream_t st = (on_device && stream) ? (cudaStream_t)stream : h->stream;
+    cudaStream_t st = on_device ? (cudaStream_t)stream : h->stream;
     float* dst = h->x + h->ntotal * (int64_t)h->d;
     size_t bytes = (size_t)n * h->d * sizeof(float);
     B2K_CUDA(cudaMemcpyAsync(dst, x, bytes, on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, st));
     rc = prep_new_rows(h, h->ntotal, n, st);
     if (rc) return rc;
+    B2K_CUDA(cudaEventRecord(h->ev_rows, st));
     h->ntotal += n;
     if (!on_device) {
         cudaError_t e = cudaStreamSynchronize(st);
@@ -344,7 +351,7 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
     if (h->sticky) { set_error("handle has a sticky CUDA error (%d)", h->sticky); return B2K_ECUDA; }
     DeviceGuard g(h->device);
     const int kk = (int)k;
-    cudaStream_t st = (on_device && stream) ? (cudaStream_t)stream : h->stream;
+    cudaStream_t st = on_device ? (cudaStream_t)stream : h->stream;
 
     const bool want_tc = h->ntotal > 0 && (h->opt_path == 2 || (h->opt_path == 0 && nq >= 20)) && k3_supported(h->d, kk);
 
@@ -360,6 +367,8 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
     }
     int rc = ensure_ws(h, io_bytes + align256(scratch));
     if (rc) return rc;
+    B2K_CUDA(cudaStreamWaitEvent(st, h->ev_rows, 0));
+    B2K_CUDA(cudaStreamWaitEvent(st, h->ev_ws, 0));
     unsigned char* wsb = static_cast<unsigned char*>(h->ws);
     const float* qd = xq;
     float* Dd = D;
@@ -388,6 +397,7 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
         rc = scan_search(h, nq, qd, kk, Dd, Id, ws_tail, st);
     }
     if (rc) return rc;
+    B2K_CUDA(cudaEventRecord(h->ev_ws, st));
 
     if (!on_device) {
         unsigned char* pb = static_cast<unsigned char*>(h->pin);

@@ -47,7 +47,7 @@ def assert_knn_matches(D, I, x, q, k, Dref=None, Iref=None, rtol=RTOL, expanded=
     assert not bad.any(), "%s: distance mismatch, worst rel %.3g at %s" % (
         what, (err[ok] / np.maximum(scale[ok], 1e-30)).max(), np.argwhere(bad)[:3])
     # sorted ascending
-    assert np.all(np.diff(np.where(pad, np.inf, D.astype(np.float64)), axis=1) >= 0), "%s: D not ascending" % what
+    assert np.all(np.diff(np.where(pad, 1e300, D.astype(np.float64)), axis=1) >= 0), "%s: D not ascending" % what
     # ids
     diff_rows = np.where((I != Iref).any(1))[0]
     for i in diff_rows:
