@@ -180,6 +180,7 @@ def main():
         index = b200knn.IndexFlatL2(d, device=local_rank)
         index.reserve(N)
         index.add_synthetic(N, SEED_DB, 0)
+    index.set_option("timing", 1)
     q_dev = b200knn.synth(SEED_Q, 0, nq, d, device=local_rank)
     q_host = q_dev.cpu().numpy()
 
@@ -241,6 +242,29 @@ def main():
 
     # ---- roofline of the dominant kernel ----------------------------------------------
     pk = peaks()
+    tf32_meas = None
+    if nq >= 20 and rank == 0:
+        # cuBLAS TF32 GEMM on this box (MEASURED_PEAKS.json has no TF32 row): best of 5 and a 1.5 s loop
+        torch.backends.cuda.matmul.allow_tf32 = True
+        a = torch.randn(8192, 8192, device="cuda"); b = torch.randn(8192, 8192, device="cuda")
+        for _ in range(2):
+            a @ b
+        best = 1e9
+        for _ in range(5):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(); a @ b; e1.record(); torch.cuda.synchronize()
+            best = min(best, e0.elapsed_time(e1))
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        reps = max(int(1500.0 / best), 1)
+        e0.record()
+        for _ in range(reps):
+            a @ b
+        e1.record(); torch.cuda.synchronize()
+        tf32_meas = {"burst": 2 * 8192 ** 3 / (best * 1e-3) / 1e12,
+                     "sustained": 2 * 8192 ** 3 * reps / (e0.elapsed_time(e1) * 1e-3) / 1e12,
+                     "how": "torch.matmul fp32 8192^3 with allow_tf32 (cuBLAS), CUDA events"}
+        del a, b
+        torch.backends.cuda.matmul.allow_tf32 = False
     stats = index.stats() if hasattr(index, "stats") else {}
     n_local = N // world if world > 1 else N
     if stats.get("path") == "tensor":
@@ -250,7 +274,8 @@ def main():
         roof = {"bound": "tensor", "kernel": "k3_tf32x3_topk", "achieved": flops / (k_ms * 1e-3) / 1e12, "peak": peak,
                 "unit": "TFLOP/s", "traffic": None, "launch_ms": k_ms,
                 "peak_source": "%s bf16 sustained / 2 (TF32 dense; derived, MEASURED_PEAKS.json has no TF32 row)" % pk["source"],
-                "algorithmic": "executed tensor flops = 3 (3xTF32) * 2*nq*N*d per launch"}
+                "algorithmic": "executed tensor flops = 3 (3xTF32) * 2*nq*N*d per launch",
+                "fp32_equivalent_tflops": flops / 3 / (k_ms * 1e-3) / 1e12, "tf32_cublas_measured": tf32_meas}
     else:
         per_launch_ms = ms_dev / max(launches, 1)
         gbs = n_local * d * 4 / (per_launch_ms * 1e-3) / 1e9

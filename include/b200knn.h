@@ -104,8 +104,13 @@ B2K_API int b2k_merge_topk(int device, int nlists, int64_t nq, int64_t k, const 
                    int on_device, void* stream);
 
 /* Tuning / test hooks.  Keys: "path" (0 auto, 1 force the scan kernel, 2 force the
- * tensor-core kernel), "scan_ctas_per_sm".  Unknown key -> B2K_EINVAL. */
+ * tensor-core kernel), "scan_ctas_per_sm", "timing" (0/1).  Unknown key -> B2K_EINVAL. */
 B2K_API int b2k_set_option(b2k_index* h, const char* key, int64_t value);
+
+/* Read-back of measurements / state.  Keys: "last_path" (1 = scan kernel, 2 = tensor-core
+ * kernel served the last search), "tensor_kernel_ms" (CUDA-event duration of the last
+ * tensor-core main kernel; needs option "timing" = 1; synchronises on that kernel). */
+B2K_API int b2k_get_stat(b2k_index* h, const char* key, double* out);
 
 /* Number of kernels this library has launched in this process (bench `gpu_launches`). */
 B2K_API int64_t b2k_launch_count(void);

@@ -149,6 +149,17 @@ class IndexFlatL2:
         """Append n rows of the counter-based synthetic stream, generated on the GPU."""
         _lib.check(_lib.lib().b2k_add_synthetic(self._h, int(n), int(seed), int(first_row)))
 
+    def stats(self):
+        """{'path': 'scan'|'tensor'|None, 'main_kernel_ms': float|None} for the last search."""
+        L = _lib.lib()
+        v = C.c_double()
+        out = {"path": None, "main_kernel_ms": None}
+        if L.b2k_get_stat(self._h, b"last_path", C.byref(v)) == 0:
+            out["path"] = {1: "scan", 2: "tensor"}.get(int(v.value))
+        if out["path"] == "tensor" and L.b2k_get_stat(self._h, b"tensor_kernel_ms", C.byref(v)) == 0:
+            out["main_kernel_ms"] = v.value
+        return out
+
     def set_option(self, key, value):
         _lib.check(_lib.lib().b2k_set_option(self._h, key.encode(), int(value)))
 

@@ -35,6 +35,7 @@ SIGNATURES = {
     "b2k_merge_topk": (C.c_int, [C.c_int, C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
                                  C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     "b2k_set_option": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int64]),
+    "b2k_get_stat": (C.c_int, [C.c_void_p, C.c_char_p, C.POINTER(C.c_double)]),
     "b2k_launch_count": (C.c_int64, []),
     "b2k_version": (C.c_int, []),
 }

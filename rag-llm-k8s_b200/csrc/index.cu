@@ -56,6 +56,8 @@ struct b2k_index {
     unsigned int* done = nullptr;
     int opt_path = 0;
     int opt_scan_ctas_per_sm = 2;
+    int opt_timing = 0;
+    int last_path = 0;
     int sticky = 0;
     K3State* k3 = nullptr;
     // cross-stream ordering: rows written (add) -> later searches; workspace users -> next user
@@ -251,11 +253,28 @@ int b2k_set_option(b2k_index* h, const char* key, int64_t value) {
     } else if (!strcmp(key, "scan_ctas_per_sm")) {
         if (value < 1 || value > 8) { set_error("option scan_ctas_per_sm must be 1..8"); return B2K_EINVAL; }
         h->opt_scan_ctas_per_sm = (int)value;
+    } else if (!strcmp(key, "timing")) {
+        h->opt_timing = value != 0;
+        if (h->k3) k3_set_timing(h->k3, h->opt_timing != 0);
     } else {
         set_error("unknown option '%s'", key);
         return B2K_EINVAL;
     }
     return B2K_OK;
+}
+
+int b2k_get_stat(b2k_index* h, const char* key, double* out) {
+    if (!h || !key || !out) { set_error("b2k_get_stat: null argument"); return B2K_EINVAL; }
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (!strcmp(key, "last_path")) { *out = h->last_path; return B2K_OK; }
+    if (!strcmp(key, "tensor_kernel_ms")) {
+        float ms = 0.f;
+        if (!h->k3 || k3_last_kernel_ms(h->k3, &ms)) { set_error("no timed tensor-core kernel yet (set option timing=1)"); return B2K_EINVAL; }
+        *out = ms;
+        return B2K_OK;
+    }
+    set_error("unknown stat '%s'", key);
+    return B2K_EINVAL;
 }
 
 int b2k_reserve(b2k_index* h, int64_t nrows) {
@@ -389,11 +408,16 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
     } else if (want_tc) {
         rc = enable_lo(h, st);
         if (!rc) {
-            if (!h->k3) rc = k3_create(&h->k3, h->device, h->sm_count);
+            if (!h->k3) {
+                rc = k3_create(&h->k3, h->device, h->sm_count);
+                if (!rc) k3_set_timing(h->k3, h->opt_timing != 0);
+            }
+            if (!rc) h->last_path = 2;
             if (!rc) rc = k3_search(h->k3, h->x, h->xlo, h->norms, h->ntotal, h->capacity, h->d, qd, nq, kk, Dd, Id,
                                     ws_tail, st);
         }
     } else {
+        h->last_path = 1;
         rc = scan_search(h, nq, qd, kk, Dd, Id, ws_tail, st);
     }
     if (rc) return rc;

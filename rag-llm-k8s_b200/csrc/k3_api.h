@@ -17,4 +17,8 @@ int k3_search(K3State* s, const float* x, const float* xlo, const float* norms, 
               int d, const float* q, int64_t nq, int k, float* D, int64_t* I, unsigned char* scratch,
               cudaStream_t st);
 
+// optional CUDA-event timing of the main kernel (bench.py's roofline numbers)
+void k3_set_timing(K3State* s, bool on);
+int k3_last_kernel_ms(K3State* s, float* ms);
+
 }  // namespace b2k

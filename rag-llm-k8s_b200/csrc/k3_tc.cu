@@ -1,16 +1,548 @@
-// k3_tc.cu -- placeholder until the tcgen05 kernel lands: reports "not supported" so the
-// dispatch uses the exact scan kernel (K2) for every nq.
+// k3_tc.cu -- K3: batched exact search on the 5th-generation tensor cores, with the top-k
+// selection fused into the accumulator epilogue, and K4, the cross-CTA merge.
+//
+// Stands in for faiss `exhaustive_L2sqr_blas` (sgemm in 4096 x 1024 blocks, then
+// ||q||^2 + ||x||^2 - 2<q,x>, clamp at 0) + heap/reservoir result handlers behind
+// `index.search(xq, k)` (/root/reference/llm/rag.py:116) for nq >= 20 -- oracle rule (2).
+//
+// What runs where (per CTA; CG = 1, or CG = 2 for a CTA pair issuing cta_group::2 MMAs):
+//   warp 0  TMA producer : cp.async.bulk.tensor 2-D boxes (32 fp32 = one 128-byte swizzle row
+//           wide) of Q_hi, Q_lo (128 query rows) and X_hi, X_lo (256/CG database rows) into an
+//           NS-stage shared-memory ring, completion on mbarriers.
+//   warp 1  MMA issuer   : one elected thread issues tcgen05.mma kind::tf32 (M = 128*CG,
+//           N = 256, K = 8): per 8 columns of K three products  Q_lo*X_hi + Q_hi*X_lo +
+//           Q_hi*X_hi  ("3xTF32": hi = the fp32 value as the tensor core reads it, i.e. with the
+//           low 13 mantissa bits ignored; lo = the exact fp32 remainder) accumulated in fp32 in
+//           TMEM.  Two 256-column accumulators (all 512 TMEM columns) so the MMAs of tile t+1
+//           overlap the epilogue of tile t.
+//   warps 2-5  epilogue  : tcgen05.ld 32 lanes x 32 columns at a time; one thread owns one
+//           query row, so its pruning threshold lives in a register:
+//                 s = ||x||^2 - 2*acc        (one FFMA; ||x||^2 staged in shared memory)
+//                 keep if s <= tau - ||q||^2 (one compare; taken ~k/N of the time)
+//           survivors are appended as 64-bit (distance,row) keys to that query's private list
+//           in global memory (L2-resident); a list that could overflow on the next tile is
+//           compacted by its warp with a bitonic sort in shared memory, which also lowers the
+//           threshold and publishes it (atomicMin) to the other CTAs.
+// No distance matrix is ever written: per tile the only global traffic is the operand
+// stream and the rare survivor keys.  K4 then merges, per query, the lists of all CTAs.
+//
+// Work split: unit = (database tile of 256 rows, block of 128*CG queries), units ordered tile-
+// major and dealt round-robin to the CTAs/pairs, so the CTAs running at any moment share a few
+// database tiles through L2 and every tile is fetched from HBM once per query batch.
+// Roofline: tensor (kind::tf32); executed flops = 3 * 2 * nq * N * d.
+#include <cuda.h>
+
 #include "k3_api.h"
+#include "kernels.h"
+#include "sm100.cuh"
+
 namespace b2k {
-struct K3State { int unused; };
-bool k3_supported(int, int) { return false; }
-size_t k3_scratch_bytes(int, int, int64_t, int) { return 0; }
-int k3_create(K3State** out, int, int) { *out = new K3State(); return B2K_OK; }
-void k3_destroy(K3State* s) { delete s; }
-void k3_invalidate_maps(K3State*) {}
-int k3_search(K3State*, const float*, const float*, const float*, int64_t, int64_t, int, const float*, int64_t, int,
-              float*, int64_t*, unsigned char*, cudaStream_t) {
-    set_error("tensor-core path not built");
-    return B2K_ECUDA;
+
+static constexpr int K3_BM = 128;       // query rows per CTA = TMEM lanes
+static constexpr int K3_BN = 256;       // database rows per tile = TMEM columns per accumulator
+static constexpr int K3_BK = 32;        // fp32 per k-chunk: one 128-byte swizzle row
+static constexpr int K3_THREADS = 192;  // warp 0 TMA, warp 1 MMA, warps 2..5 epilogue
+static constexpr int K3_EPI_THREADS = 128;
+static constexpr int K3_A_BYTES = K3_BM * K3_BK * 4;  // 16 KB
+
+struct K3Params {
+    int64_t n;        // database rows
+    int d;
+    int64_t nq;
+    int k;
+    int P;            // per-(CTA,query) list capacity (power of two, >= k + 256)
+    int nqb;          // query blocks of 128*CG
+    int64_t nunits;   // ntiles * nqb
+    int qpc;          // list slots per CTA = nqb * 128
+    const float* norms;
+    const float* qn;
+    unsigned int* gts;  // [nq]   shared upper bound of the k-th distance (float bits)
+    int* cnt;           // [ncta][qpc]
+    float* tau;         // [ncta][qpc]
+    u64* kth;           // [ncta][qpc]
+    u64* cand;          // [ncta][qpc][P]
+};
+
+template <int CG, int NS>
+struct K3Smem {
+    static constexpr int B_ROWS = K3_BN / CG;
+    static constexpr int B_BYTES = B_ROWS * K3_BK * 4;
+    static constexpr int STAGE_BYTES = 2 * K3_A_BYTES + 2 * B_BYTES;
+    static constexpr int OFF_XN = NS * STAGE_BYTES;            // float[2][256]
+    static constexpr int OFF_BAR = OFF_XN + 2 * K3_BN * 4;     // full[NS] empty[NS] tfull[2] tempty[2]
+    static constexpr int OFF_TMEM = OFF_BAR + (2 * NS + 4) * 8;
+    static constexpr int OFF_SCRATCH = (OFF_TMEM + 16 + 15) & ~15;  // 4 warps x P keys
+    static size_t bytes(int P) { return (size_t)OFF_SCRATCH + (size_t)4 * P * 8 + 1024; }
+};
+
+template <int CG, int NS>
+__global__ void __launch_bounds__(K3_THREADS, 1)
+k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_ql,
+                      const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_xl,
+                      const K3Params p) {
+    using L = K3Smem<CG, NS>;
+    extern __shared__ unsigned char smem_raw[];
+    unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    float* xn_s = reinterpret_cast<float*>(smem + L::OFF_XN);
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + L::OFF_BAR);
+    uint64_t* empty = full + NS;
+    uint64_t* tfull = empty + NS;
+    uint64_t* tempty = tfull + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + L::OFF_TMEM);
+    u64* scratch = reinterpret_cast<u64*>(smem + L::OFF_SCRATCH);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = (CG == 2) ? ptx::cluster_ctarank() : 0u;
+    const int cluster_id = blockIdx.x / CG;
+    const int nclusters = gridDim.x / CG;
+    const int nkc = (p.d + K3_BK - 1) / K3_BK;
+
+    if (warp == 0 && lane == 0) {
+        ptx::prefetch_tmap(&tm_q); ptx::prefetch_tmap(&tm_ql); ptx::prefetch_tmap(&tm_x); ptx::prefetch_tmap(&tm_xl);
+        for (int s = 0; s < NS; ++s) { ptx::mbar_init(&full[s], CG); ptx::mbar_init(&empty[s], 1); }
+        for (int s = 0; s < 2; ++s) { ptx::mbar_init(&tfull[s], 1); ptx::mbar_init(&tempty[s], 4 * CG); }
+        ptx::fence_barrier_init();
+    }
+    if (warp == 1) {
+        ptx::tmem_alloc<CG>(tmem_slot, 512);
+        ptx::tmem_relinquish<CG>();
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (CG == 2) ptx::cluster_sync_all();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int64_t u = cluster_id; u < p.nunits; u += nclusters) {
+                const int64_t t = u / p.nqb;
+                const int qb = (int)(u - t * p.nqb);
+                const int qrow0 = qb * (K3_BM * CG) + (int)rank * K3_BM;
+                const int64_t xrow0 = t * K3_BN + (int64_t)rank * L::B_ROWS;
+                for (int kc = 0; kc < nkc; ++kc) {
+                    ptx::mbar_wait(&empty[stage], phase ^ 1);
+                    unsigned char* sb = smem + stage * L::STAGE_BYTES;
+                    if (CG == 1) {
+                        ptx::mbar_arrive_expect_tx(&full[stage], L::STAGE_BYTES);
+                        ptx::tma_load_2d(sb, &tm_q, &full[stage], kc * K3_BK, qrow0);
+                        ptx::tma_load_2d(sb + K3_A_BYTES, &tm_ql, &full[stage], kc * K3_BK, qrow0);
+                        ptx::tma_load_2d(sb + 2 * K3_A_BYTES, &tm_x, &full[stage], kc * K3_BK, (int)xrow0);
+                        ptx::tma_load_2d(sb + 2 * K3_A_BYTES + L::B_BYTES, &tm_xl, &full[stage], kc * K3_BK, (int)xrow0);
+                    } else {
+                        if (rank == 0) ptx::mbar_arrive_expect_tx(&full[stage], 2 * L::STAGE_BYTES);
+                        else ptx::mbar_arrive_cluster(&full[stage], 0);
+                        ptx::tma_load_2d_pair(sb, &tm_q, &full[stage], kc * K3_BK, qrow0);
+                        ptx::tma_load_2d_pair(sb + K3_A_BYTES, &tm_ql, &full[stage], kc * K3_BK, qrow0);
+                        ptx::tma_load_2d_pair(sb + 2 * K3_A_BYTES, &tm_x, &full[stage], kc * K3_BK, (int)xrow0);
+                        ptx::tma_load_2d_pair(sb + 2 * K3_A_BYTES + L::B_BYTES, &tm_xl, &full[stage], kc * K3_BK, (int)xrow0);
+                    }
+                    if (++stage == NS) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer (leader CTA only) =====================
+        if (rank == 0) {
+            constexpr uint32_t idesc = ptx::umma_idesc_tf32(K3_BM * CG, K3_BN);
+            int stage = 0, as = 0;
+            uint32_t phase = 0, aphase = 0;
+            for (int64_t u = cluster_id; u < p.nunits; u += nclusters) {
+                ptx::mbar_wait(&tempty[as], aphase ^ 1);  // epilogue has drained this accumulator
+                ptx::tc_fence_after();
+                const uint32_t d_tmem = tmem_base + (uint32_t)(as * K3_BN);
+                for (int kc = 0; kc < nkc; ++kc) {
+                    ptx::mbar_wait(&full[stage], phase);
+                    ptx::tc_fence_after();
+                    if (lane == 0) {
+                        const uint32_t sb = ptx::smem_u32(smem + stage * L::STAGE_BYTES);
+                        const uint64_t a_hi = ptx::umma_desc_k_sw128(sb);
+                        const uint64_t a_lo = ptx::umma_desc_k_sw128(sb + K3_A_BYTES);
+                        const uint64_t b_hi = ptx::umma_desc_k_sw128(sb + 2 * K3_A_BYTES);
+                        const uint64_t b_lo = ptx::umma_desc_k_sw128(sb + 2 * K3_A_BYTES + L::B_BYTES);
+#pragma unroll
+                        for (int ks = 0; ks < K3_BK / 8; ++ks) {
+                            const uint64_t off = (uint64_t)(ks * 32 >> 4);  // 8 fp32 = 32 bytes along K
+                            ptx::mma_tf32<CG>(d_tmem, a_lo + off, b_hi + off, idesc, (kc | ks) != 0);  // small terms first
+                            ptx::mma_tf32<CG>(d_tmem, a_hi + off, b_lo + off, idesc, 1u);
+                            ptx::mma_tf32<CG>(d_tmem, a_hi + off, b_hi + off, idesc, 1u);
+                        }
+                        ptx::mma_commit<CG>(&empty[stage]);            // smem slot free once these MMAs retire
+                        if (kc == nkc - 1) ptx::mma_commit<CG>(&tfull[as]);  // accumulator complete
+                    }
+                    __syncwarp();
+                    if (++stage == NS) { stage = 0; phase ^= 1; }
+                }
+                as ^= 1;
+                if (as == 0) aphase ^= 1;
+            }
+        }
+    } else {
+        // ===================== epilogue: fused top-k selection =====================
+        const int e = warp & 3;                 // TMEM lane quarter this warp may access
+        const int row = e * 32 + lane;          // query row inside the CTA's 128
+        const int epi_tid = (warp - 2) * 32 + lane;
+        u64* scr = scratch + (size_t)(warp - 2) * p.P;
+        int as = 0;
+        uint32_t aphase = 0;
+        const float INF = __int_as_float(0x7f800000);
+        for (int64_t u = cluster_id; u < p.nunits; u += nclusters) {
+            const int64_t t = u / p.nqb;
+            const int qb = (int)(u - t * p.nqb);
+            const int64_t qi = (int64_t)qb * (K3_BM * CG) + (int64_t)rank * K3_BM + row;
+            const bool valid = qi < p.nq;
+            const int64_t sidx = (int64_t)blockIdx.x * p.qpc + (int64_t)qb * K3_BM + row;
+            int cnt = p.cnt[sidx];
+            float tau = p.tau[sidx];
+            u64 kth = p.kth[sidx];
+            const float qn = valid ? p.qn[qi] : 0.f;
+            const float tau_eff = valid ? fminf(tau, __uint_as_float(__ldcg(p.gts + qi))) : 0.f;
+            // filter threshold on s = ||x||^2 - 2 ip, widened by a few ulps so it never rejects a
+            // candidate the exact test below would accept
+            const float t_cmp = valid ? (tau_eff - qn) + 2e-6f * (fabsf(tau_eff) + qn) : -INF;
+            float* xn = xn_s + as * K3_BN;
+            for (int j = epi_tid; j < K3_BN; j += K3_EPI_THREADS) {
+                const int64_t r = t * K3_BN + j;
+                xn[j] = r < p.n ? p.norms[r] : INF;
+            }
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+
+            ptx::mbar_wait(&tfull[as], aphase);
+            ptx::tc_fence_after();
+            const uint32_t taddr = tmem_base + ((uint32_t)(e * 32) << 16) + (uint32_t)(as * K3_BN);
+            u64* list = p.cand + sidx * p.P;
+#pragma unroll 1
+            for (int c0 = 0; c0 < K3_BN; c0 += 32) {
+                uint32_t v[32];
+                ptx::tmem_ld_32x32(taddr + c0, v);
+                ptx::tmem_ld_wait();
+#pragma unroll
+                for (int c = 0; c < 32; ++c) {
+                    const float ip = __uint_as_float(v[c]);
+                    const float xv = xn[c0 + c];
+                    const float s = fmaf(-2.f, ip, xv);
+                    if (s <= t_cmp) {
+                        float dist = (qn + xv) - 2.f * ip;  // oracle rule (2), then clamp
+                        dist = dist < 0.f ? 0.f : dist;
+                        if (dist <= tau_eff) {
+                            const u64 key = make_key(dist, (uint32_t)(t * K3_BN + c0 + c));
+                            if (key < kth) { list[cnt] = key; ++cnt; }
+                        }
+                    }
+                }
+            }
+            // accumulator drained: hand it back to the MMA warp
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) {
+                if (CG == 1) ptx::mbar_arrive(&tempty[as]);
+                else ptx::mbar_arrive_cluster(&tempty[as], 0);
+            }
+
+            // compaction of lists that could overflow on the next tile (warp-cooperative)
+            unsigned need = __ballot_sync(0xffffffffu, valid && cnt > p.P - K3_BN);
+            while (need) {
+                const int Lq = __ffs(need) - 1;
+                need &= need - 1;
+                const int c = __shfl_sync(0xffffffffu, cnt, Lq);
+                u64* lst = p.cand + (sidx - lane + Lq) * p.P;
+                int Ps = 2;
+                while (Ps < c) Ps <<= 1;
+                __syncwarp();
+                for (int i = lane; i < Ps; i += 32) scr[i] = i < c ? __ldcg(lst + i) : KEY_EMPTY;
+                __syncwarp();
+                warp_bitonic_sort(scr, Ps, lane);
+                const int nc = c < p.k ? c : p.k;
+                for (int i = lane; i < nc; i += 32) lst[i] = scr[i];
+                const u64 newkth = scr[p.k - 1 < Ps ? p.k - 1 : 0];
+                __syncwarp();
+                if (lane == Lq) {
+                    cnt = nc;
+                    if (nc >= p.k) {
+                        kth = newkth;
+                        tau = key_dist(newkth);
+                        atomicMin(p.gts + qi, __float_as_uint(tau));
+                    }
+                }
+            }
+            p.cnt[sidx] = cnt;
+            p.tau[sidx] = tau;
+            p.kth[sidx] = kth;
+            as ^= 1;
+            if (as == 0) aphase ^= 1;
+        }
+    }
+
+    // ---- teardown ----
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (CG == 2) ptx::cluster_sync_all();
+    if (warp == 1) {
+        ptx::tc_fence_after();
+        ptx::tmem_dealloc<CG>(tmem_base, 512);
+    }
 }
+
+// ---- state initialisation -------------------------------------------------------------------
+__global__ void k3_init_kernel(int64_t nslots, int* cnt, float* tau, u64* kth, int64_t nq, unsigned int* gts) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < nslots) { cnt[i] = 0; tau[i] = FLT_MAX; kth[i] = (u64)FLT_MAX_BITS << 32; }
+    if (gts && i < nq) gts[i] = FLT_MAX_BITS;
+}
+
+// ---- K4: per query, merge the lists of every CTA that saw it ---------------------------------
+static constexpr int K4_THREADS = 256;
+static constexpr int K4_P = 4096;
+
+__global__ void __launch_bounds__(K4_THREADS)
+k4_merge_kernel(const K3Params p, int cg, int ncta, int threshold_only, float* __restrict__ D, int64_t* __restrict__ I) {
+    __shared__ u64 buf[K4_P];
+    __shared__ int s_cnt;
+    __shared__ u64 s_kth;
+    const int tid = threadIdx.x;
+    const int64_t qi = blockIdx.x;
+    const int bq = K3_BM * cg;
+    const int qb = (int)(qi / bq);
+    const int r = (int)(qi - (int64_t)qb * bq) / K3_BM;
+    const int row = (int)(qi % K3_BM);
+    const float bound = __uint_as_float(p.gts[qi]);
+    if (tid == 0) { s_cnt = 0; s_kth = KEY_EMPTY; }
+    __syncthreads();
+    for (int cta = r; cta < ncta; cta += cg) {
+        const int64_t sidx = (int64_t)cta * p.qpc + (int64_t)qb * K3_BM + row;
+        const int c = p.cnt[sidx];
+        const u64* lst = p.cand + sidx * p.P;
+        for (int i0 = 0; i0 < c; i0 += K4_THREADS) {
+            int flag = 0;
+            const int i = i0 + tid;
+            if (i < c) {
+                const u64 key = lst[i];
+                if (key_dist(key) <= bound && key < s_kth) {
+                    int pos = atomicAdd(&s_cnt, 1);
+                    buf[pos] = key;
+                    if (pos + 1 > K4_P - K4_THREADS) flag = 1;
+                }
+            }
+            if (__syncthreads_or(flag)) {
+                // sort, keep k (same routine as the scan kernel's compaction, inlined for static smem)
+                const int cc = s_cnt;
+                int Ps = 2;
+                while (Ps < cc) Ps <<= 1;
+                for (int j = cc + tid; j < Ps; j += K4_THREADS) buf[j] = KEY_EMPTY;
+                __syncthreads();
+                block_bitonic_sort(buf, Ps);
+                if (tid == 0) { s_cnt = cc < p.k ? cc : p.k; if (cc >= p.k) s_kth = buf[p.k - 1]; }
+                __syncthreads();
+            }
+        }
+    }
+    __syncthreads();
+    const int cc = s_cnt;
+    int Ps = 2;
+    while (Ps < cc) Ps <<= 1;
+    for (int j = cc + tid; j < Ps; j += K4_THREADS) buf[j] = KEY_EMPTY;
+    __syncthreads();
+    block_bitonic_sort(buf, Ps);
+    if (threshold_only) {
+        // warm start: the k-th smallest distance over a sample of the rows bounds the final one
+        if (tid == 0 && cc >= p.k) p.gts[qi] = (unsigned int)(buf[p.k - 1] >> 32);
+        return;
+    }
+    for (int j = tid; j < p.k; j += K4_THREADS) {
+        if (j < cc) {
+            D[qi * p.k + j] = key_dist(buf[j]);
+            I[qi * p.k + j] = (int64_t)key_row(buf[j]);
+        } else {
+            D[qi * p.k + j] = FLT_MAX;
+            I[qi * p.k + j] = -1;
+        }
+    }
+}
+
+// ---- host side ----------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+struct K3State {
+    int device = 0, sm_count = 148;
+    int cg = 1;
+    EncodeTiledFn encode = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    bool timing = false;
+    bool timed = false;
+};
+
+static int k3_cg_for(int k) { (void)k; return 1; }
+static int k3_P(int k) { return next_pow2(k + K3_BN); }
+
+bool k3_supported(int d, int k) {
+    // TMA needs a 16-byte row pitch; the CG = 1 configuration has shared memory for lists up to 512 keys
+    return d % 4 == 0 && k3_P(k) <= 512;
+}
+
+struct K3Layout {
+    int cg, ncta, nqb, qpc, P;
+    size_t off_qlo, off_qn, off_gts, off_cnt, off_tau, off_kth, off_cand, total;
+};
+
+static K3Layout k3_layout(int sm_count, int d, int64_t nq, int k) {
+    K3Layout L;
+    L.cg = k3_cg_for(k);
+    L.ncta = (sm_count / L.cg) * L.cg;
+    L.nqb = (int)((nq + K3_BM * L.cg - 1) / (K3_BM * L.cg));
+    L.qpc = L.nqb * K3_BM;
+    L.P = k3_P(k);
+    auto al = [](size_t v) { return (v + 255) & ~(size_t)255; };
+    size_t o = 0;
+    L.off_qlo = o; o += al((size_t)nq * d * 4);
+    L.off_qn = o; o += al((size_t)nq * 4);
+    L.off_gts = o; o += al((size_t)nq * 4);
+    size_t slots = (size_t)L.ncta * L.qpc;
+    L.off_cnt = o; o += al(slots * 4);
+    L.off_tau = o; o += al(slots * 4);
+    L.off_kth = o; o += al(slots * 8);
+    L.off_cand = o; o += al(slots * (size_t)L.P * 8);
+    L.total = o;
+    return L;
+}
+
+size_t k3_scratch_bytes(int sm_count, int d, int64_t nq, int k) { return k3_layout(sm_count, d, nq, k).total; }
+
+int k3_create(K3State** out, int device, int sm_count) {
+    K3State* s = new K3State();
+    s->device = device;
+    s->sm_count = sm_count;
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+    if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn) {
+        set_error("cuTensorMapEncodeTiled not available from the driver (%s)", cudaGetErrorString(e));
+        delete s;
+        return B2K_ECUDA;
+    }
+    s->encode = (EncodeTiledFn)fn;
+    cudaEventCreate(&s->ev0);
+    cudaEventCreate(&s->ev1);
+    *out = s;
+    return B2K_OK;
+}
+
+void k3_destroy(K3State* s) {
+    if (!s) return;
+    if (s->ev0) cudaEventDestroy(s->ev0);
+    if (s->ev1) cudaEventDestroy(s->ev1);
+    delete s;
+}
+
+void k3_invalidate_maps(K3State*) {}  // maps are re-encoded on every search (host-side, ~1 us each)
+
+void k3_set_timing(K3State* s, bool on) { s->timing = on; }
+
+int k3_last_kernel_ms(K3State* s, float* ms) {
+    if (!s->timed) return B2K_EINVAL;
+    B2K_CUDA(cudaEventSynchronize(s->ev1));
+    B2K_CUDA(cudaEventElapsedTime(ms, s->ev0, s->ev1));
+    return B2K_OK;
+}
+
+static int make_map(K3State* s, CUtensorMap* m, const float* base, int64_t rows, int d, int box_rows) {
+    cuuint64_t gdim[2] = {(cuuint64_t)d, (cuuint64_t)rows};
+    cuuint64_t gstr[1] = {(cuuint64_t)d * 4};
+    cuuint32_t box[2] = {(cuuint32_t)K3_BK, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = s->encode(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), gdim, gstr, box, estr,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled failed (%d) for %lld x %d", (int)r, (long long)rows, d);
+        return B2K_ECUDA;
+    }
+    return B2K_OK;
+}
+
+template <int CG, int NS>
+static int launch_k3(const CUtensorMap& mq, const CUtensorMap& mql, const CUtensorMap& mx, const CUtensorMap& mxl,
+                     const K3Params& p, int ncta, cudaStream_t st) {
+    size_t smem = K3Smem<CG, NS>::bytes(p.P);
+    B2K_CUDA(cudaFuncSetAttribute(k3_tf32x3_topk_kernel<CG, NS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(ncta);
+    cfg.blockDim = dim3(K3_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = CG;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    B2K_CUDA(cudaLaunchKernelEx(&cfg, k3_tf32x3_topk_kernel<CG, NS>, mq, mql, mx, mxl, p));
+    count_launch();
+    return B2K_OK;
+}
+
+int k3_search(K3State* s, const float* x, const float* xlo, const float* norms, int64_t n, int64_t capacity, int d,
+              const float* q, int64_t nq, int k, float* D, int64_t* I, unsigned char* scratch, cudaStream_t st) {
+    (void)capacity;
+    K3Layout L = k3_layout(s->sm_count, d, nq, k);
+    float* qlo = reinterpret_cast<float*>(scratch + L.off_qlo);
+    K3Params p;
+    p.n = n; p.d = d; p.nq = nq; p.k = k; p.P = L.P; p.nqb = L.nqb; p.qpc = L.qpc;
+    const int64_t ntiles = (n + K3_BN - 1) / K3_BN;
+    p.nunits = ntiles * L.nqb;
+    p.norms = norms;
+    p.qn = reinterpret_cast<float*>(scratch + L.off_qn);
+    p.gts = reinterpret_cast<unsigned int*>(scratch + L.off_gts);
+    p.cnt = reinterpret_cast<int*>(scratch + L.off_cnt);
+    p.tau = reinterpret_cast<float*>(scratch + L.off_tau);
+    p.kth = reinterpret_cast<u64*>(scratch + L.off_kth);
+    p.cand = reinterpret_cast<u64*>(scratch + L.off_cand);
+
+    // queries: norms + TF32 residual rows (K1 reused), list state reset
+    int rc = launch_row_prep(q, nq, d, const_cast<float*>(p.qn), qlo, st);
+    if (rc) return rc;
+    const int64_t nslots = (int64_t)L.ncta * L.qpc;
+    const int64_t ninit = nslots > nq ? nslots : nq;
+    k3_init_kernel<<<(unsigned)((ninit + 255) / 256), 256, 0, st>>>(nslots, p.cnt, p.tau, p.kth, nq, p.gts);
+    count_launch();
+    B2K_CUDA(cudaGetLastError());
+
+    CUtensorMap mq, mql, mx, mxl;
+    if ((rc = make_map(s, &mq, q, nq, d, K3_BM))) return rc;
+    if ((rc = make_map(s, &mql, qlo, nq, d, K3_BM))) return rc;
+    if ((rc = make_map(s, &mx, x, n, d, K3_BN / L.cg))) return rc;
+    if ((rc = make_map(s, &mxl, xlo, n, d, K3_BN / L.cg))) return rc;
+
+    // Warm start: one tile per CTA (pair) with open thresholds, then per query the k-th smallest
+    // distance of that sample becomes the shared threshold -- an upper bound of the final k-th
+    // distance, so the full pass prunes from its first tile instead of sorting its way down.
+    const int nclusters = L.ncta / L.cg;
+    if (ntiles >= 4 * (int64_t)nclusters && (int64_t)nclusters * K3_BN >= 2 * (int64_t)k) {
+        K3Params pre = p;
+        pre.n = (int64_t)nclusters * K3_BN;
+        pre.nunits = (int64_t)nclusters * L.nqb;
+        rc = launch_k3<1, 2>(mq, mql, mx, mxl, pre, L.ncta, st);
+        if (rc) return rc;
+        k4_merge_kernel<<<(unsigned)nq, K4_THREADS, 0, st>>>(pre, L.cg, L.ncta, 1, nullptr, nullptr);
+        k3_init_kernel<<<(unsigned)((nslots + 255) / 256), 256, 0, st>>>(nslots, p.cnt, p.tau, p.kth, nq, nullptr);
+        count_launch(2);
+        B2K_CUDA(cudaGetLastError());
+    }
+
+    if (s->timing) B2K_CUDA(cudaEventRecord(s->ev0, st));
+    rc = launch_k3<1, 2>(mq, mql, mx, mxl, p, L.ncta, st);
+    if (rc) return rc;
+    if (s->timing) { B2K_CUDA(cudaEventRecord(s->ev1, st)); s->timed = true; }
+
+    k4_merge_kernel<<<(unsigned)nq, K4_THREADS, 0, st>>>(p, L.cg, L.ncta, 0, D, I);
+    count_launch();
+    B2K_CUDA(cudaGetLastError());
+    return B2K_OK;
+}
+
 }  // namespace b2k
