@@ -217,6 +217,7 @@ def main():
     ms_dev, _, launches = timed(lambda: index.search(q_dev, k), args.steps, args.warmup)
     sampler.stop_flag = True
     sampler.join()
+    stats = index.stats() if hasattr(index, "stats") else {}
     _, wall_e2e, _ = timed(lambda: index.search(q_host, k), args.steps, max(args.warmup, 1))
     if dist is not None:
         t = torch.tensor([wall_e2e], device="cuda")
@@ -265,7 +266,6 @@ def main():
                      "how": "torch.matmul fp32 8192^3 with allow_tf32 (cuBLAS), CUDA events"}
         del a, b
         torch.backends.cuda.matmul.allow_tf32 = False
-    stats = index.stats() if hasattr(index, "stats") else {}
     n_local = N // world if world > 1 else N
     if stats.get("path") == "tensor":
         k_ms = stats["main_kernel_ms"]

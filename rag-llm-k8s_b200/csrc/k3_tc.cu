@@ -61,7 +61,10 @@ struct K3Params {
     float* tau;         // [ncta][qpc]
     u64* kth;           // [ncta][qpc]
     u64* cand;          // [ncta][qpc][P]
+    u64* next_unit;     // dynamic scheduler: next unit to hand out
 };
+
+static constexpr int K3_NSCHED = 4;  // depth of the unit-id ring between the scheduler and the other roles
 
 template <int CG, int NS>
 struct K3Smem {
@@ -69,11 +72,29 @@ struct K3Smem {
     static constexpr int B_BYTES = B_ROWS * K3_BK * 4;
     static constexpr int STAGE_BYTES = 2 * K3_A_BYTES + 2 * B_BYTES;
     static constexpr int OFF_XN = NS * STAGE_BYTES;            // float[2][256]
-    static constexpr int OFF_BAR = OFF_XN + 2 * K3_BN * 4;     // full[NS] empty[NS] tfull[2] tempty[2]
-    static constexpr int OFF_TMEM = OFF_BAR + (2 * NS + 4) * 8;
+    static constexpr int OFF_BAR = OFF_XN + 2 * K3_BN * 4;     // full[NS] empty[NS] tfull[2] tempty[2] sfull[4] sempty[4]
+    static constexpr int NBAR = 2 * NS + 4 + 2 * K3_NSCHED;
+    static constexpr int OFF_SCHED = OFF_BAR + NBAR * 8;       // long long[K3_NSCHED]
+    static constexpr int OFF_TMEM = OFF_SCHED + K3_NSCHED * 8;
     static constexpr int OFF_SCRATCH = (OFF_TMEM + 16 + 15) & ~15;  // 4 warps x P keys
     static size_t bytes(int P) { return (size_t)OFF_SCRATCH + (size_t)4 * P * 8 + 1024; }
 };
+
+// Consumer side of the unit-id ring: wait for slot `ss`, read the unit, release the slot to the
+// scheduler (the leader CTA's producer thread).  Called by whole warps (warp-uniform result).
+template <int CG>
+__device__ __forceinline__ long long sched_take_warp(uint64_t* sfull, uint64_t* sempty, const long long* sched_u,
+                                                     int ss, uint32_t sph, uint32_t rank, int lane) {
+    if (CG == 1) ptx::mbar_wait(&sfull[ss], sph);
+    else ptx::mbar_wait_cluster(&sfull[ss], sph);
+    const long long u = *reinterpret_cast<const volatile long long*>(&sched_u[ss]);
+    __syncwarp();
+    if (lane == 0) {
+        if (CG == 1 || rank == 0) ptx::mbar_arrive(&sempty[ss]);
+        else ptx::mbar_arrive_cluster(&sempty[ss], 0);
+    }
+    return u;
+}
 
 template <int CG, int NS>
 __global__ void __launch_bounds__(K3_THREADS, 1)
@@ -88,19 +109,21 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
     uint64_t* empty = full + NS;
     uint64_t* tfull = empty + NS;
     uint64_t* tempty = tfull + 2;
+    uint64_t* sfull = tempty + 2;
+    uint64_t* sempty = sfull + K3_NSCHED;
+    long long* sched_u = reinterpret_cast<long long*>(smem + L::OFF_SCHED);
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + L::OFF_TMEM);
     u64* scratch = reinterpret_cast<u64*>(smem + L::OFF_SCRATCH);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t rank = (CG == 2) ? ptx::cluster_ctarank() : 0u;
-    const int cluster_id = blockIdx.x / CG;
-    const int nclusters = gridDim.x / CG;
     const int nkc = (p.d + K3_BK - 1) / K3_BK;
 
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tmap(&tm_q); ptx::prefetch_tmap(&tm_ql); ptx::prefetch_tmap(&tm_x); ptx::prefetch_tmap(&tm_xl);
         for (int s = 0; s < NS; ++s) { ptx::mbar_init(&full[s], CG); ptx::mbar_init(&empty[s], 1); }
         for (int s = 0; s < 2; ++s) { ptx::mbar_init(&tfull[s], 1); ptx::mbar_init(&tempty[s], 4 * CG); }
+        for (int s = 0; s < K3_NSCHED; ++s) { ptx::mbar_init(&sfull[s], 1); ptx::mbar_init(&sempty[s], 5 * CG); }
         ptx::fence_barrier_init();
     }
     if (warp == 1) {
@@ -114,11 +137,29 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
     const uint32_t tmem_base = *tmem_slot;
 
     if (warp == 0) {
-        // ===================== TMA producer =====================
+        // ===================== scheduler + TMA producer =====================
         if (lane == 0) {
-            int stage = 0;
-            uint32_t phase = 0;
-            for (int64_t u = cluster_id; u < p.nunits; u += nclusters) {
+            int stage = 0, ss = 0;
+            uint32_t phase = 0, sph = 0;
+            for (;;) {
+                long long u;
+                if (rank == 0) {
+                    // dynamic scheduling: units are handed out in order, so the CTAs running at any
+                    // moment work on neighbouring database tiles and share them through L2
+                    ptx::mbar_wait(&sempty[ss], sph ^ 1);
+                    u = (long long)atomicAdd(p.next_unit, 1ull);
+                    if (u >= p.nunits) u = -1;
+                    sched_u[ss] = u;
+                    if (CG == 2) ptx::st_cluster_b64(&sched_u[ss], 1, (uint64_t)u);
+                    ptx::mbar_arrive(&sfull[ss]);
+                    if (CG == 2) ptx::mbar_arrive_cluster(&sfull[ss], 1);
+                } else {
+                    ptx::mbar_wait_cluster(&sfull[ss], sph);
+                    u = *reinterpret_cast<const volatile long long*>(&sched_u[ss]);
+                    ptx::mbar_arrive_cluster(&sempty[ss], 0);
+                }
+                if (++ss == K3_NSCHED) { ss = 0; sph ^= 1; }
+                if (u < 0) break;
                 const int64_t t = u / p.nqb;
                 const int qb = (int)(u - t * p.nqb);
                 const int qrow0 = qb * (K3_BM * CG) + (int)rank * K3_BM;
@@ -148,9 +189,12 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
         // ===================== MMA issuer (leader CTA only) =====================
         if (rank == 0) {
             constexpr uint32_t idesc = ptx::umma_idesc_tf32(K3_BM * CG, K3_BN);
-            int stage = 0, as = 0;
-            uint32_t phase = 0, aphase = 0;
-            for (int64_t u = cluster_id; u < p.nunits; u += nclusters) {
+            int stage = 0, as = 0, ss = 0;
+            uint32_t phase = 0, aphase = 0, sph = 0;
+            for (;;) {
+                const long long u = sched_take_warp<CG>(sfull, sempty, sched_u, ss, sph, rank, lane);
+                if (++ss == K3_NSCHED) { ss = 0; sph ^= 1; }
+                if (u < 0) break;
                 ptx::mbar_wait(&tempty[as], aphase ^ 1);  // epilogue has drained this accumulator
                 ptx::tc_fence_after();
                 const uint32_t d_tmem = tmem_base + (uint32_t)(as * K3_BN);
@@ -186,10 +230,13 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
         const int row = e * 32 + lane;          // query row inside the CTA's 128
         const int epi_tid = (warp - 2) * 32 + lane;
         u64* scr = scratch + (size_t)(warp - 2) * p.P;
-        int as = 0;
-        uint32_t aphase = 0;
+        int as = 0, ss = 0;
+        uint32_t aphase = 0, sph = 0;
         const float INF = __int_as_float(0x7f800000);
-        for (int64_t u = cluster_id; u < p.nunits; u += nclusters) {
+        for (;;) {
+            const long long u = sched_take_warp<CG>(sfull, sempty, sched_u, ss, sph, rank, lane);
+            if (++ss == K3_NSCHED) { ss = 0; sph ^= 1; }
+            if (u < 0) break;
             const int64_t t = u / p.nqb;
             const int qb = (int)(u - t * p.nqb);
             const int64_t qi = (int64_t)qb * (K3_BM * CG) + (int64_t)rank * K3_BM + row;
@@ -234,11 +281,11 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
                     }
                 }
             }
-            // accumulator drained: hand it back to the MMA warp
+            // accumulator drained: hand it back to the MMA warp (of the leader CTA)
             ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) {
-                if (CG == 1) ptx::mbar_arrive(&tempty[as]);
+                if (CG == 1 || rank == 0) ptx::mbar_arrive(&tempty[as]);
                 else ptx::mbar_arrive_cluster(&tempty[as], 0);
             }
 
@@ -287,8 +334,10 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
 }
 
 // ---- state initialisation -------------------------------------------------------------------
-__global__ void k3_init_kernel(int64_t nslots, int* cnt, float* tau, u64* kth, int64_t nq, unsigned int* gts) {
+__global__ void k3_init_kernel(int64_t nslots, int* cnt, float* tau, u64* kth, int64_t nq, unsigned int* gts,
+                               u64* next_unit) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) *next_unit = 0;
     if (i < nslots) { cnt[i] = 0; tau[i] = FLT_MAX; kth[i] = (u64)FLT_MAX_BITS << 32; }
     if (gts && i < nq) gts[i] = FLT_MAX_BITS;
 }
@@ -367,31 +416,36 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
+static int g_default_cg = 1;  // until the CTA-pair configuration is validated on hardware
+
 struct K3State {
     int device = 0, sm_count = 148;
-    int cg = 1;
+    int cg = g_default_cg;
     EncodeTiledFn encode = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     bool timing = false;
     bool timed = false;
 };
 
-static int k3_cg_for(int k) { (void)k; return 1; }
 static int k3_P(int k) { return next_pow2(k + K3_BN); }
+// CG = 1 has shared memory for compaction scratch up to 512 keys per warp; CG = 2 up to 2048.
+static int k3_cg_for(int k, int want) { return (want == 2 || k3_P(k) > 512) ? 2 : 1; }
 
 bool k3_supported(int d, int k) {
-    // TMA needs a 16-byte row pitch; the CG = 1 configuration has shared memory for lists up to 512 keys
-    return d % 4 == 0 && k3_P(k) <= 512;
+    // TMA needs a 16-byte row pitch
+    return d % 4 == 0 && k3_P(k) <= 2048;
 }
+
+void k3_set_cta_group(K3State* s, int cg);
 
 struct K3Layout {
     int cg, ncta, nqb, qpc, P;
-    size_t off_qlo, off_qn, off_gts, off_cnt, off_tau, off_kth, off_cand, total;
+    size_t off_qlo, off_qn, off_gts, off_next, off_cnt, off_tau, off_kth, off_cand, total;
 };
 
-static K3Layout k3_layout(int sm_count, int d, int64_t nq, int k) {
+static K3Layout k3_layout(int sm_count, int d, int64_t nq, int k, int want_cg) {
     K3Layout L;
-    L.cg = k3_cg_for(k);
+    L.cg = k3_cg_for(k, want_cg);
     L.ncta = (sm_count / L.cg) * L.cg;
     L.nqb = (int)((nq + K3_BM * L.cg - 1) / (K3_BM * L.cg));
     L.qpc = L.nqb * K3_BM;
@@ -401,6 +455,7 @@ static K3Layout k3_layout(int sm_count, int d, int64_t nq, int k) {
     L.off_qlo = o; o += al((size_t)nq * d * 4);
     L.off_qn = o; o += al((size_t)nq * 4);
     L.off_gts = o; o += al((size_t)nq * 4);
+    L.off_next = o; o += 256;
     size_t slots = (size_t)L.ncta * L.qpc;
     L.off_cnt = o; o += al(slots * 4);
     L.off_tau = o; o += al(slots * 4);
@@ -410,7 +465,11 @@ static K3Layout k3_layout(int sm_count, int d, int64_t nq, int k) {
     return L;
 }
 
-size_t k3_scratch_bytes(int sm_count, int d, int64_t nq, int k) { return k3_layout(sm_count, d, nq, k).total; }
+size_t k3_scratch_bytes(int sm_count, int d, int64_t nq, int k) {
+    // sized for either CTA-group configuration
+    size_t a = k3_layout(sm_count, d, nq, k, 1).total, b = k3_layout(sm_count, d, nq, k, 2).total;
+    return a > b ? a : b;
+}
 
 int k3_create(K3State** out, int device, int sm_count) {
     K3State* s = new K3State();
@@ -441,6 +500,7 @@ void k3_destroy(K3State* s) {
 void k3_invalidate_maps(K3State*) {}  // maps are re-encoded on every search (host-side, ~1 us each)
 
 void k3_set_timing(K3State* s, bool on) { s->timing = on; }
+void k3_set_cta_group(K3State* s, int cg) { s->cg = cg == 2 ? 2 : 1; }
 
 int k3_last_kernel_ms(K3State* s, float* ms) {
     if (!s->timed) return B2K_EINVAL;
@@ -486,10 +546,17 @@ static int launch_k3(const CUtensorMap& mq, const CUtensorMap& mql, const CUtens
     return B2K_OK;
 }
 
+static int launch_k3_any(int cg, int P, const CUtensorMap& mq, const CUtensorMap& mql, const CUtensorMap& mx,
+                         const CUtensorMap& mxl, const K3Params& p, int ncta, cudaStream_t st) {
+    if (cg == 1) return launch_k3<1, 2>(mq, mql, mx, mxl, p, ncta, st);
+    if (P <= 512) return launch_k3<2, 3>(mq, mql, mx, mxl, p, ncta, st);
+    return launch_k3<2, 2>(mq, mql, mx, mxl, p, ncta, st);
+}
+
 int k3_search(K3State* s, const float* x, const float* xlo, const float* norms, int64_t n, int64_t capacity, int d,
               const float* q, int64_t nq, int k, float* D, int64_t* I, unsigned char* scratch, cudaStream_t st) {
     (void)capacity;
-    K3Layout L = k3_layout(s->sm_count, d, nq, k);
+    K3Layout L = k3_layout(s->sm_count, d, nq, k, s->cg);
     float* qlo = reinterpret_cast<float*>(scratch + L.off_qlo);
     K3Params p;
     p.n = n; p.d = d; p.nq = nq; p.k = k; p.P = L.P; p.nqb = L.nqb; p.qpc = L.qpc;
@@ -502,13 +569,14 @@ int k3_search(K3State* s, const float* x, const float* xlo, const float* norms, 
     p.tau = reinterpret_cast<float*>(scratch + L.off_tau);
     p.kth = reinterpret_cast<u64*>(scratch + L.off_kth);
     p.cand = reinterpret_cast<u64*>(scratch + L.off_cand);
+    p.next_unit = reinterpret_cast<u64*>(scratch + L.off_next);
 
     // queries: norms + TF32 residual rows (K1 reused), list state reset
     int rc = launch_row_prep(q, nq, d, const_cast<float*>(p.qn), qlo, st);
     if (rc) return rc;
     const int64_t nslots = (int64_t)L.ncta * L.qpc;
     const int64_t ninit = nslots > nq ? nslots : nq;
-    k3_init_kernel<<<(unsigned)((ninit + 255) / 256), 256, 0, st>>>(nslots, p.cnt, p.tau, p.kth, nq, p.gts);
+    k3_init_kernel<<<(unsigned)((ninit + 255) / 256), 256, 0, st>>>(nslots, p.cnt, p.tau, p.kth, nq, p.gts, p.next_unit);
     count_launch();
     B2K_CUDA(cudaGetLastError());
 
@@ -522,20 +590,20 @@ int k3_search(K3State* s, const float* x, const float* xlo, const float* norms, 
     // distance of that sample becomes the shared threshold -- an upper bound of the final k-th
     // distance, so the full pass prunes from its first tile instead of sorting its way down.
     const int nclusters = L.ncta / L.cg;
-    if (ntiles >= 4 * (int64_t)nclusters && (int64_t)nclusters * K3_BN >= 2 * (int64_t)k) {
+    if (ntiles >= 2 * (int64_t)nclusters && (int64_t)nclusters * K3_BN >= 2 * (int64_t)k) {
         K3Params pre = p;
         pre.n = (int64_t)nclusters * K3_BN;
         pre.nunits = (int64_t)nclusters * L.nqb;
-        rc = launch_k3<1, 2>(mq, mql, mx, mxl, pre, L.ncta, st);
+        rc = launch_k3_any(L.cg, L.P, mq, mql, mx, mxl, pre, L.ncta, st);
         if (rc) return rc;
         k4_merge_kernel<<<(unsigned)nq, K4_THREADS, 0, st>>>(pre, L.cg, L.ncta, 1, nullptr, nullptr);
-        k3_init_kernel<<<(unsigned)((nslots + 255) / 256), 256, 0, st>>>(nslots, p.cnt, p.tau, p.kth, nq, nullptr);
+        k3_init_kernel<<<(unsigned)((nslots + 255) / 256), 256, 0, st>>>(nslots, p.cnt, p.tau, p.kth, nq, nullptr, p.next_unit);
         count_launch(2);
         B2K_CUDA(cudaGetLastError());
     }
 
     if (s->timing) B2K_CUDA(cudaEventRecord(s->ev0, st));
-    rc = launch_k3<1, 2>(mq, mql, mx, mxl, p, L.ncta, st);
+    rc = launch_k3_any(L.cg, L.P, mq, mql, mx, mxl, p, L.ncta, st);
     if (rc) return rc;
     if (s->timing) { B2K_CUDA(cudaEventRecord(s->ev1, st)); s->timed = true; }
 
