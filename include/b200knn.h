@@ -104,7 +104,8 @@ B2K_API int b2k_merge_topk(int device, int nlists, int64_t nq, int64_t k, const 
                    int on_device, void* stream);
 
 /* Tuning / test hooks.  Keys: "path" (0 auto, 1 force the scan kernel, 2 force the
- * tensor-core kernel), "scan_ctas_per_sm", "timing" (0/1).  Unknown key -> B2K_EINVAL. */
+ * tensor-core kernel), "scan_ctas_per_sm", "timing" (0/1), "tensor_cta_group" (1 or 2),
+ * "tensor_sep_accum" (0 auto, 1 on, 2 off).  Unknown key -> B2K_EINVAL. */
 B2K_API int b2k_set_option(b2k_index* h, const char* key, int64_t value);
 
 /* Read-back of measurements / state.  Keys: "last_path" (1 = scan kernel, 2 = tensor-core

@@ -58,6 +58,7 @@ struct b2k_index {
     int opt_scan_ctas_per_sm = 2;
     int opt_timing = 0;
     int opt_cta_group = 0;  // 0 = library default
+    int opt_sep = 0;
     int last_path = 0;
     int sticky = 0;
     K3State* k3 = nullptr;
@@ -258,6 +259,10 @@ int b2k_set_option(b2k_index* h, const char* key, int64_t value) {
         if (value != 1 && value != 2) { set_error("option tensor_cta_group must be 1 or 2"); return B2K_EINVAL; }
         h->opt_cta_group = (int)value;
         if (h->k3) k3_set_cta_group(h->k3, h->opt_cta_group);
+    } else if (!strcmp(key, "tensor_sep_accum")) {
+        if (value < 0 || value > 2) { set_error("option tensor_sep_accum must be 0 (auto), 1 (on) or 2 (off)"); return B2K_EINVAL; }
+        h->opt_sep = (int)value;
+        if (h->k3) k3_set_sep_mode(h->k3, h->opt_sep);
     } else if (!strcmp(key, "timing")) {
         h->opt_timing = value != 0;
         if (h->k3) k3_set_timing(h->k3, h->opt_timing != 0);
@@ -417,6 +422,7 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
                 rc = k3_create(&h->k3, h->device, h->sm_count);
                 if (!rc) k3_set_timing(h->k3, h->opt_timing != 0);
                 if (!rc && h->opt_cta_group) k3_set_cta_group(h->k3, h->opt_cta_group);
+                if (!rc) k3_set_sep_mode(h->k3, h->opt_sep);
             }
             if (!rc) h->last_path = 2;
             if (!rc) rc = k3_search(h->k3, h->x, h->xlo, h->norms, h->ntotal, h->capacity, h->d, qd, nq, kk, Dd, Id,

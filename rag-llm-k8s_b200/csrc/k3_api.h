@@ -19,7 +19,8 @@ int k3_search(K3State* s, const float* x, const float* xlo, const float* norms, 
 
 // optional CUDA-event timing of the main kernel (bench.py's roofline numbers)
 void k3_set_timing(K3State* s, bool on);
-void k3_set_cta_group(K3State* s, int cg);  // 1 = one CTA per tile, 2 = CTA pairs (cta_group::2)
+void k3_set_cta_group(K3State* s, int cg);
+void k3_set_sep_mode(K3State* s, int m);     // separate accumulator for the small cross terms: 0 auto, 1 on, 2 off  // 1 = one CTA per tile, 2 = CTA pairs (cta_group::2)
 int k3_last_kernel_ms(K3State* s, float* ms);
 
 }  // namespace b2k

@@ -62,6 +62,7 @@ struct K3Params {
     u64* kth;           // [ncta][qpc]
     u64* cand;          // [ncta][qpc][P]
     u64* next_unit;     // dynamic scheduler: next unit to hand out
+    int static_mode;    // 1: CTA (pair) c takes exactly the nqb units of tile c (warm-start pass)
 };
 
 static constexpr int K3_NSCHED = 4;  // depth of the unit-id ring between the scheduler and the other roles
@@ -96,7 +97,50 @@ __device__ __forceinline__ long long sched_take_warp(uint64_t* sfull, uint64_t* 
     return u;
 }
 
-template <int CG, int NS>
+// One thread, 32 consecutive accumulator columns of its query row: branch-free filter, then the
+// (rare) survivors.  v = main accumulator, w = cross-term accumulator (SEP only).
+template <bool SEP>
+__device__ __forceinline__ void k3_filter_chunk(const uint32_t (&v)[32], const uint32_t (&w)[32], const float* xn,
+                                                float t_cmp, float qn, float tau_eff, u64 kth, uint32_t row0,
+                                                u64* list, int& cnt) {
+    uint32_t mask = 0;
+    float ip[32];
+#pragma unroll
+    for (int c = 0; c < 32; c += 4) {
+        const float4 x4 = *reinterpret_cast<const float4*>(xn + c);
+        const float xs[4] = {x4.x, x4.y, x4.z, x4.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            ip[c + j] = SEP ? __uint_as_float(v[c + j]) + __uint_as_float(w[c + j]) : __uint_as_float(v[c + j]);
+            const float s = fmaf(-2.f, ip[c + j], xs[j]);
+            mask |= (s <= t_cmp) ? (1u << (c + j)) : 0u;
+        }
+    }
+    if (mask) {
+#pragma unroll
+        for (int c = 0; c < 32; ++c) {
+            if (mask & (1u << c)) {
+                const float xv = xn[c];
+                float dist = (qn + xv) - 2.f * ip[c];  // oracle rule (2), then clamp
+                dist = dist < 0.f ? 0.f : dist;
+                if (dist <= tau_eff) {
+                    const u64 key = make_key(dist, row0 + c);
+                    if (key < kth) { list[cnt] = key; ++cnt; }
+                }
+            }
+        }
+    }
+}
+
+// SEP = true keeps the two small cross products (Q_lo*X_hi + Q_hi*X_lo) in their own TMEM
+// accumulator (columns 256..511) and adds it to the main one in the epilogue.  The tensor core
+// truncates on every accumulate (measured ~0.8 ulp of the accumulator per MMA, biased towards
+// zero), so adding the 2^-11-sized terms into the large accumulator triples that error for
+// nothing; with SEP the large accumulator sees d/8 accumulations instead of 3d/8.  It costs the
+// double buffering (the MMAs of the next tile wait for the epilogue), so it is used for long
+// rows (d >= 512) where the relative cost is a few percent and the error would otherwise
+// exceed 1e-5 of ||q||^2 + ||x||^2 on near-duplicate unit-norm vectors.
+template <int CG, int NS, bool SEP>
 __global__ void __launch_bounds__(K3_THREADS, 1)
 k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_ql,
                       const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_xl,
@@ -139,7 +183,7 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
     if (warp == 0) {
         // ===================== scheduler + TMA producer =====================
         if (lane == 0) {
-            int stage = 0, ss = 0;
+            int stage = 0, ss = 0, static_i = 0;
             uint32_t phase = 0, sph = 0;
             for (;;) {
                 long long u;
@@ -147,7 +191,12 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
                     // dynamic scheduling: units are handed out in order, so the CTAs running at any
                     // moment work on neighbouring database tiles and share them through L2
                     ptx::mbar_wait(&sempty[ss], sph ^ 1);
-                    u = (long long)atomicAdd(p.next_unit, 1ull);
+                    if (p.static_mode) {
+                        u = static_i < p.nqb ? (long long)(blockIdx.x / CG) * p.nqb + static_i : -1;
+                        ++static_i;
+                    } else {
+                        u = (long long)atomicAdd(p.next_unit, 1ull);
+                    }
                     if (u >= p.nunits) u = -1;
                     sched_u[ss] = u;
                     if (CG == 2) ptx::st_cluster_b64(&sched_u[ss], 1, (uint64_t)u);
@@ -198,6 +247,7 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
                 ptx::mbar_wait(&tempty[as], aphase ^ 1);  // epilogue has drained this accumulator
                 ptx::tc_fence_after();
                 const uint32_t d_tmem = tmem_base + (uint32_t)(as * K3_BN);
+                const uint32_t d_corr = SEP ? tmem_base + (uint32_t)K3_BN : d_tmem;
                 for (int kc = 0; kc < nkc; ++kc) {
                     ptx::mbar_wait(&full[stage], phase);
                     ptx::tc_fence_after();
@@ -210,9 +260,9 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
 #pragma unroll
                         for (int ks = 0; ks < K3_BK / 8; ++ks) {
                             const uint64_t off = (uint64_t)(ks * 32 >> 4);  // 8 fp32 = 32 bytes along K
-                            ptx::mma_tf32<CG>(d_tmem, a_lo + off, b_hi + off, idesc, (kc | ks) != 0);  // small terms first
-                            ptx::mma_tf32<CG>(d_tmem, a_hi + off, b_lo + off, idesc, 1u);
-                            ptx::mma_tf32<CG>(d_tmem, a_hi + off, b_hi + off, idesc, 1u);
+                            ptx::mma_tf32<CG>(d_corr, a_lo + off, b_hi + off, idesc, (kc | ks) != 0);  // small terms first
+                            ptx::mma_tf32<CG>(d_corr, a_hi + off, b_lo + off, idesc, 1u);
+                            ptx::mma_tf32<CG>(d_tmem, a_hi + off, b_hi + off, idesc, SEP ? (uint32_t)((kc | ks) != 0) : 1u);
                         }
                         ptx::mma_commit<CG>(&empty[stage]);            // smem slot free once these MMAs retire
                         if (kc == nkc - 1) ptx::mma_commit<CG>(&tfull[as]);  // accumulator complete
@@ -220,8 +270,8 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
                     __syncwarp();
                     if (++stage == NS) { stage = 0; phase ^= 1; }
                 }
-                as ^= 1;
-                if (as == 0) aphase ^= 1;
+                if (SEP) { aphase ^= 1; }
+                else { as ^= 1; if (as == 0) aphase ^= 1; }
             }
         }
     } else {
@@ -230,7 +280,7 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
         const int row = e * 32 + lane;          // query row inside the CTA's 128
         const int epi_tid = (warp - 2) * 32 + lane;
         u64* scr = scratch + (size_t)(warp - 2) * p.P;
-        int as = 0, ss = 0;
+        int as = 0, ss = 0, xb = 0;
         uint32_t aphase = 0, sph = 0;
         const float INF = __int_as_float(0x7f800000);
         for (;;) {
@@ -250,7 +300,8 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
             // filter threshold on s = ||x||^2 - 2 ip, widened by a few ulps so it never rejects a
             // candidate the exact test below would accept
             const float t_cmp = valid ? (tau_eff - qn) + 2e-6f * (fabsf(tau_eff) + qn) : -INF;
-            float* xn = xn_s + as * K3_BN;
+            float* xn = xn_s + xb * K3_BN;
+            xb ^= 1;
             for (int j = epi_tid; j < K3_BN; j += K3_EPI_THREADS) {
                 const int64_t r = t * K3_BN + j;
                 xn[j] = r < p.n ? p.norms[r] : INF;
@@ -261,25 +312,25 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
             ptx::tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(e * 32) << 16) + (uint32_t)(as * K3_BN);
             u64* list = p.cand + sidx * p.P;
+            // Two register buffers: the tcgen05.ld of the next 32 columns is in flight while this
+            // chunk is filtered.  Filtering is branch-free (one FFMA + one compare per element folded
+            // into a bit mask); the rare survivors are handled after the chunk.
+            uint32_t va[32], vb[32], wa[32], wb[32];
+            ptx::tmem_ld_32x32(taddr, va);
+            if (SEP) ptx::tmem_ld_32x32(taddr + K3_BN, wa);
+            const uint32_t row_base = (uint32_t)(t * K3_BN);
 #pragma unroll 1
-            for (int c0 = 0; c0 < K3_BN; c0 += 32) {
-                uint32_t v[32];
-                ptx::tmem_ld_32x32(taddr + c0, v);
+            for (int c0 = 0; c0 < K3_BN; c0 += 64) {
                 ptx::tmem_ld_wait();
-#pragma unroll
-                for (int c = 0; c < 32; ++c) {
-                    const float ip = __uint_as_float(v[c]);
-                    const float xv = xn[c0 + c];
-                    const float s = fmaf(-2.f, ip, xv);
-                    if (s <= t_cmp) {
-                        float dist = (qn + xv) - 2.f * ip;  // oracle rule (2), then clamp
-                        dist = dist < 0.f ? 0.f : dist;
-                        if (dist <= tau_eff) {
-                            const u64 key = make_key(dist, (uint32_t)(t * K3_BN + c0 + c));
-                            if (key < kth) { list[cnt] = key; ++cnt; }
-                        }
-                    }
+                ptx::tmem_ld_32x32(taddr + c0 + 32, vb);
+                if (SEP) ptx::tmem_ld_32x32(taddr + K3_BN + c0 + 32, wb);
+                k3_filter_chunk<SEP>(va, wa, xn + c0, t_cmp, qn, tau_eff, kth, row_base + c0, list, cnt);
+                ptx::tmem_ld_wait();
+                if (c0 + 64 < K3_BN) {
+                    ptx::tmem_ld_32x32(taddr + c0 + 64, va);
+                    if (SEP) ptx::tmem_ld_32x32(taddr + K3_BN + c0 + 64, wa);
                 }
+                k3_filter_chunk<SEP>(vb, wb, xn + c0 + 32, t_cmp, qn, tau_eff, kth, row_base + c0 + 32, list, cnt);
             }
             // accumulator drained: hand it back to the MMA warp (of the leader CTA)
             ptx::tc_fence_before();
@@ -318,8 +369,8 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
             p.cnt[sidx] = cnt;
             p.tau[sidx] = tau;
             p.kth[sidx] = kth;
-            as ^= 1;
-            if (as == 0) aphase ^= 1;
+            if (SEP) { aphase ^= 1; }
+            else { as ^= 1; if (as == 0) aphase ^= 1; }
         }
     }
 
@@ -424,6 +475,7 @@ struct K3State {
     EncodeTiledFn encode = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     bool timing = false;
+    int sep_mode = 0;  // 0 auto (d >= 512), 1 always, 2 never
     bool timed = false;
 };
 
@@ -501,6 +553,7 @@ void k3_invalidate_maps(K3State*) {}  // maps are re-encoded on every search (ho
 
 void k3_set_timing(K3State* s, bool on) { s->timing = on; }
 void k3_set_cta_group(K3State* s, int cg) { s->cg = cg == 2 ? 2 : 1; }
+void k3_set_sep_mode(K3State* s, int m) { s->sep_mode = m; }
 
 int k3_last_kernel_ms(K3State* s, float* ms) {
     if (!s->timed) return B2K_EINVAL;
@@ -524,11 +577,11 @@ static int make_map(K3State* s, CUtensorMap* m, const float* base, int64_t rows,
     return B2K_OK;
 }
 
-template <int CG, int NS>
+template <int CG, int NS, bool SEP>
 static int launch_k3(const CUtensorMap& mq, const CUtensorMap& mql, const CUtensorMap& mx, const CUtensorMap& mxl,
                      const K3Params& p, int ncta, cudaStream_t st) {
     size_t smem = K3Smem<CG, NS>::bytes(p.P);
-    B2K_CUDA(cudaFuncSetAttribute(k3_tf32x3_topk_kernel<CG, NS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    B2K_CUDA(cudaFuncSetAttribute(k3_tf32x3_topk_kernel<CG, NS, SEP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(ncta);
     cfg.blockDim = dim3(K3_THREADS);
@@ -541,16 +594,21 @@ static int launch_k3(const CUtensorMap& mq, const CUtensorMap& mql, const CUtens
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    B2K_CUDA(cudaLaunchKernelEx(&cfg, k3_tf32x3_topk_kernel<CG, NS>, mq, mql, mx, mxl, p));
+    B2K_CUDA(cudaLaunchKernelEx(&cfg, k3_tf32x3_topk_kernel<CG, NS, SEP>, mq, mql, mx, mxl, p));
     count_launch();
     return B2K_OK;
 }
 
-static int launch_k3_any(int cg, int P, const CUtensorMap& mq, const CUtensorMap& mql, const CUtensorMap& mx,
+static int launch_k3_any(int cg, int P, bool sep, const CUtensorMap& mq, const CUtensorMap& mql, const CUtensorMap& mx,
                          const CUtensorMap& mxl, const K3Params& p, int ncta, cudaStream_t st) {
-    if (cg == 1) return launch_k3<1, 2>(mq, mql, mx, mxl, p, ncta, st);
-    if (P <= 512) return launch_k3<2, 3>(mq, mql, mx, mxl, p, ncta, st);
-    return launch_k3<2, 2>(mq, mql, mx, mxl, p, ncta, st);
+    if (sep) {
+        if (cg == 1) return launch_k3<1, 2, true>(mq, mql, mx, mxl, p, ncta, st);
+        if (P <= 512) return launch_k3<2, 3, true>(mq, mql, mx, mxl, p, ncta, st);
+        return launch_k3<2, 2, true>(mq, mql, mx, mxl, p, ncta, st);
+    }
+    if (cg == 1) return launch_k3<1, 2, false>(mq, mql, mx, mxl, p, ncta, st);
+    if (P <= 512) return launch_k3<2, 3, false>(mq, mql, mx, mxl, p, ncta, st);
+    return launch_k3<2, 2, false>(mq, mql, mx, mxl, p, ncta, st);
 }
 
 int k3_search(K3State* s, const float* x, const float* xlo, const float* norms, int64_t n, int64_t capacity, int d,
@@ -570,6 +628,7 @@ int k3_search(K3State* s, const float* x, const float* xlo, const float* norms, 
     p.kth = reinterpret_cast<u64*>(scratch + L.off_kth);
     p.cand = reinterpret_cast<u64*>(scratch + L.off_cand);
     p.next_unit = reinterpret_cast<u64*>(scratch + L.off_next);
+    p.static_mode = 0;
 
     // queries: norms + TF32 residual rows (K1 reused), list state reset
     int rc = launch_row_prep(q, nq, d, const_cast<float*>(p.qn), qlo, st);
@@ -590,11 +649,13 @@ int k3_search(K3State* s, const float* x, const float* xlo, const float* norms, 
     // distance of that sample becomes the shared threshold -- an upper bound of the final k-th
     // distance, so the full pass prunes from its first tile instead of sorting its way down.
     const int nclusters = L.ncta / L.cg;
+    const bool sep = s->sep_mode == 1 || (s->sep_mode == 0 && d >= 512);
     if (ntiles >= 2 * (int64_t)nclusters && (int64_t)nclusters * K3_BN >= 2 * (int64_t)k) {
         K3Params pre = p;
+        pre.static_mode = 1;  // one tile per CTA (pair): every list gets at most 256 keys, no compaction
         pre.n = (int64_t)nclusters * K3_BN;
         pre.nunits = (int64_t)nclusters * L.nqb;
-        rc = launch_k3_any(L.cg, L.P, mq, mql, mx, mxl, pre, L.ncta, st);
+        rc = launch_k3_any(L.cg, L.P, sep, mq, mql, mx, mxl, pre, L.ncta, st);
         if (rc) return rc;
         k4_merge_kernel<<<(unsigned)nq, K4_THREADS, 0, st>>>(pre, L.cg, L.ncta, 1, nullptr, nullptr);
         k3_init_kernel<<<(unsigned)((nslots + 255) / 256), 256, 0, st>>>(nslots, p.cnt, p.tau, p.kth, nq, nullptr, p.next_unit);
@@ -603,7 +664,7 @@ int k3_search(K3State* s, const float* x, const float* xlo, const float* norms, 
     }
 
     if (s->timing) B2K_CUDA(cudaEventRecord(s->ev0, st));
-    rc = launch_k3_any(L.cg, L.P, mq, mql, mx, mxl, p, L.ncta, st);
+    rc = launch_k3_any(L.cg, L.P, sep, mq, mql, mx, mxl, p, L.ncta, st);
     if (rc) return rc;
     if (s->timing) { B2K_CUDA(cudaEventRecord(s->ev1, st)); s->timed = true; }
 
