@@ -1,0 +1,144 @@
+"""Row-sharded IndexFlatL2 across the GPUs of one node.
+
+One process per GPU (torchrun); every rank makes the same calls (SPMD).  Each rank keeps a
+contiguous slice of every `add` batch in its own `IndexFlatL2` (C ABI, one B200) and answers
+`search` with its shard-local top-k; the per-rank (D, I) are exchanged with ONE NCCL all-gather
+of a packed buffer and combined by the merge kernel (K5, `b2k_merge_topk`).  Ids are global row
+positions, exactly as a single index would number them, so `llm/rag.py`'s rule "row id == index
+into the metadata list" (rag.py:81, :119) still holds.
+
+The reference is single-process and has no counterpart of this file; the behaviour it must
+reproduce is that of one `faiss.IndexFlatL2` holding all rows (rag.py:61-86, :116).
+"""
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+
+def split_range(n, world, rank):
+    """Rows [lo, hi) of a batch of n rows kept by `rank`: contiguous blocks of ceil(n/world)."""
+    per = -(-n // world) if n else 0
+    lo = min(rank * per, n)
+    hi = min(lo + per, n)
+    return lo, hi
+
+
+class ShardedIndexFlatL2:
+    is_trained = True
+    metric_type = 1
+
+    def __init__(self, d, device=None, group=None, _local=None, _merge=None):
+        """`_local` / `_merge` replace the CUDA shard index and merge kernel; only the CPU (gloo)
+        tests of the host logic use them."""
+        self.group = group
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        self._d = int(d)
+        if _local is None:
+            from . import IndexFlatL2, default_device
+            self.device = default_device() if device is None else int(device)
+            self.local = IndexFlatL2(d, device=self.device)
+            self._tdev = torch.device("cuda", self.device)
+        else:
+            self.device = None
+            self.local = _local
+            self._tdev = torch.device("cpu")
+        self._merge = _merge
+        self._ntotal = 0
+        # segments of this rank's shard: local rows [ls, ls+cnt) are global rows [gs, gs+cnt)
+        self._seg_local = []
+        self._seg_global = []
+
+    # ---- faiss surface -------------------------------------------------------------------
+    @property
+    def d(self):
+        return self._d
+
+    @property
+    def ntotal(self):
+        return self._ntotal
+
+    def _note_segment(self, gstart, count):
+        if count <= 0:
+            return
+        lstart = self.local.ntotal - count
+        if self._seg_local and self._seg_global[-1] + (lstart - self._seg_local[-1]) == gstart:
+            return  # contiguous with the previous segment
+        self._seg_local.append(lstart)
+        self._seg_global.append(gstart)
+
+    def add(self, x):
+        """Every rank passes the same batch; rank r keeps rows split_range(n, world, r)."""
+        n = int(x.shape[0])
+        assert x.shape[1] == self._d, "add: dimension mismatch"
+        lo, hi = split_range(n, self.world, self.rank)
+        if hi > lo:
+            self.local.add(x[lo:hi])
+            self._note_segment(self._ntotal + lo, hi - lo)
+        self._ntotal += n
+
+    def add_synthetic_global(self, n, seed):
+        """Benchmark helper: global rows [ntotal, ntotal+n) of the synthetic stream, each rank
+        generating only its own slice on its own GPU (100M x 768 never exists in one place)."""
+        lo, hi = split_range(n, self.world, self.rank)
+        if hi > lo:
+            self.local.reserve(self.local.ntotal + hi - lo)
+            self.local.add_synthetic(hi - lo, seed, self._ntotal + lo)
+            self._note_segment(self._ntotal + lo, hi - lo)
+        self._ntotal += n
+
+    def reset(self):
+        self.local.reset()
+        self._ntotal = 0
+        self._seg_local, self._seg_global = [], []
+
+    def set_option(self, key, value):
+        self.local.set_option(key, value)
+
+    def stats(self):
+        return self.local.stats()
+
+    def _to_global(self, I):
+        """Shard-local row ids -> global ids (-1 stays -1)."""
+        if not self._seg_local:
+            return I
+        if len(self._seg_local) == 1:
+            return torch.where(I >= 0, I + (self._seg_global[0] - self._seg_local[0]), I)
+        ls = torch.tensor(self._seg_local, dtype=torch.int64, device=I.device)
+        delta = torch.tensor([g - l for g, l in zip(self._seg_global, self._seg_local)], dtype=torch.int64,
+                             device=I.device)
+        seg = torch.searchsorted(ls, I.clamp(min=0), right=True) - 1
+        return torch.where(I >= 0, I + delta[seg], I)
+
+    def search(self, x, k):
+        """(D, I) of the k nearest rows over ALL shards; identical on every rank."""
+        k = int(k)
+        assert k > 0, "search: k must be positive"
+        as_numpy = not torch.is_tensor(x)
+        xq = torch.as_tensor(np.ascontiguousarray(x, dtype=np.float32)) if as_numpy else x
+        xq = xq.to(self._tdev, torch.float32).contiguous()
+        assert xq.dim() == 2 and xq.shape[1] == self._d, "search: dimension mismatch"
+        nq = xq.shape[0]
+        nk = nq * k
+        # packed send buffer: nk int64 ids followed by nk float32 distances (8-byte aligned)
+        words = nk + (nk + 1) // 2
+        send = torch.empty(words, dtype=torch.int64, device=self._tdev)
+        I_loc = send[:nk].view(nq, k)
+        D_loc = send[nk:].view(torch.float32)[:nk].view(nq, k)
+        D, I = self.local.search(xq, k)
+        D_loc.copy_(torch.as_tensor(D))
+        I_loc.copy_(self._to_global(torch.as_tensor(I).to(self._tdev)))
+        recv = torch.empty(self.world * words, dtype=torch.int64, device=self._tdev)
+        dist.all_gather_into_tensor(recv, send, group=self.group)     # the one collective of the path
+        recv = recv.view(self.world, words)
+        Icat = recv[:, :nk].reshape(self.world, nq, k)
+        Dcat = recv[:, nk:].contiguous().view(torch.float32)[:, :nk].reshape(self.world, nq, k)
+        if self._merge is not None:
+            Dm, Im = self._merge(Dcat, Icat)
+        else:
+            from . import merge_topk
+            Dm, Im = merge_topk(Dcat, Icat)
+        if as_numpy:
+            return torch.as_tensor(Dm).cpu().numpy(), torch.as_tensor(Im).cpu().numpy()
+        return Dm, Im

@@ -62,7 +62,9 @@ struct K3Params {
     u64* kth;           // [ncta][qpc]
     u64* cand;          // [ncta][qpc][P]
     u64* next_unit;     // dynamic scheduler: next unit to hand out
-    int static_mode;    // 1: CTA (pair) c takes exactly the nqb units of tile c (warm-start pass)
+    int static_mode;    // 1: warm-start pass, CTA (pair) c takes tiles static_tile0 + c*static_tpc + [0,static_tpc), all query blocks
+    int static_tpc;
+    int64_t static_tile0;
 };
 
 static constexpr int K3_NSCHED = 4;  // depth of the unit-id ring between the scheduler and the other roles
@@ -192,7 +194,9 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
                     // moment work on neighbouring database tiles and share them through L2
                     ptx::mbar_wait(&sempty[ss], sph ^ 1);
                     if (p.static_mode) {
-                        u = static_i < p.nqb ? (long long)(blockIdx.x / CG) * p.nqb + static_i : -1;
+                        u = static_i < p.nqb * p.static_tpc
+                                ? (p.static_tile0 + (long long)(blockIdx.x / CG) * p.static_tpc) * p.nqb + static_i
+                                : -1;
                         ++static_i;
                     } else {
                         u = (long long)atomicAdd(p.next_unit, 1ull);
@@ -402,7 +406,7 @@ k4_merge_kernel(const K3Params p, int cg, int ncta, int threshold_only, float* _
     __shared__ u64 buf[K4_P];
     __shared__ int s_cnt;
     __shared__ u64 s_kth;
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t qi = blockIdx.x;
     const int bq = K3_BM * cg;
     const int qb = (int)(qi / bq);
@@ -411,35 +415,82 @@ k4_merge_kernel(const K3Params p, int cg, int ncta, int threshold_only, float* _
     const float bound = __uint_as_float(p.gts[qi]);
     if (tid == 0) { s_cnt = 0; s_kth = KEY_EMPTY; }
     __syncthreads();
-    for (int cta = r; cta < ncta; cta += cg) {
-        const int64_t sidx = (int64_t)cta * p.qpc + (int64_t)qb * K3_BM + row;
-        const int c = p.cnt[sidx];
-        const u64* lst = p.cand + sidx * p.P;
-        for (int i0 = 0; i0 < c; i0 += K4_THREADS) {
-            int flag = 0;
-            const int i = i0 + tid;
-            if (i < c) {
-                const u64 key = lst[i];
-                if (key_dist(key) <= bound && key < s_kth) {
-                    int pos = atomicAdd(&s_cnt, 1);
-                    buf[pos] = key;
-                    if (pos + 1 > K4_P - K4_THREADS) flag = 1;
+    // Every warp walks its share of the lists and gathers the keys under the shared bound.  If
+    // they do not fit the buffer, the k-th smallest of the subset that did fit is a tighter bound
+    // (still an upper bound of the final k-th key) and the lists are gathered once more under it.
+    u64 kbound = ((u64)__float_as_uint(bound) << 32) | 0xffffffffull;
+    for (int pass = 0; pass < 2; ++pass) {
+        // four lists per warp at a time: their counts, then their keys, are independent loads
+        constexpr int LB = 4;
+        const int wstride = (K4_THREADS / 32) * LB * cg;
+        for (int cta0 = r + warp * LB * cg; cta0 < ncta; cta0 += wstride) {
+            int c[LB];
+            const u64* lst[LB];
+            int cmax = 0;
+#pragma unroll
+            for (int j = 0; j < LB; ++j) {
+                const int cta = cta0 + j * cg;
+                const int64_t sidx = (int64_t)(cta < ncta ? cta : r) * p.qpc + (int64_t)qb * K3_BM + row;
+                c[j] = cta < ncta ? p.cnt[sidx] : 0;
+                lst[j] = p.cand + sidx * p.P;
+            }
+#pragma unroll
+            for (int j = 0; j < LB; ++j) cmax = c[j] > cmax ? c[j] : cmax;
+            for (int i = lane; i < cmax; i += 32) {
+                u64 key[LB];
+#pragma unroll
+                for (int j = 0; j < LB; ++j) key[j] = i < c[j] ? lst[j][i] : KEY_EMPTY;
+#pragma unroll
+                for (int j = 0; j < LB; ++j) {
+                    if (key[j] <= kbound) {  // KEY_EMPTY (all ones) is above any bound
+                        const int pos = atomicAdd(&s_cnt, 1);
+                        if (pos < K4_P) buf[pos] = key[j];
+                    }
                 }
             }
-            if (__syncthreads_or(flag)) {
-                // sort, keep k (same routine as the scan kernel's compaction, inlined for static smem)
-                const int cc = s_cnt;
-                int Ps = 2;
-                while (Ps < cc) Ps <<= 1;
-                for (int j = cc + tid; j < Ps; j += K4_THREADS) buf[j] = KEY_EMPTY;
-                __syncthreads();
-                block_bitonic_sort(buf, Ps);
-                if (tid == 0) { s_cnt = cc < p.k ? cc : p.k; if (cc >= p.k) s_kth = buf[p.k - 1]; }
-                __syncthreads();
+        }
+        __syncthreads();
+        if (s_cnt <= K4_P || pass == 1) break;
+        block_bitonic_sort(buf, K4_P);
+        kbound = buf[p.k - 1];
+        __syncthreads();
+        if (tid == 0) s_cnt = 0;
+        __syncthreads();
+    }
+    if (s_cnt > K4_P) {
+        // slow path (bound too loose for the buffer): stream the lists, compacting as needed
+        __syncthreads();
+        if (tid == 0) { s_cnt = 0; s_kth = KEY_EMPTY; }
+        __syncthreads();
+        for (int cta = r; cta < ncta; cta += cg) {
+            const int64_t sidx = (int64_t)cta * p.qpc + (int64_t)qb * K3_BM + row;
+            const int c = p.cnt[sidx];
+            const u64* lst = p.cand + sidx * p.P;
+            for (int i0 = 0; i0 < c; i0 += K4_THREADS) {
+                int flag = 0;
+                const int i = i0 + tid;
+                if (i < c) {
+                    const u64 key = lst[i];
+                    if (key_dist(key) <= bound && key < s_kth) {
+                        int pos = atomicAdd(&s_cnt, 1);
+                        buf[pos] = key;
+                        if (pos + 1 > K4_P - K4_THREADS) flag = 1;
+                    }
+                }
+                if (__syncthreads_or(flag)) {
+                    const int cc = s_cnt;
+                    int Ps = 2;
+                    while (Ps < cc) Ps <<= 1;
+                    for (int j = cc + tid; j < Ps; j += K4_THREADS) buf[j] = KEY_EMPTY;
+                    __syncthreads();
+                    block_bitonic_sort(buf, Ps);
+                    if (tid == 0) { s_cnt = cc < p.k ? cc : p.k; if (cc >= p.k) s_kth = buf[p.k - 1]; }
+                    __syncthreads();
+                }
             }
         }
+        __syncthreads();
     }
-    __syncthreads();
     const int cc = s_cnt;
     int Ps = 2;
     while (Ps < cc) Ps <<= 1;
@@ -448,7 +499,7 @@ k4_merge_kernel(const K3Params p, int cg, int ncta, int threshold_only, float* _
     block_bitonic_sort(buf, Ps);
     if (threshold_only) {
         // warm start: the k-th smallest distance over a sample of the rows bounds the final one
-        if (tid == 0 && cc >= p.k) p.gts[qi] = (unsigned int)(buf[p.k - 1] >> 32);
+        if (tid == 0 && cc >= p.k) atomicMin(p.gts + qi, (unsigned int)(buf[p.k - 1] >> 32));
         return;
     }
     for (int j = tid; j < p.k; j += K4_THREADS) {
@@ -629,6 +680,8 @@ int k3_search(K3State* s, const float* x, const float* xlo, const float* norms, 
     p.cand = reinterpret_cast<u64*>(scratch + L.off_cand);
     p.next_unit = reinterpret_cast<u64*>(scratch + L.off_next);
     p.static_mode = 0;
+    p.static_tpc = 1;
+    p.static_tile0 = 0;
 
     // queries: norms + TF32 residual rows (K1 reused), list state reset
     int rc = launch_row_prep(q, nq, d, const_cast<float*>(p.qn), qlo, st);
@@ -645,22 +698,42 @@ int k3_search(K3State* s, const float* x, const float* xlo, const float* norms, 
     if ((rc = make_map(s, &mx, x, n, d, K3_BN / L.cg))) return rc;
     if ((rc = make_map(s, &mxl, xlo, n, d, K3_BN / L.cg))) return rc;
 
-    // Warm start: one tile per CTA (pair) with open thresholds, then per query the k-th smallest
-    // distance of that sample becomes the shared threshold -- an upper bound of the final k-th
-    // distance, so the full pass prunes from its first tile instead of sorting its way down.
+    // Warm start.  Round A: one tile per CTA (pair) with open thresholds; per query the k-th
+    // smallest distance of that sample becomes the shared threshold (an upper bound of the final
+    // k-th distance).  Round B: a few more tiles per CTA under that threshold (few survivors), and
+    // the threshold is tightened again.  The full pass then prunes from its first tile: its lists
+    // stay far below capacity (no compaction sorts) and K4 has little to merge.
     const int nclusters = L.ncta / L.cg;
     const bool sep = s->sep_mode == 1 || (s->sep_mode == 0 && d >= 512);
     if (ntiles >= 2 * (int64_t)nclusters && (int64_t)nclusters * K3_BN >= 2 * (int64_t)k) {
         K3Params pre = p;
-        pre.static_mode = 1;  // one tile per CTA (pair): every list gets at most 256 keys, no compaction
-        pre.n = (int64_t)nclusters * K3_BN;
+        pre.static_mode = 1;
+        pre.static_tpc = 1;
+        pre.static_tile0 = 0;
         pre.nunits = (int64_t)nclusters * L.nqb;
+        pre.n = (int64_t)nclusters * K3_BN;
         rc = launch_k3_any(L.cg, L.P, sep, mq, mql, mx, mxl, pre, L.ncta, st);
         if (rc) return rc;
         k4_merge_kernel<<<(unsigned)nq, K4_THREADS, 0, st>>>(pre, L.cg, L.ncta, 1, nullptr, nullptr);
         k3_init_kernel<<<(unsigned)((nslots + 255) / 256), 256, 0, st>>>(nslots, p.cnt, p.tau, p.kth, nq, nullptr, p.next_unit);
         count_launch(2);
         B2K_CUDA(cudaGetLastError());
+        // rows the second round should cover so that the full pass leaves ~<= 64 keys per list
+        const double want_rows = (double)n * k / ((double)nclusters * 64.0);
+        int tpc = (int)(want_rows / ((double)nclusters * K3_BN) + 0.999);
+        if (tpc > 16) tpc = 16;
+        if (tpc >= 2 && ntiles >= (int64_t)(tpc + 1) * nclusters * 2) {
+            pre.static_tpc = tpc;
+            pre.static_tile0 = nclusters;
+            pre.n = (int64_t)nclusters * (tpc + 1) * K3_BN;
+            pre.nunits = (int64_t)nclusters * (tpc + 1) * L.nqb;
+            rc = launch_k3_any(L.cg, L.P, sep, mq, mql, mx, mxl, pre, L.ncta, st);
+            if (rc) return rc;
+            k4_merge_kernel<<<(unsigned)nq, K4_THREADS, 0, st>>>(pre, L.cg, L.ncta, 1, nullptr, nullptr);
+            k3_init_kernel<<<(unsigned)((nslots + 255) / 256), 256, 0, st>>>(nslots, p.cnt, p.tau, p.kth, nq, nullptr, p.next_unit);
+            count_launch(2);
+            B2K_CUDA(cudaGetLastError());
+        }
     }
 
     if (s->timing) B2K_CUDA(cudaEventRecord(s->ev0, st));

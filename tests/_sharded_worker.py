@@ -1,0 +1,91 @@
+"""Worker for test_sharded_gloo.py: run under torch.distributed.run with the gloo backend (CPU).
+
+The CUDA shard index and merge kernel are replaced by oracle-backed stand-ins so that the HOST
+logic of ShardedIndexFlatL2 (row split, id remapping across several adds, the packed all-gather,
+SPMD result equality) is exercised without a GPU.  The product path never takes these stand-ins."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "rag-llm-k8s_b200"))
+from oracle import oracle as O  # noqa: E402
+from b200knn.sharded import ShardedIndexFlatL2, split_range  # noqa: E402
+
+
+class OracleShard:
+    def __init__(self, d):
+        self.x = np.zeros((0, d), np.float32)
+
+    @property
+    def ntotal(self):
+        return self.x.shape[0]
+
+    def add(self, x):
+        self.x = np.concatenate([self.x, np.asarray(x, np.float32)], 0)
+
+    def reserve(self, n):
+        pass
+
+    def add_synthetic(self, n, seed, first_row=0):
+        self.add(O.synth(seed, first_row, n, self.x.shape[1]))
+
+    def reset(self):
+        self.x = self.x[:0]
+
+    def search(self, xq, k):
+        D, I = O.search(self.x, np.asarray(xq, np.float32), k)
+        return torch.from_numpy(D), torch.from_numpy(I)
+
+
+def oracle_merge(Dcat, Icat):
+    D, I = O.merge(Dcat.numpy(), Icat.numpy())
+    return torch.from_numpy(D), torch.from_numpy(I)
+
+
+def main():
+    dist.init_process_group("gloo")
+    rank, world = dist.get_rank(), dist.get_world_size()
+    d = 24
+    idx = ShardedIndexFlatL2(d, _local=OracleShard(d), _merge=oracle_merge)
+    x = O.synth(11, 0, 1003, d)
+    # several adds of awkward sizes (including fewer rows than ranks) -> several id segments per rank
+    cuts = [0, 1, 2, 400, 401, 1003]
+    for a, b in zip(cuts[:-1], cuts[1:]):
+        idx.add(x[a:b])
+    assert idx.ntotal == 1003
+    counts = [torch.zeros(1, dtype=torch.int64) for _ in range(world)]
+    dist.all_gather(counts, torch.tensor([idx.local.ntotal]))
+    assert sum(int(c) for c in counts) == 1003
+    for nq, k in ((1, 5), (7, 10), (25, 3), (2, 1003 + 5)):
+        q = O.synth(12, 0, nq, d)
+        D, I = idx.search(q, k)
+        Dr, Ir = O.search(x, q, k)
+        assert np.array_equal(I, Ir), (rank, nq, k, I[0, :8], Ir[0, :8])
+        assert np.array_equal(D, Dr), (rank, nq, k)
+    # the benchmark's way of filling the shards
+    idx.reset()
+    idx.add_synthetic_global(777, 5)
+    idx.add_synthetic_global(100, 5)          # second call continues the id space, not the stream
+    xa = np.concatenate([O.synth(5, 0, 777, d), O.synth(5, 777, 100, d)], 0)
+    q = O.synth(13, 0, 3, d)
+    D, I = idx.search(q, 9)
+    Dr, Ir = O.search(xa, q, 9)
+    assert np.array_equal(I, Ir) and np.array_equal(D, Dr)
+    # empty index pads
+    idx.reset()
+    D, I = idx.search(q, 4)
+    assert np.all(I == -1) and np.all(D == O.FLT_MAX)
+    assert split_range(10, 4, 3) == (9, 10) and split_range(2, 4, 3) == (2, 2)
+    dist.barrier()
+    if rank == 0:
+        print("SHARDED-OK world=%d" % world)
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
