@@ -103,6 +103,26 @@ B2K_API int b2k_merge_topk(int device, int nlists, int64_t nq, int64_t k, const 
                    const int64_t* Iin, const int64_t* id_offset, float* D, int64_t* I,
                    int on_device, void* stream);
 
+/* Search without allocating anything.  No counterpart in the reference (llm/rag.py never
+ * manages device memory); it exists for callers that cannot call cudaMalloc -- a process
+ * whose inference engine has already reserved HBM, or a latency-critical thread that must
+ * avoid the device-wide synchronisation of cudaMalloc/cudaFree.  The caller owns everything:
+ * x_dev (n x d float32 rows), q_dev (nq x d), D_dev (nq x k float32), I_dev (nq x k int64),
+ * all device pointers on `device`; work is enqueued on `stream`.  Same results as b2k_search
+ * on the scan path (direct differences, any nq).  The kernel's scratch (per-CTA partial
+ * lists + a ticket) is a fixed B2K_NOALLOC_SCRATCH_BYTES array inside the library, held by
+ * every GPU that loads it until the process exits.  Limits: k <= B2K_MAX_K and
+ * (3 * SM count) * k keys must fit the array -- true for every k <= 1024 on a B200; anything
+ * larger is refused with B2K_ELIMIT.  All calls on a device share that one array, which keeps
+ * the previous call's contents: calls ordered on the GPU are independent (the ticket is
+ * cleared on `stream` before each launch, the lists are rewritten), calls that overlap on the
+ * GPU race.  The first call on each device resolves the array's address
+ * (cudaGetSymbolAddress): make it at start-up, before any stream capture. */
+#define B2K_NOALLOC_SCRATCH_BYTES (4u << 20)
+B2K_API int b2k_search_rows_noalloc(int device, const float* x_dev, int64_t n, int d,
+                                    const float* q_dev, int64_t nq, int64_t k, float* D_dev,
+                                    int64_t* I_dev, void* stream);
+
 /* Tuning / test hooks.  Keys: "path" (0 auto, 1 force the scan kernel, 2 force the
  * tensor-core kernel), "scan_ctas_per_sm", "timing" (0/1), "tensor_cta_group" (1 or 2),
  * "tensor_sep_accum" (0 auto, 1 on, 2 off).  Unknown key -> B2K_EINVAL. */

@@ -34,6 +34,8 @@ SIGNATURES = {
     "b2k_add_synthetic": (C.c_int, [C.c_void_p, C.c_int64, C.c_uint64, C.c_int64]),
     "b2k_merge_topk": (C.c_int, [C.c_int, C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
                                  C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
+    "b2k_search_rows_noalloc": (C.c_int, [C.c_int, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_int64, C.c_int64,
+                                          C.c_void_p, C.c_void_p, C.c_void_p]),
     "b2k_set_option": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int64]),
     "b2k_get_stat": (C.c_int, [C.c_void_p, C.c_char_p, C.POINTER(C.c_double)]),
     "b2k_launch_count": (C.c_int64, []),
