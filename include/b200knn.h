@@ -130,7 +130,9 @@ B2K_API int b2k_set_option(b2k_index* h, const char* key, int64_t value);
 
 /* Read-back of measurements / state.  Keys: "last_path" (1 = scan kernel, 2 = tensor-core
  * kernel served the last search), "tensor_kernel_ms" (CUDA-event duration of the last
- * tensor-core main kernel; needs option "timing" = 1; synchronises on that kernel). */
+ * tensor-core main kernel; needs option "timing" = 1; synchronises on that kernel),
+ * "scan_kernel_ms" / "scan_launches" (the same for the scan kernel launches of the last
+ * scan-path search). */
 B2K_API int b2k_get_stat(b2k_index* h, const char* key, double* out);
 
 /* Number of kernels this library has launched in this process (bench `gpu_launches`). */

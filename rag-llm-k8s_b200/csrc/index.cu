@@ -64,6 +64,9 @@ struct b2k_index {
     K3State* k3 = nullptr;
     // cross-stream ordering: rows written (add) -> later searches; workspace users -> next user
     cudaEvent_t ev_rows = nullptr, ev_ws = nullptr;
+    cudaEvent_t ev_t0 = nullptr, ev_t1 = nullptr;  // option timing: around the scan launches
+    int scan_launches = 0;
+    bool scan_timed = false;
 };
 
 static constexpr int64_t MAX_ROWS = 0xFFFFFFFEll;  // row index lives in the low 32 bits of a key
@@ -180,13 +183,20 @@ int scan_search(b2k_index* h, int64_t nq, const float* qd, int k, float* Dd, int
                 cudaStream_t st) {
     const int grid = scan_grid(h->ntotal, h->sm_count, h->opt_scan_ctas_per_sm);
     u64* partial = reinterpret_cast<u64*>(ws_tail);
+    if (h->opt_timing) {
+        if (!h->ev_t0) { B2K_CUDA(cudaEventCreate(&h->ev_t0)); B2K_CUDA(cudaEventCreate(&h->ev_t1)); }
+        B2K_CUDA(cudaEventRecord(h->ev_t0, st));
+    }
+    h->scan_launches = 0;
     for (int64_t q0 = 0; q0 < nq;) {
         int qt = scan_pick_qt(nq - q0, k);
         int rc = launch_scan(h->x, qd + q0 * (int64_t)h->d, h->ntotal, h->d, qt, k, grid, partial, h->done,
                              Dd + q0 * k, Id + q0 * k, st);
         if (rc) return rc;
         q0 += qt;
+        ++h->scan_launches;
     }
+    if (h->opt_timing) { B2K_CUDA(cudaEventRecord(h->ev_t1, st)); h->scan_timed = true; }
     return B2K_OK;
 }
 
@@ -238,6 +248,8 @@ int b2k_destroy(b2k_index* h) {
     if (h->pin) cudaFreeHost(h->pin);
     if (h->ev_rows) cudaEventDestroy(h->ev_rows);
     if (h->ev_ws) cudaEventDestroy(h->ev_ws);
+    if (h->ev_t0) cudaEventDestroy(h->ev_t0);
+    if (h->ev_t1) cudaEventDestroy(h->ev_t1);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
     return B2K_OK;
@@ -280,6 +292,16 @@ int b2k_get_stat(b2k_index* h, const char* key, double* out) {
     if (!strcmp(key, "tensor_kernel_ms")) {
         float ms = 0.f;
         if (!h->k3 || k3_last_kernel_ms(h->k3, &ms)) { set_error("no timed tensor-core kernel yet (set option timing=1)"); return B2K_EINVAL; }
+        *out = ms;
+        return B2K_OK;
+    }
+    if (!strcmp(key, "scan_kernel_ms") || !strcmp(key, "scan_launches")) {
+        if (!h->scan_timed) { set_error("no timed scan yet (set option timing=1)"); return B2K_EINVAL; }
+        if (!strcmp(key, "scan_launches")) { *out = h->scan_launches; return B2K_OK; }
+        DeviceGuard g(h->device);
+        float ms = 0.f;
+        B2K_CUDA(cudaEventSynchronize(h->ev_t1));
+        B2K_CUDA(cudaEventElapsedTime(&ms, h->ev_t0, h->ev_t1));
         *out = ms;
         return B2K_OK;
     }

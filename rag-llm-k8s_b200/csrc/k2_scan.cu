@@ -262,16 +262,28 @@ scan_l2_topk_kernel(const float* __restrict__ X, const float* __restrict__ Q, in
         if (tid == 0) { s.cnt[0] = 0; s.kth[0] = KEY_EMPTY; s.tau[0] = FLT_MAX; }
         __syncthreads();
 
-        for (int64_t b0 = 0; b0 < total; b0 += SCAN_THREADS) {
-            int64_t idx = b0 + tid;
+        // eight keys per thread per round: the loads are independent, so a round costs one L2
+        // round trip instead of eight; at most 2048 keys can be appended between two checks
+        constexpr int KPT = 8;
+        for (int64_t b0 = 0; b0 < total; b0 += (int64_t)SCAN_THREADS * KPT) {
+            u64 keys[KPT];
+#pragma unroll
+            for (int j = 0; j < KPT; ++j) {
+                const int64_t idx = b0 + (int64_t)j * SCAN_THREADS + tid;
+                keys[j] = KEY_EMPTY;
+                if (idx < total) {
+                    const int b = (int)(idx / k), jj = (int)(idx - (int64_t)b * k);
+                    keys[j] = ((const volatile u64*)partial)[((int64_t)b * QT + q) * k + jj];
+                }
+            }
             int flag = 0;
-            if (idx < total) {
-                int b = (int)(idx / k), j = (int)(idx - (int64_t)b * k);
-                u64 key = ((const volatile u64*)partial)[((int64_t)b * QT + q) * k + j];
-                if (key != KEY_EMPTY && key <= bound && key < s.kth[0]) {
+            const u64 kth_now = s.kth[0];
+#pragma unroll
+            for (int j = 0; j < KPT; ++j) {
+                if (keys[j] != KEY_EMPTY && keys[j] <= bound && keys[j] < kth_now) {
                     int pos = atomicAdd(&s.cnt[0], 1);
-                    s.buf[pos] = key;
-                    if (pos + 1 > SCAN_FINAL_P - SCAN_THREADS) flag = 1;
+                    s.buf[pos] = keys[j];
+                    if (pos + 1 > SCAN_FINAL_P - SCAN_THREADS * KPT) flag = 1;
                 }
             }
             if (__syncthreads_or(flag)) compact(s.buf, SCAN_FINAL_P, &s.cnt[0], &s.kth[0], &s.tau[0], k);

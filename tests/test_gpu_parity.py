@@ -292,3 +292,91 @@ def test_one_million_rows_nq1_k10(faiss):
     Dm, Im = faiss.merge_topk(np.stack([h[0] for h in halves]), np.stack([h[1] for h in halves]),
                               id_offset=np.array([0, 500_000]))
     assert np.array_equal(Im, I) and np.array_equal(Dm, D)
+
+
+@pytest.mark.parametrize("cg,sep,k", [(1, 2, 10), (1, 1, 10), (2, 2, 100), (2, 1, 100), (2, 2, 700), (2, 1, 1024)])
+def test_tensor_kernel_variants(faiss, cg, sep, k):
+    """Every instantiation of the tcgen05 kernel (one CTA / CTA pair, shared / separate cross-term
+    accumulator, 3-stage / 2-stage ring for long lists) against the oracle's expansion numerics,
+    on N(0,1) rows and on unit-norm rows with planted duplicates (the rag.py distribution)."""
+    rng = np.random.default_rng(cg * 10 + sep)
+    for unit in (False, True):
+        x = O.synth(31, 0, 40000, 256)
+        q = O.synth(32, 0, 70, 256)
+        if unit:
+            x, q = unit_rows(x), unit_rows(q)
+            q[:8] = x[rng.integers(0, 40000, 8)]          # self matches: true distance 0
+        idx = _build(faiss, x)
+        idx.set_option("path", 2)
+        idx.set_option("tensor_cta_group", cg)
+        idx.set_option("tensor_sep_accum", sep)
+        D, I = idx.search(q, k)
+        assert idx.stats()["path"] == "tensor"
+        assert np.all(D >= 0.0)
+        assert_knn_matches(D, I, x, q, k, expanded=True, what="cg=%d sep=%d k=%d unit=%s" % (cg, sep, k, unit))
+
+
+def test_full_size_c3_properties(faiss):
+    """BASELINE.json configs[2] at full size (10M x 384, nq=1024, k=100), checked through
+    size-independent properties: (a) rows sorted, ids unique and in range; (b) searching the two
+    halves separately and merging gives the same answer; (c) for a few queries the exact scan
+    kernel (direct differences, path=1) returns the same neighbours within tolerance; (d) the
+    reported distances match float64 distances recomputed on the CPU for the returned ids."""
+    import torch
+    N, d, nq, k = 10_000_000, 384, 1024, 100
+    idx = faiss.IndexFlatL2(d)
+    idx.reserve(N)
+    idx.add_synthetic(N, 1234, 0)
+    q = faiss.synth(5678, 0, nq, d)
+    D, I = idx.search(q, k)
+    assert idx.stats()["path"] == "tensor"
+    Dh, Ih = D.cpu().numpy(), I.cpu().numpy()
+    assert np.all(np.diff(Dh, axis=1) >= 0) and Ih.min() >= 0 and Ih.max() < N
+    assert all(len(set(r.tolist())) == k for r in Ih[::64])
+    # (b) halves + merge
+    parts = []
+    for a in (0, N // 2):
+        h = faiss.IndexFlatL2(d)
+        h.reserve(N // 2)
+        h.add_synthetic(N // 2, 1234, a)
+        parts.append(h.search(q, k))
+        del h
+    Dm, Im = faiss.merge_topk(torch.stack([p[0] for p in parts]), torch.stack([p[1] for p in parts]),
+                              id_offset=np.array([0, N // 2]))
+    assert torch.equal(Im, I) and torch.equal(Dm, D)
+    # (c) exact scan on a few queries
+    idx.set_option("path", 1)
+    sel = [0, 17, 513, 1023]
+    Ds, Is = idx.search(q[sel].contiguous(), k)
+    Ds, Is = Ds.cpu().numpy(), Is.cpu().numpy()
+    qh = q.cpu().numpy()
+    for j, qi in enumerate(sel):
+        assert np.allclose(Dh[qi], Ds[j], rtol=RTOL)
+        differ = Ih[qi] != Is[j]
+        if differ.any():       # only near-ties may swap
+            assert np.allclose(Dh[qi][differ], Ds[j][differ], rtol=2 * RTOL)
+            assert len(set(Ih[qi]) ^ set(Is[j])) <= 2
+        # (d) float64 recomputation for the returned ids
+        rows = np.stack([O.synth(1234, int(r), 1, d)[0] for r in Ih[qi]])
+        d64 = ((rows.astype(np.float64) - qh[qi].astype(np.float64)) ** 2).sum(1)
+        mag = (rows.astype(np.float64) ** 2).sum(1) + (qh[qi].astype(np.float64) ** 2).sum()
+        assert np.all(np.abs(d64 - Dh[qi]) <= RTOL * np.maximum(d64, mag))
+
+
+def test_large_k_large_batch_stress(faiss):
+    """The shape of BASELINE.json configs[4] (d=1024, nq=4096, k=1024) at 300k rows: against the
+    exact scan kernel on a sample of queries, plus the halves-merge property."""
+    import torch
+    N, d, nq, k = 300_000, 1024, 4096, 1024
+    idx = faiss.IndexFlatL2(d)
+    idx.add_synthetic(N, 1234, 0)
+    q = faiss.synth(5678, 0, nq, d)
+    D, I = idx.search(q, k)
+    assert idx.stats()["path"] == "tensor"
+    idx.set_option("path", 1)
+    sel = [0, 1000, 4095]
+    Ds, Is = idx.search(q[sel].contiguous(), k)
+    for j, qi in enumerate(sel):
+        a, b = D[qi].cpu().numpy(), Ds[j].cpu().numpy()
+        assert np.allclose(a, b, rtol=RTOL, atol=RTOL * 2048)
+        assert len(set(I[qi].cpu().tolist()) ^ set(Is[j].cpu().tolist())) <= 4
