@@ -84,7 +84,15 @@ struct DeviceGuard {
     ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
 };
 
+// Validated devices are cached: cudaGetDeviceProperties costs about a millisecond, far too much
+// for per-call use (the merge entry point is on the sharded search's critical path).
 int check_device(int device, int* sm_count) {
+    static std::mutex mu;
+    static int cached_sm[64] = {0};
+    if (device >= 0 && device < 64) {
+        std::lock_guard<std::mutex> lk(mu);
+        if (cached_sm[device] > 0) { if (sm_count) *sm_count = cached_sm[device]; return B2K_OK; }
+    }
     int count = 0;
     cudaError_t e = cudaGetDeviceCount(&count);
     if (e != cudaSuccess || count == 0) {
@@ -96,13 +104,16 @@ int check_device(int device, int* sm_count) {
         set_error("device %d out of range (0..%d)", device, count - 1);
         return B2K_EINVAL;
     }
-    cudaDeviceProp prop;
-    B2K_CUDA(cudaGetDeviceProperties(&prop, device));
-    if (prop.major != 10) {
-        set_error("device %d is sm_%d%d; libb200knn is built for sm_100a (B200) only", device, prop.major, prop.minor);
+    int major = 0, minor = 0, sms = 0;
+    B2K_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device));
+    B2K_CUDA(cudaDeviceGetAttribute(&minor, cudaDevAttrComputeCapabilityMinor, device));
+    B2K_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    if (major != 10) {
+        set_error("device %d is sm_%d%d; libb200knn is built for sm_100a (B200) only", device, major, minor);
         return B2K_ECUDA;
     }
-    if (sm_count) *sm_count = prop.multiProcessorCount;
+    if (device < 64) { std::lock_guard<std::mutex> lk(mu); cached_sm[device] = sms; }
+    if (sm_count) *sm_count = sms;
     return B2K_OK;
 }
 

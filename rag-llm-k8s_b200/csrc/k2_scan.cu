@@ -344,6 +344,12 @@ static int launch_scan_t(const float* X, const float* Q, int64_t n, int d, int k
     if (smem > 48 * 1024)  // per-device attribute: set on every large launch (a handle may live on any GPU)
         B2K_CUDA(cudaFuncSetAttribute(scan_l2_topk_kernel<QT, VEC>,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    // one wave: never launch more CTAs than are resident at once (register/smem limited per variant)
+    int occ = 0, dev = 0, sms = 0;
+    B2K_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, scan_l2_topk_kernel<QT, VEC>, SCAN_THREADS, smem));
+    B2K_CUDA(cudaGetDevice(&dev));
+    B2K_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    if (occ > 0 && grid > occ * sms) grid = occ * sms;
     int64_t per = (n + grid - 1) / grid;
     per = (per + SCAN_ROWS_PER_ITER - 1) / SCAN_ROWS_PER_ITER * SCAN_ROWS_PER_ITER;
     scan_l2_topk_kernel<QT, VEC><<<grid, SCAN_THREADS, smem, st>>>(X, Q, n, d, k, P, per, partial, done, D, I);
