@@ -1,0 +1,107 @@
+"""Turn the ncu outputs in gpurun_out/ into the tracked summaries under profiles/.
+
+    python scripts/summarise_profiles.py r01
+"""
+import csv
+import json
+import os
+import re
+import subprocess
+import sys
+from collections import OrderedDict
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+R = sys.argv[1] if len(sys.argv) > 1 else "r01"
+G = os.path.join(ROOT, "gpurun_out")
+P = os.path.join(ROOT, "profiles")
+os.makedirs(P, exist_ok=True)
+
+
+def launches(path):
+    rows = list(csv.reader(open(path)))
+    for i, r in enumerate(rows):
+        if r and r[0] == "ID":
+            hdr, start = r, i + 1
+            break
+    ki, vi, ui = hdr.index("Kernel Name"), hdr.index("Metric Value"), hdr.index("Metric Unit")
+    out = []
+    for r in rows[start:]:
+        if len(r) > vi:
+            v = float(r[vi].replace(",", ""))
+            v *= {"ns": 1e-3, "us": 1.0, "ms": 1e3, "s": 1e6}.get(r[ui], 1.0)
+            out.append((re.sub(r"\(.*", "", r[ki]).replace("void ", "").strip(), v))
+    return out
+
+
+def raw_metrics(rep, wanted):
+    txt = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(txt.splitlines()))
+    hdr, units, vals = rows[0], rows[1], rows[2]
+    res = OrderedDict()
+    for w in wanted:
+        if w in hdr:
+            i = hdr.index(w)
+            res[w] = (vals[i], units[i])
+    return res
+
+
+WANTED = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
+          "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "lts__t_sector_hit_rate.pct",
+          "l1tex__m_xbar2l1tex_read_bytes.sum", "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_elapsed",
+          "sm__inst_executed_pipe_tensor_subpipe_hmma.avg.pct_of_peak_sustained_active",
+          "sm__cycles_elapsed.avg.per_second", "sm__warps_active.avg.pct_of_peak_sustained_active",
+          "launch__registers_per_thread", "launch__grid_size", "launch__block_size",
+          "launch__shared_mem_per_block_dynamic", "smsp__inst_executed.sum"]
+
+
+def to_bytes(v, u):
+    x = float(v.replace(",", ""))
+    return x * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}[u]
+
+
+traffic = {}
+md = ["# Round %s profile summary (B200, `scripts/profile.sh %s`; raw files in gpurun_out/, not tracked)\n" % (R, R)]
+for tag, rep, wl, kern, note in [
+        ("K3 main pass, C3 (10M x 384, nq=1024, k=100)", "%s_k3_c3.ncu-rep" % R, "c3", "k3_tf32x3_topk", "third k3 launch of the first search = the full pass"),
+        ("K2 scan, C3 nq=1 (10M x 384, k=100)", "%s_k2_c3q1.ncu-rep" % R, "c3q1", "scan_l2_topk_kernel", "one scan launch")]:
+    rep_path = os.path.join(G, rep)
+    if not os.path.exists(rep_path):
+        continue
+    m = raw_metrics(rep_path, WANTED)
+    md.append("## %s\n\n`ncu --set full --clock-control none --import-source on` (%s). Cold-ish caches, serialised: compare shares, not absolutes.\n" % (tag, note))
+    md.append("| metric | value |\n|---|---|")
+    for k, (v, u) in m.items():
+        md.append("| `%s` | %s %s |" % (k, v, u))
+    if "dram__bytes_read.sum" in m:
+        tot = to_bytes(*m["dram__bytes_read.sum"]) + to_bytes(*m["dram__bytes_write.sum"])
+        traffic["%s:%s:n1" % (wl, kern)] = {"bytes_per_launch": tot, "source": "profiles/%s_summary.md (ncu --set full, one launch)" % R}
+        md.append("\nDRAM traffic per launch (read + write) = **%.2f GB**." % (tot / 1e9))
+    md.append("")
+
+for tag, path in [("bench.py --workload c3 --steps 2 --warmup 1", "%s_c3_launches.csv" % R),
+                  ("bench.py --workload c3q1 --steps 5 --warmup 3", "%s_q1_launches.csv" % R)]:
+    fp = os.path.join(G, path)
+    if not os.path.exists(fp):
+        continue
+    L = launches(fp)
+    with open(os.path.join(P, path), "w") as f:
+        f.write("launch,kernel,gpu__time_duration_us\n")
+        for i, (k, v) in enumerate(L):
+            f.write("%d,%s,%.3f\n" % (i, k, v))
+    agg = OrderedDict()
+    for k, v in L:
+        agg.setdefault(k, []).append(v)
+    md.append("## Launch list: `%s` (first %d launches, `--metrics gpu__time_duration.sum --clock-control none`)\n" % (tag, len(L)))
+    md.append("Full list: `profiles/%s`.\n" % path)
+    md.append("| kernel | launches | mean us | min us | max us | share of listed GPU time |\n|---|---|---|---|---|---|")
+    total = sum(v for _, v in L)
+    for k, vs in agg.items():
+        md.append("| `%s` | %d | %.1f | %.1f | %.1f | %.1f %% |" % (k, len(vs), sum(vs) / len(vs), min(vs), max(vs), 100 * sum(vs) / total))
+    md.append("")
+
+open(os.path.join(P, "%s_summary.md" % R), "w").write("\n".join(md) + "\n")
+tj = os.path.join(P, "traffic.json")
+old = json.load(open(tj)) if os.path.exists(tj) else {}
+old.update(traffic)
+json.dump(old, open(tj, "w"), indent=1)
+print("\n".join(md))
