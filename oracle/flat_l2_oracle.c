@@ -329,6 +329,56 @@ ORC_API int orc_merge(int nlists, int64_t nq, int64_t k, const float* Din, const
     return 0;
 }
 
+/* ---- BLAS-backed variant of rule (2) -----------------------------------------------------
+ * faiss hands the inner-product block to sgemm_ (exhaustive_L2sqr_blas).  For the timed CPU
+ * baseline the caller (oracle.py: search_blas) computes each block <Q, X_blk> with the best
+ * BLAS present (MKL through torch.mm) and this code does what faiss does around the sgemm:
+ * norms, dis = qn + xn - 2 ip, clamp, result-handler update, final reorder.               */
+typedef struct { int64_t nq, k; orc_pair* heaps; int64_t* hn; } orc_state;
+
+ORC_API void* orc_blas_begin(int64_t nq, int64_t k) {
+    orc_state* st = (orc_state*)malloc(sizeof(orc_state));
+    st->nq = nq; st->k = k;
+    st->heaps = (orc_pair*)malloc(sizeof(orc_pair) * (size_t)k * (size_t)nq);
+    st->hn = (int64_t*)calloc((size_t)nq, sizeof(int64_t));
+    return st;
+}
+
+ORC_API void orc_norms(const float* x, int64_t n, int d, float* out) {
+#pragma omp parallel for schedule(static)
+    for (int64_t j = 0; j < n; ++j) out[j] = orc_norm2(x + j * (int64_t)d, d);
+}
+
+/* ip is [nq][nb] row-major: inner products of every query with database rows j0 .. j0+nb-1 */
+ORC_API void orc_blas_update(void* vst, int64_t nb, int64_t j0, const float* ip, const float* qn, const float* xn) {
+    orc_state* st = (orc_state*)vst;
+#pragma omp parallel for schedule(dynamic, 8)
+    for (int64_t i = 0; i < st->nq; ++i) {
+        orc_heap hp; hp.h = st->heaps + i * st->k; hp.k = st->k; hp.n = st->hn[i];
+        const float* row = ip + i * nb;
+        float qi = qn[i];
+        /* fast reject against the current worst once the heap is full (what the heap handler's
+         * threshold test does), exact (distance, id) test inside orc_heap_push */
+        for (int64_t j = 0; j < nb; ++j) {
+            float dv = qi + xn[j] - 2.f * row[j];
+            if (dv < 0.f) dv = 0.f;
+            if (hp.n == hp.k && dv > hp.h[0].dis) continue;
+            orc_heap_push(&hp, dv, j0 + j);
+        }
+        st->hn[i] = hp.n;
+    }
+}
+
+ORC_API void orc_blas_end(void* vst, float* D, int64_t* I) {
+    orc_state* st = (orc_state*)vst;
+#pragma omp parallel for schedule(static)
+    for (int64_t i = 0; i < st->nq; ++i) {
+        orc_heap hp; hp.h = st->heaps + i * st->k; hp.k = st->k; hp.n = st->hn[i];
+        orc_heap_emit(&hp, D + i * st->k, I + i * st->k);
+    }
+    free(st->heaps); free(st->hn); free(st);
+}
+
 ORC_API int orc_num_threads(void) {
 #ifdef _OPENMP
     return omp_get_max_threads();

@@ -39,6 +39,14 @@ def lib():
         L.orc_synth.argtypes = [ctypes.c_uint64, ctypes.c_int64, ctypes.c_int64, ctypes.c_int, fp]
         L.orc_synth.restype = None
         L.orc_num_threads.restype = ctypes.c_int
+        L.orc_blas_begin.argtypes = [ctypes.c_int64, ctypes.c_int64]
+        L.orc_blas_begin.restype = ctypes.c_void_p
+        L.orc_norms.argtypes = [fp, ctypes.c_int64, ctypes.c_int, fp]
+        L.orc_norms.restype = None
+        L.orc_blas_update.argtypes = [ctypes.c_void_p, ctypes.c_int64, ctypes.c_int64, fp, fp, fp]
+        L.orc_blas_update.restype = None
+        L.orc_blas_end.argtypes = [ctypes.c_void_p, fp, ip]
+        L.orc_blas_end.restype = None
         _lib = L
     return _lib
 
@@ -65,6 +73,35 @@ def search(x, q, k, mode=MODE_FAISS):
     I = np.empty((nq, k), np.int64)
     rc = lib().orc_search(_f(x), x.shape[0], d, _f(q), nq, k, _f(D), _i(I), mode)
     assert rc == 0
+    return D, I
+
+
+def search_blas(x, q, k, db_bs=8192):
+    """Rule (2) with the inner-product blocks delegated to the best BLAS present (MKL sgemm via
+    torch.mm on the CPU), as faiss delegates them to sgemm_; norms, clamp and result handling in
+    the C oracle.  Used as the timed CPU baseline for batched searches; same results as
+    search(..., MODE_EXPAND) up to the summation order inside the BLAS."""
+    import torch
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    q = np.ascontiguousarray(q, dtype=np.float32)
+    nq, d = q.shape
+    n = x.shape[0]
+    L = lib()
+    qn = np.empty(nq, np.float32)
+    xn = np.empty(max(n, 1), np.float32)
+    L.orc_norms(_f(q), nq, d, _f(qn))
+    if n:
+        L.orc_norms(_f(x), n, d, _f(xn))
+    st = L.orc_blas_begin(nq, k)
+    qt = torch.from_numpy(q)
+    xt = torch.from_numpy(x)
+    for j0 in range(0, n, db_bs):
+        nb = min(db_bs, n - j0)
+        ip = torch.mm(qt, xt[j0:j0 + nb].T).contiguous().numpy()
+        L.orc_blas_update(st, nb, j0, _f(ip), _f(qn), _f(xn[j0:j0 + nb]))
+    D = np.empty((nq, k), np.float32)
+    I = np.empty((nq, k), np.int64)
+    L.orc_blas_end(st, _f(D), _i(I))
     return D, I
 
 

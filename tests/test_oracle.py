@@ -121,3 +121,14 @@ def test_golden_fixtures(name):
     D, I = O.search(x, q, int(g["k"]))
     assert np.array_equal(I, g["I"])
     assert np.allclose(D, g["D"], rtol=2e-6, atol=2e-6)
+
+
+def test_blas_backed_variant_matches_plain_restatement():
+    """search_blas (sgemm blocks through torch's MKL, used only as the timed CPU baseline) returns
+    the same neighbours as the plain-C expansion path; distances agree to BLAS summation order."""
+    x = O.synth(1234, 0, 20000, 96)
+    q = O.synth(5678, 0, 33, 96)
+    D1, I1 = O.search(x, q, 10, O.MODE_EXPAND)
+    D2, I2 = O.search_blas(x, q, 10, db_bs=4096)
+    assert np.allclose(D1, D2, rtol=1e-5, atol=1e-4)
+    assert (I1 == I2).mean() > 0.99
