@@ -73,6 +73,14 @@ B2K_API int b2k_reset(b2k_index* h);
  * (45-byte header + ntotal*d float32), written to path.tmp then renamed. */
 B2K_API int b2k_write(const b2k_index* h, const char* path);
 
+/* Incremental form of write_index for `update_index` (llm/rag.py:74-84: read the file, add
+ * rows, rewrite the whole file).  If `path` is an IxF2 file of the same d that holds exactly
+ * the first `first_row` rows of this index (header and size are checked; the row CONTENT is
+ * the caller's claim -- the Python layer only makes it for an index it loaded from that file),
+ * rows [first_row, ntotal) are appended and the 45-byte header is rewritten with one write.
+ * The result is byte-identical to b2k_write.  Any mismatch -> B2K_EINVAL, file untouched. */
+B2K_API int b2k_write_append(const b2k_index* h, const char* path, int64_t first_row);
+
 /* faiss.read_index(path) -- llm/rag.py:74, :153, :186.  Missing file -> B2K_EIO. */
 B2K_API int b2k_read(const char* path, int device, b2k_index** out);
 

@@ -13,15 +13,18 @@ is no CPU path.  numpy inputs are host buffers (results are fresh numpy arrays, 
 returns); torch CUDA tensors are used in place (results are torch tensors on that device,
 enqueued on torch's current stream).
 """
+import collections
 import ctypes as C
 import os
+import threading
 
 import numpy as np
 
 from . import _lib
 from ._lib import MAX_K
 
-__all__ = ["IndexFlatL2", "write_index", "read_index", "METRIC_L2", "default_device", "launch_count"]
+__all__ = ["IndexFlatL2", "write_index", "read_index", "METRIC_L2", "default_device", "launch_count",
+           "clear_index_cache"]
 
 METRIC_L2 = 1
 __version__ = "0.1.0"
@@ -65,6 +68,9 @@ class IndexFlatL2:
 
     is_trained = True
     metric_type = METRIC_L2
+    # provenance for the resident-index cache / incremental write_index (see read_index below):
+    _origin = None   # (realpath, stat key, rows in that file) while those rows are a prefix of this index
+    _clean = False   # True while the index content is exactly that file
 
     def __init__(self, d, device=None, _handle=None):
         self._h = None
@@ -99,6 +105,7 @@ class IndexFlatL2:
     def add(self, x):
         """Append rows (rag.py:80).  Ids are row positions, sequential across adds."""
         L = _lib.lib()
+        self._clean = False
         if _is_torch(x) and x.is_cuda:
             x = _as_dev_f32(x, self.d, self.device, "add")
             _lib.check(L.b2k_add(self._h, x.shape[0], C.c_void_p(x.data_ptr()), 1, self._stream()))
@@ -133,6 +140,7 @@ class IndexFlatL2:
         return D, I
 
     def reset(self):
+        self._origin, self._clean = None, False
         _lib.check(_lib.lib().b2k_reset(self._h))
 
     def reserve(self, nrows):
@@ -147,6 +155,7 @@ class IndexFlatL2:
 
     def add_synthetic(self, n, seed, first_row=0):
         """Append n rows of the counter-based synthetic stream, generated on the GPU."""
+        self._clean = False
         _lib.check(_lib.lib().b2k_add_synthetic(self._h, int(n), int(seed), int(first_row)))
 
     def stats(self):
@@ -168,17 +177,92 @@ class IndexFlatL2:
         _lib.check(_lib.lib().b2k_set_option(self._h, key.encode(), int(value)))
 
 
+# ---- persistence ---------------------------------------------------
+# llm/rag.py re-reads the whole index file on EVERY request (rag.py:153, :186) and rewrites the
+# whole file on every upload (rag.py:74-84).  With the index in HBM that would put a file read
+# plus an H2D copy of the full index in front of every search, so:
+#   * read_index keeps the last few loaded indexes resident, keyed on (realpath, mtime_ns, size,
+#     inode); an unchanged file returns the resident index without touching the disk or the bus;
+#   * write_index of an index that was loaded from `path` and only grew since appends the new
+#     rows and rewrites the 45-byte header instead of rewriting everything (the file stays
+#     byte-identical to a full write).
+# Observable difference from faiss: two read_index calls on an unchanged file return the SAME
+# object, so rows added through one reference are visible through the other until the next
+# read_index (which sees the index is no longer the file and loads a fresh one).
+# B200KNN_INDEX_CACHE=0 restores independent loads; =N keeps N indexes (default 4).
+_cache = collections.OrderedDict()
+_cache_lock = threading.Lock()
+
+
+def _cache_max():
+    try:
+        return max(int(os.environ.get("B200KNN_INDEX_CACHE", "4")), 0)
+    except ValueError:
+        return 4
+
+
+def _stat_key(path):
+    st = os.stat(path)
+    return (st.st_mtime_ns, st.st_size, st.st_ino)
+
+
+def _remember(rp, key, index):
+    index._origin = (rp, key, index.ntotal)
+    index._clean = True
+    n = _cache_max()
+    with _cache_lock:
+        _cache.pop(rp, None)
+        if n:
+            _cache[rp] = (key, index)
+            while len(_cache) > n:
+                _cache.popitem(last=False)
+
+
+def clear_index_cache():
+    with _cache_lock:
+        _cache.clear()
+
+
 def write_index(index, path):
-    """faiss.write_index (rag.py:62, :82): byte-exact IxF2 file, written atomically."""
-    _lib.check(_lib.lib().b2k_write(index._h, os.fsencode(path)))
+    """faiss.write_index (rag.py:62, :82): byte-exact IxF2 file.  Full writes go through
+    path.tmp + rename; an index that only grew since it was loaded from `path` is appended."""
+    L = _lib.lib()
+    rp = os.path.realpath(path)
+    o = index._origin
+    appended = False
+    if o is not None and o[0] == rp and o[2] <= index.ntotal and _cache_max():
+        try:
+            same = _stat_key(rp) == o[1]
+        except OSError:
+            same = False
+        if same:
+            appended = L.b2k_write_append(index._h, os.fsencode(path), o[2]) == _lib.OK
+    if not appended:
+        _lib.check(L.b2k_write(index._h, os.fsencode(path)))
+    _remember(rp, _stat_key(rp), index)
 
 
 def read_index(path, device=None):
     """faiss.read_index (rag.py:74, :153, :186); a missing file raises RuntimeError."""
     dev = default_device() if device is None else int(device)
+    rp = os.path.realpath(path)
+    key = None
+    try:
+        key = _stat_key(rp)
+    except OSError:
+        pass                                   # let the library produce faiss's error message
+    if key is not None and _cache_max():
+        with _cache_lock:
+            ent = _cache.get(rp)
+            if ent is not None and ent[0] == key and ent[1]._clean and ent[1].device == dev:
+                _cache.move_to_end(rp)
+                return ent[1]
     h = C.c_void_p()
     _lib.check(_lib.lib().b2k_read(os.fsencode(path), dev, C.byref(h)))
-    return IndexFlatL2(0, device=dev, _handle=h)
+    idx = IndexFlatL2(0, device=dev, _handle=h)
+    if key is not None and _stat_key(rp) == key:
+        _remember(rp, key, idx)
+    return idx
 
 
 def synth(seed, row0, nrows, d, device=None):

@@ -26,6 +26,7 @@ SIGNATURES = {
     "b2k_d": (C.c_int, [C.c_void_p]),
     "b2k_reset": (C.c_int, [C.c_void_p]),
     "b2k_write": (C.c_int, [C.c_void_p, C.c_char_p]),
+    "b2k_write_append": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int64]),
     "b2k_read": (C.c_int, [C.c_char_p, C.c_int, C.POINTER(C.c_void_p)]),
     "b2k_last_error": (C.c_char_p, []),
     "b2k_reserve": (C.c_int, [C.c_void_p, C.c_int64]),

@@ -581,6 +581,54 @@ int b2k_write(const b2k_index* hc, const char* path) {
     return rc;
 }
 
+int b2k_write_append(const b2k_index* hc, const char* path, int64_t first_row) {
+    b2k_index* h = const_cast<b2k_index*>(hc);
+    if (!h || !path || first_row < 0) { set_error("b2k_write_append: bad argument"); return B2K_EINVAL; }
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (first_row > h->ntotal) { set_error("b2k_write_append: first_row %lld > ntotal %lld", (long long)first_row, (long long)h->ntotal); return B2K_EINVAL; }
+    DeviceGuard g(h->device);
+    FILE* f = fopen(path, "r+b");
+    if (!f) { set_error("could not open %s for appending: %s", path, strerror(errno)); return B2K_EIO; }
+    unsigned char hdr[IXF2_HEADER], want[IXF2_HEADER];
+    put_header(want, h->d, first_row);
+    int rc = B2K_OK;
+    if (fread(hdr, 1, IXF2_HEADER, f) != IXF2_HEADER || memcmp(hdr, want, IXF2_HEADER) != 0) {
+        set_error("%s does not hold exactly the first %lld rows of a d=%d IxF2 index", path, (long long)first_row, h->d);
+        rc = B2K_EINVAL;
+    }
+    const size_t row_bytes = (size_t)h->d * sizeof(float);
+    if (!rc) {
+        if (fseeko(f, 0, SEEK_END) != 0 || (size_t)ftello(f) != IXF2_HEADER + (size_t)first_row * row_bytes) {
+            set_error("%s: size does not match its header", path);
+            rc = B2K_EINVAL;
+        }
+    }
+    size_t total = (size_t)(h->ntotal - first_row) * row_bytes, done = 0;
+    if (!rc && total) {
+        rc = ensure_pin(h, total < IO_CHUNK ? total : IO_CHUNK);
+        const unsigned char* src = reinterpret_cast<const unsigned char*>(h->x) + (size_t)first_row * row_bytes;
+        while (!rc && done < total) {
+            size_t n = total - done < IO_CHUNK ? total - done : IO_CHUNK;
+            cudaError_t e = cudaMemcpyAsync(h->pin, src + done, n, cudaMemcpyDeviceToHost, h->stream);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+            if (e != cudaSuccess) { set_error("b2k_write_append: %s", cudaGetErrorString(e)); rc = B2K_ECUDA; break; }
+            if (fwrite(h->pin, 1, n, f) != n) { set_error("error appending to %s: %s", path, strerror(errno)); rc = B2K_EIO; break; }
+            done += n;
+        }
+    }
+    if (!rc) {
+        // rows first, header last: a reader that opens the file in between still sees a consistent
+        // (old) header and ignores the extra bytes behind the payload it describes
+        put_header(want, h->d, h->ntotal);
+        if (fflush(f) != 0 || fseeko(f, 0, SEEK_SET) != 0 || fwrite(want, 1, IXF2_HEADER, f) != IXF2_HEADER) {
+            set_error("error updating the header of %s: %s", path, strerror(errno));
+            rc = B2K_EIO;
+        }
+    }
+    if (fclose(f) != 0 && !rc) { set_error("error closing %s: %s", path, strerror(errno)); rc = B2K_EIO; }
+    return rc;
+}
+
 int b2k_read(const char* path, int device, b2k_index** out) {
     if (!path || !out) { set_error("b2k_read: null argument"); return B2K_EINVAL; }
     *out = nullptr;

@@ -380,3 +380,48 @@ def test_large_k_large_batch_stress(faiss):
         a, b = D[qi].cpu().numpy(), Ds[j].cpu().numpy()
         assert np.allclose(a, b, rtol=RTOL, atol=RTOL * 2048)
         assert len(set(I[qi].cpu().tolist()) ^ set(Is[j].cpu().tolist())) <= 4
+
+
+def test_resident_index_cache_and_incremental_write(faiss, tmp_path, monkeypatch):
+    """rag.py re-reads the index file on every request (rag.py:153) and
+    rewrites it on every upload (rag.py:74-84).  An unchanged file must come back resident (same
+    object, no reload); an index that only grew since it was loaded is appended to the file, and the
+    file stays byte-identical to a full write; any other change falls back to load / full write."""
+    monkeypatch.delenv("B200KNN_INDEX_CACHE", raising=False)
+    faiss.clear_index_cache()
+    p = str(tmp_path / "faiss_index")
+    x = O.synth(3, 0, 5000, 64)
+    idx = faiss.IndexFlatL2(64)
+    idx.add(x[:2000])
+    faiss.write_index(idx, p)
+    a = faiss.read_index(p)
+    b = faiss.read_index(p)
+    assert a is b                                   # resident: no second load
+    a.add(x[2000:3500])                             # update_index: read -> add -> write
+    c = faiss.read_index(p)                         # the file still has 2000 rows: fresh load, not the dirty object
+    assert c is not a and c.ntotal == 2000
+    size_before = os.path.getsize(p)
+    faiss.write_index(a, p)                         # appended in place
+    assert os.path.getsize(p) == 45 + 4 * 3500 * 64 and os.path.getsize(p) > size_before
+    ref = str(tmp_path / "ref")
+    O.write_ixf2(ref, x[:3500])
+    assert open(p, "rb").read() == open(ref, "rb").read()
+    assert faiss.read_index(p) is a                 # cache follows the write
+    d2, x2 = O.read_ixf2(p)
+    assert d2 == 64 and np.array_equal(x2, x[:3500])
+    # a file changed behind our back is reloaded
+    O.write_ixf2(p, x[:100])
+    os.utime(p, ns=(1, 1))
+    e = faiss.read_index(p)
+    assert e is not a and e.ntotal == 100
+    # a reset index is written in full, not appended
+    a.reset()
+    a.add(x[:10])
+    faiss.write_index(a, p)
+    assert os.path.getsize(p) == 45 + 4 * 10 * 64
+    q = O.synth(4, 0, 2, 64)
+    D, I = faiss.read_index(p).search(q, 3)
+    assert_knn_matches(D, I, x[:10], q, 3, what="after rewrite")
+    # cache off: independent loads, as faiss
+    monkeypatch.setenv("B200KNN_INDEX_CACHE", "0")
+    assert faiss.read_index(p) is not faiss.read_index(p)
