@@ -38,6 +38,7 @@ WORKLOADS = {
     "c2": (1_000_000, 384, 1, 10),
     "c3": (10_000_000, 384, 1024, 100),
     "c3q1": (10_000_000, 384, 1, 100),
+    "c4": (100_000_000, 768, 256, 100),      # needs 8 GPUs (38.4 GB of rows + 38.4 GB residual rows per GPU)
     "c5": (10_000_000, 1024, 4096, 1024),
     "smoke": (200_000, 384, 64, 10),
 }
@@ -175,6 +176,8 @@ def main():
     import b200knn
     from b200knn import _lib
 
+    if N * d * 8 / max(world, 1) > 150e9:
+        raise SystemExit("bench.py: workload %s needs more GPUs (%.0f GB per GPU at --gpus %d)" % (args.workload, N * d * 8 / world / 1e9, world))
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; b200knn has no CPU path (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local_rank)

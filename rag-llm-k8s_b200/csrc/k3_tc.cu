@@ -64,6 +64,7 @@ struct K3Params {
     u64* next_unit;     // dynamic scheduler: next unit to hand out
     int static_mode;    // 1: warm-start pass, CTA (pair) c takes tiles static_tile0 + c*static_tpc + [0,static_tpc), all query blocks
     int static_tpc;
+    int tile_cols;      // columns (rows of the tile) the epilogue looks at: 256, or fewer in the first warm-start pass
     int64_t static_tile0;
 };
 
@@ -308,7 +309,7 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
             xb ^= 1;
             for (int j = epi_tid; j < K3_BN; j += K3_EPI_THREADS) {
                 const int64_t r = t * K3_BN + j;
-                xn[j] = r < p.n ? p.norms[r] : INF;
+                xn[j] = (r < p.n && j < p.tile_cols) ? p.norms[r] : INF;
             }
             asm volatile("bar.sync 1, 128;" ::: "memory");
 
@@ -682,6 +683,7 @@ int k3_search(K3State* s, const float* x, const float* xlo, const float* norms, 
     p.static_mode = 0;
     p.static_tpc = 1;
     p.static_tile0 = 0;
+    p.tile_cols = K3_BN;
 
     // queries: norms + TF32 residual rows (K1 reused), list state reset
     int rc = launch_row_prep(q, nq, d, const_cast<float*>(p.qn), qlo, st);
@@ -698,18 +700,21 @@ int k3_search(K3State* s, const float* x, const float* xlo, const float* norms, 
     if ((rc = make_map(s, &mx, x, n, d, K3_BN / L.cg))) return rc;
     if ((rc = make_map(s, &mxl, xlo, n, d, K3_BN / L.cg))) return rc;
 
-    // Warm start.  Round A: one tile per CTA (pair) with open thresholds; per query the k-th
-    // smallest distance of that sample becomes the shared threshold (an upper bound of the final
-    // k-th distance).  Round B: a few more tiles per CTA under that threshold (few survivors), and
-    // the threshold is tightened again.  The full pass then prunes from its first tile: its lists
-    // stay far below capacity (no compaction sorts) and K4 has little to merge.
+    // Warm start.  Round A: the first 64 rows of one tile per CTA (pair) with open thresholds --
+    // every key is kept, so the pass is kept small; per query the k-th smallest distance of that
+    // sample becomes the shared threshold (an upper bound of the final k-th distance).  Round B:
+    // a few whole tiles per CTA under that threshold (few survivors), and the threshold is
+    // tightened again.  The full pass then prunes from its first tile: its lists stay far below
+    // capacity (no compaction sorts) and K4 has a few k keys per query to merge.
     const int nclusters = L.ncta / L.cg;
     const bool sep = s->sep_mode == 1 || (s->sep_mode == 0 && d >= 512);
-    if (ntiles >= 2 * (int64_t)nclusters && (int64_t)nclusters * K3_BN >= 2 * (int64_t)k) {
+    const int cols_a = 64;
+    if (ntiles >= 2 * (int64_t)nclusters && (int64_t)nclusters * cols_a >= 2 * (int64_t)k) {
         K3Params pre = p;
         pre.static_mode = 1;
         pre.static_tpc = 1;
         pre.static_tile0 = 0;
+        pre.tile_cols = cols_a;
         pre.nunits = (int64_t)nclusters * L.nqb;
         pre.n = (int64_t)nclusters * K3_BN;
         rc = launch_k3_any(L.cg, L.P, sep, mq, mql, mx, mxl, pre, L.ncta, st);
@@ -721,10 +726,12 @@ int k3_search(K3State* s, const float* x, const float* xlo, const float* norms, 
         // rows the second round should cover so that the full pass leaves ~<= 64 keys per list
         const double want_rows = (double)n * k / ((double)nclusters * 64.0);
         int tpc = (int)(want_rows / ((double)nclusters * K3_BN) + 0.999);
+        if (tpc < 1) tpc = 1;
         if (tpc > 16) tpc = 16;
-        if (tpc >= 2 && ntiles >= (int64_t)(tpc + 1) * nclusters * 2) {
+        if (ntiles >= (int64_t)(tpc + 1) * nclusters * 2) {
             pre.static_tpc = tpc;
             pre.static_tile0 = nclusters;
+            pre.tile_cols = K3_BN;
             pre.n = (int64_t)nclusters * (tpc + 1) * K3_BN;
             pre.nunits = (int64_t)nclusters * (tpc + 1) * L.nqb;
             rc = launch_k3_any(L.cg, L.P, sep, mq, mql, mx, mxl, pre, L.ncta, st);
