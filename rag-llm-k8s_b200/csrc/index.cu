@@ -71,6 +71,7 @@ struct b2k_index {
 
 static constexpr int64_t MAX_ROWS = 0xFFFFFFFEll;  // row index lives in the low 32 bits of a key
 static constexpr size_t IO_CHUNK = (size_t)64 << 20;
+static constexpr int64_t TC_QUERY_CHUNK = 4096;  // queries per tensor-core pass (faiss: distance_compute_blas_query_bs)
 
 namespace {
 
@@ -424,7 +425,7 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
     size_t io_bytes = on_device ? 0 : q_bytes + d_bytes + i_bytes;
     size_t scratch = 0;
     if (h->ntotal > 0) {
-        if (want_tc) scratch = k3_scratch_bytes(h->sm_count, h->d, nq, kk);
+        if (want_tc) scratch = k3_scratch_bytes(h->sm_count, h->d, nq < TC_QUERY_CHUNK ? nq : TC_QUERY_CHUNK, kk);
         else scratch = scan_partial_bytes(scan_grid(h->ntotal, h->sm_count, h->opt_scan_ctas_per_sm), 8, kk);
     }
     int rc = ensure_ws(h, io_bytes + align256(scratch));
@@ -458,8 +459,13 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
                 if (!rc) k3_set_sep_mode(h->k3, h->opt_sep);
             }
             if (!rc) h->last_path = 2;
-            if (!rc) rc = k3_search(h->k3, h->x, h->xlo, h->norms, h->ntotal, h->capacity, h->d, qd, nq, kk, Dd, Id,
-                                    ws_tail, st);
+            // like faiss (query blocks of 4096), long batches go through in chunks: the candidate-list
+            // scratch is sized per chunk and one pass over the rows per chunk is still compute-bound
+            for (int64_t q0 = 0; q0 < nq && !rc; q0 += TC_QUERY_CHUNK) {
+                const int64_t nqc = nq - q0 < TC_QUERY_CHUNK ? nq - q0 : TC_QUERY_CHUNK;
+                rc = k3_search(h->k3, h->x, h->xlo, h->norms, h->ntotal, h->capacity, h->d, qd + q0 * (int64_t)h->d, nqc,
+                               kk, Dd + q0 * kk, Id + q0 * kk, ws_tail, st);
+            }
         }
     } else {
         h->last_path = 1;

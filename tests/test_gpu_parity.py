@@ -425,3 +425,35 @@ def test_resident_index_cache_and_incremental_write(faiss, tmp_path, monkeypatch
     # cache off: independent loads, as faiss
     monkeypatch.setenv("B200KNN_INDEX_CACHE", "0")
     assert faiss.read_index(p) is not faiss.read_index(p)
+
+
+def test_long_query_batch_is_chunked(faiss):
+    """More than 4096 queries go through the tensor-core kernel in chunks (faiss's query block
+    size); results must not depend on the chunking."""
+    x = O.synth(1234, 0, 30000, 64)
+    q = O.synth(5678, 0, 4096 + 300, 64)
+    idx = _build(faiss, x)
+    D, I = idx.search(q, 5)
+    D2, I2 = idx.search(q[4000:], 5)
+    assert np.array_equal(I[4000:], I2) and np.array_equal(D[4000:], D2)
+    sel = [0, 4095, 4096, 4395]
+    assert_knn_matches(D[sel], I[sel], x, q[sel], 5, expanded=True, what="chunked")
+
+
+def test_adversarial_row_order(faiss):
+    """Rows ordered so that every later row is closer to every query than all earlier ones: the
+    running thresholds never help, every tile floods the candidate lists and every list is
+    compacted again and again.  Slow by construction, but the answer must still be exact."""
+    n, d = 60000, 32
+    u = np.zeros(d, np.float32)
+    u[0] = 1.0
+    scale = (2.0 - np.arange(n, dtype=np.float32) / n)[:, None]        # 2.0 -> 1.0, strictly decreasing
+    x = (scale * u[None, :]).astype(np.float32)
+    x[:, 1:] = O.synth(9, 0, n, d - 1) * 1e-3
+    q = O.synth(10, 0, 40, d) * 1e-2                                    # near the origin
+    for path in (2, 1):
+        idx = _build(faiss, x)
+        idx.set_option("path", path)
+        D, I = idx.search(q, 10)
+        assert_knn_matches(D, I, x, q, 10, expanded=(path == 2), what="adversarial path=%d" % path)
+        assert I.min() >= n - 200                                       # the neighbours are the last rows
