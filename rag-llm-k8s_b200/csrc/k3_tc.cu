@@ -399,71 +399,135 @@ __global__ void k3_init_kernel(int64_t nslots, int* cnt, float* tau, u64* kth, i
 }
 
 // ---- K4: per query, merge the lists of every CTA that saw it ---------------------------------
+// One CTA per query.  The lists hold every key under the warm-started shared bound: a few
+// thousand per query, of which k are wanted.  A full sort of them is what made this kernel cost
+// 0.2 ms, so selection is sample-based: sort 512 of the gathered keys, take the sample rank that
+// (with a 4-sigma margin) leaves at least k keys of the whole set below it, keep only the keys
+// under that value, and sort those.  The count is checked, so the result is exact: if the guess
+// leaves fewer than k keys (or too many), the kernel falls back to sorting everything.
 static constexpr int K4_THREADS = 256;
-static constexpr int K4_P = 4096;
+static constexpr int K4_P = 4096;     // gathered keys kept in shared memory
+static constexpr int K4_SAMPLE = 512;
+static constexpr int K4_DIRECT = 1024; // up to this many gathered keys are simply sorted
+static constexpr int K4_OUT = 2048;   // keys under the refined bound (k <= 1024 plus the sampling margin)
+
+struct K4Smem {
+    u64 buf[K4_P];
+    u64 smp[K4_SAMPLE];
+    u64 out[K4_OUT];
+    int cnt, cnt2;
+    u64 kth;
+};
+
+// every list_step-th list of query (qb,row), all keys <= kbound -> sm.buf (first K4_P of them); returns the total
+__device__ __forceinline__ int k4_gather(const K3Params& p, int cg, int ncta, int lstep, int r, int qb, int row,
+                                         u64 kbound, K4Smem& sm) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    __syncthreads();
+    if (tid == 0) sm.cnt = 0;
+    __syncthreads();
+    constexpr int LB = 4;  // four lists per warp at a time: their counts, then their keys, are independent loads
+    const int wstride = (K4_THREADS / 32) * LB * lstep;
+    for (int cta0 = r + warp * LB * lstep; cta0 < ncta; cta0 += wstride) {
+        int c[LB];
+        const u64* lst[LB];
+        int cmax = 0;
+#pragma unroll
+        for (int j = 0; j < LB; ++j) {
+            const int cta = cta0 + j * lstep;
+            const int64_t sidx = (int64_t)(cta < ncta ? cta : r) * p.qpc + (int64_t)qb * K3_BM + row;
+            c[j] = cta < ncta ? p.cnt[sidx] : 0;
+            lst[j] = p.cand + sidx * p.P;
+        }
+#pragma unroll
+        for (int j = 0; j < LB; ++j) cmax = c[j] > cmax ? c[j] : cmax;
+        for (int i = lane; i < cmax; i += 32) {
+            u64 key[LB];
+#pragma unroll
+            for (int j = 0; j < LB; ++j) key[j] = i < c[j] ? lst[j][i] : KEY_EMPTY;
+#pragma unroll
+            for (int j = 0; j < LB; ++j) {
+                if (key[j] <= kbound) {  // KEY_EMPTY (all ones) is above any bound
+                    const int pos = atomicAdd(&sm.cnt, 1);
+                    if (pos < K4_P) sm.buf[pos] = key[j];
+                }
+            }
+        }
+    }
+    __syncthreads();
+    return sm.cnt;
+}
+
+// sort the first n keys of a (capacity cap, power of two); block-wide
+__device__ __forceinline__ void k4_sort(u64* a, int n, int cap) {
+    int Ps = 2;
+    while (Ps < n) Ps <<= 1;
+    if (Ps > cap) Ps = cap;
+    for (int j = n + threadIdx.x; j < Ps; j += K4_THREADS) a[j] = KEY_EMPTY;
+    __syncthreads();
+    block_bitonic_sort(a, Ps);
+}
 
 __global__ void __launch_bounds__(K4_THREADS)
-k4_merge_kernel(const K3Params p, int cg, int ncta, int threshold_only, float* __restrict__ D, int64_t* __restrict__ I) {
-    __shared__ u64 buf[K4_P];
-    __shared__ int s_cnt;
-    __shared__ u64 s_kth;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+k4_merge_kernel(const K3Params p, int cg, int ncta, int threshold_only, int list_step, float* __restrict__ D,
+                int64_t* __restrict__ I) {
+    extern __shared__ __align__(16) unsigned char k4_smem_raw[];
+    K4Smem& sm = *reinterpret_cast<K4Smem*>(k4_smem_raw);
+    const int tid = threadIdx.x;
     const int64_t qi = blockIdx.x;
     const int bq = K3_BM * cg;
     const int qb = (int)(qi / bq);
     const int r = (int)(qi - (int64_t)qb * bq) / K3_BM;
     const int row = (int)(qi % K3_BM);
-    const float bound = __uint_as_float(p.gts[qi]);
-    if (tid == 0) { s_cnt = 0; s_kth = KEY_EMPTY; }
-    __syncthreads();
-    // Every warp walks its share of the lists and gathers the keys under the shared bound.  If
-    // they do not fit the buffer, the k-th smallest of the subset that did fit is a tighter bound
-    // (still an upper bound of the final k-th key) and the lists are gathered once more under it.
-    u64 kbound = ((u64)__float_as_uint(bound) << 32) | 0xffffffffull;
-    for (int pass = 0; pass < 2; ++pass) {
-        // four lists per warp at a time: their counts, then their keys, are independent loads
-        constexpr int LB = 4;
-        const int wstride = (K4_THREADS / 32) * LB * cg;
-        for (int cta0 = r + warp * LB * cg; cta0 < ncta; cta0 += wstride) {
-            int c[LB];
-            const u64* lst[LB];
-            int cmax = 0;
-#pragma unroll
-            for (int j = 0; j < LB; ++j) {
-                const int cta = cta0 + j * cg;
-                const int64_t sidx = (int64_t)(cta < ncta ? cta : r) * p.qpc + (int64_t)qb * K3_BM + row;
-                c[j] = cta < ncta ? p.cnt[sidx] : 0;
-                lst[j] = p.cand + sidx * p.P;
-            }
-#pragma unroll
-            for (int j = 0; j < LB; ++j) cmax = c[j] > cmax ? c[j] : cmax;
-            for (int i = lane; i < cmax; i += 32) {
-                u64 key[LB];
-#pragma unroll
-                for (int j = 0; j < LB; ++j) key[j] = i < c[j] ? lst[j][i] : KEY_EMPTY;
-#pragma unroll
-                for (int j = 0; j < LB; ++j) {
-                    if (key[j] <= kbound) {  // KEY_EMPTY (all ones) is above any bound
-                        const int pos = atomicAdd(&s_cnt, 1);
-                        if (pos < K4_P) buf[pos] = key[j];
-                    }
-                }
+    const int lstep = cg * list_step;
+    const int k = p.k;
+    u64 kbound = ((u64)p.gts[qi] << 32) | 0xffffffffull;
+    const u64* res = nullptr;  // sorted keys, the k smallest first
+    int nres = 0;
+
+    for (int attempt = 0; attempt < 4 && !res; ++attempt) {
+        const int total = k4_gather(p, cg, ncta, lstep, r, qb, row, kbound, sm);
+        const int have = total < K4_P ? total : K4_P;
+        if (total <= K4_DIRECT) {  // small enough: sort it all
+            if (attempt > 0 && total < k) break;  // the tightened bound cut too deep: exhaustive path
+            k4_sort(sm.buf, have, K4_P);
+            res = sm.buf; nres = have;
+            break;
+        }
+        // sample -> tighter bound
+        for (int j = tid; j < K4_SAMPLE; j += K4_THREADS) sm.smp[j] = sm.buf[j];  // first arrivals: an arbitrary subset
+        __syncthreads();
+        block_bitonic_sort(sm.smp, K4_SAMPLE);
+        const float mean = (float)k * (float)K4_SAMPLE / (float)total;      // expected sample rank of the k-th key
+        const int rk = (int)(mean + 4.f * sqrtf(mean) + 3.f);
+        if (rk >= K4_SAMPLE) break;                                          // cannot tighten: sort everything
+        const u64 b2 = sm.smp[rk];
+        if (total > K4_P) { kbound = b2; continue; }                         // did not fit: gather again under b2
+        if (tid == 0) sm.cnt2 = 0;
+        __syncthreads();
+        for (int j = tid; j < have; j += K4_THREADS) {
+            const u64 key = sm.buf[j];
+            if (key <= b2) {
+                const int pos = atomicAdd(&sm.cnt2, 1);
+                if (pos < K4_OUT) sm.out[pos] = key;
             }
         }
         __syncthreads();
-        if (s_cnt <= K4_P || pass == 1) break;
-        block_bitonic_sort(buf, K4_P);
-        kbound = buf[p.k - 1];
-        __syncthreads();
-        if (tid == 0) s_cnt = 0;
-        __syncthreads();
+        const int c2 = sm.cnt2;
+        if (c2 >= k && c2 <= K4_OUT) {
+            k4_sort(sm.out, c2, K4_OUT);
+            res = sm.out; nres = c2;
+        }
+        break;  // unlucky guess: fall through to the exhaustive path
     }
-    if (s_cnt > K4_P) {
-        // slow path (bound too loose for the buffer): stream the lists, compacting as needed
+
+    if (!res) {
+        // exhaustive path: stream the lists under the original bound, compacting as needed
+        const float bound = __uint_as_float(p.gts[qi]);
         __syncthreads();
-        if (tid == 0) { s_cnt = 0; s_kth = KEY_EMPTY; }
+        if (tid == 0) { sm.cnt = 0; sm.kth = KEY_EMPTY; }
         __syncthreads();
-        for (int cta = r; cta < ncta; cta += cg) {
+        for (int cta = r; cta < ncta; cta += lstep) {
             const int64_t sidx = (int64_t)cta * p.qpc + (int64_t)qb * K3_BM + row;
             const int c = p.cnt[sidx];
             const u64* lst = p.cand + sidx * p.P;
@@ -472,44 +536,38 @@ k4_merge_kernel(const K3Params p, int cg, int ncta, int threshold_only, float* _
                 const int i = i0 + tid;
                 if (i < c) {
                     const u64 key = lst[i];
-                    if (key_dist(key) <= bound && key < s_kth) {
-                        int pos = atomicAdd(&s_cnt, 1);
-                        buf[pos] = key;
+                    if (key_dist(key) <= bound && key < sm.kth) {
+                        int pos = atomicAdd(&sm.cnt, 1);
+                        sm.buf[pos] = key;
                         if (pos + 1 > K4_P - K4_THREADS) flag = 1;
                     }
                 }
                 if (__syncthreads_or(flag)) {
-                    const int cc = s_cnt;
-                    int Ps = 2;
-                    while (Ps < cc) Ps <<= 1;
-                    for (int j = cc + tid; j < Ps; j += K4_THREADS) buf[j] = KEY_EMPTY;
-                    __syncthreads();
-                    block_bitonic_sort(buf, Ps);
-                    if (tid == 0) { s_cnt = cc < p.k ? cc : p.k; if (cc >= p.k) s_kth = buf[p.k - 1]; }
+                    const int cc = sm.cnt;
+                    k4_sort(sm.buf, cc, K4_P);
+                    if (tid == 0) { sm.cnt = cc < k ? cc : k; if (cc >= k) sm.kth = sm.buf[k - 1]; }
                     __syncthreads();
                 }
             }
         }
         __syncthreads();
+        nres = sm.cnt;
+        k4_sort(sm.buf, nres, K4_P);
+        res = sm.buf;
     }
-    const int cc = s_cnt;
-    int Ps = 2;
-    while (Ps < cc) Ps <<= 1;
-    for (int j = cc + tid; j < Ps; j += K4_THREADS) buf[j] = KEY_EMPTY;
-    __syncthreads();
-    block_bitonic_sort(buf, Ps);
+
     if (threshold_only) {
         // warm start: the k-th smallest distance over a sample of the rows bounds the final one
-        if (tid == 0 && cc >= p.k) atomicMin(p.gts + qi, (unsigned int)(buf[p.k - 1] >> 32));
+        if (tid == 0 && nres >= k) atomicMin(p.gts + qi, (unsigned int)(res[k - 1] >> 32));
         return;
     }
-    for (int j = tid; j < p.k; j += K4_THREADS) {
-        if (j < cc) {
-            D[qi * p.k + j] = key_dist(buf[j]);
-            I[qi * p.k + j] = (int64_t)key_row(buf[j]);
+    for (int j = tid; j < k; j += K4_THREADS) {
+        if (j < nres) {
+            D[qi * k + j] = key_dist(res[j]);
+            I[qi * k + j] = (int64_t)key_row(res[j]);
         } else {
-            D[qi * p.k + j] = FLT_MAX;
-            I[qi * p.k + j] = -1;
+            D[qi * k + j] = FLT_MAX;
+            I[qi * k + j] = -1;
         }
     }
 }
@@ -694,6 +752,7 @@ int k3_search(K3State* s, const float* x, const float* xlo, const float* norms, 
     count_launch();
     B2K_CUDA(cudaGetLastError());
 
+    B2K_CUDA(cudaFuncSetAttribute(k4_merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(K4Smem)));
     CUtensorMap mq, mql, mx, mxl;
     if ((rc = make_map(s, &mq, q, nq, d, K3_BM))) return rc;
     if ((rc = make_map(s, &mql, qlo, nq, d, K3_BM))) return rc;
@@ -709,6 +768,9 @@ int k3_search(K3State* s, const float* x, const float* xlo, const float* norms, 
     const int nclusters = L.ncta / L.cg;
     const bool sep = s->sep_mode == 1 || (s->sep_mode == 0 && d >= 512);
     const int cols_a = 64;
+    // the first bound only needs ~2048 sampled rows: read every step_a-th list, as long as k of them exist
+    int step_a = nclusters / 32 > 0 ? nclusters / 32 : 1;
+    while (step_a > 1 && (int64_t)(nclusters / step_a) * cols_a < 4 * (int64_t)k) --step_a;
     if (ntiles >= 2 * (int64_t)nclusters && (int64_t)nclusters * cols_a >= 2 * (int64_t)k) {
         K3Params pre = p;
         pre.static_mode = 1;
@@ -719,7 +781,7 @@ int k3_search(K3State* s, const float* x, const float* xlo, const float* norms, 
         pre.n = (int64_t)nclusters * K3_BN;
         rc = launch_k3_any(L.cg, L.P, sep, mq, mql, mx, mxl, pre, L.ncta, st);
         if (rc) return rc;
-        k4_merge_kernel<<<(unsigned)nq, K4_THREADS, 0, st>>>(pre, L.cg, L.ncta, 1, nullptr, nullptr);
+        k4_merge_kernel<<<(unsigned)nq, K4_THREADS, sizeof(K4Smem), st>>>(pre, L.cg, L.ncta, 1, step_a, nullptr, nullptr);
         k3_init_kernel<<<(unsigned)((nslots + 255) / 256), 256, 0, st>>>(nslots, p.cnt, p.tau, p.kth, nq, nullptr, p.next_unit);
         count_launch(2);
         B2K_CUDA(cudaGetLastError());
@@ -736,7 +798,7 @@ int k3_search(K3State* s, const float* x, const float* xlo, const float* norms, 
             pre.nunits = (int64_t)nclusters * (tpc + 1) * L.nqb;
             rc = launch_k3_any(L.cg, L.P, sep, mq, mql, mx, mxl, pre, L.ncta, st);
             if (rc) return rc;
-            k4_merge_kernel<<<(unsigned)nq, K4_THREADS, 0, st>>>(pre, L.cg, L.ncta, 1, nullptr, nullptr);
+            k4_merge_kernel<<<(unsigned)nq, K4_THREADS, sizeof(K4Smem), st>>>(pre, L.cg, L.ncta, 1, 1, nullptr, nullptr);
             k3_init_kernel<<<(unsigned)((nslots + 255) / 256), 256, 0, st>>>(nslots, p.cnt, p.tau, p.kth, nq, nullptr, p.next_unit);
             count_launch(2);
             B2K_CUDA(cudaGetLastError());
@@ -748,7 +810,7 @@ int k3_search(K3State* s, const float* x, const float* xlo, const float* norms, 
     if (rc) return rc;
     if (s->timing) { B2K_CUDA(cudaEventRecord(s->ev1, st)); s->timed = true; }
 
-    k4_merge_kernel<<<(unsigned)nq, K4_THREADS, 0, st>>>(p, L.cg, L.ncta, 0, D, I);
+    k4_merge_kernel<<<(unsigned)nq, K4_THREADS, sizeof(K4Smem), st>>>(p, L.cg, L.ncta, 0, 1, D, I);
     count_launch();
     B2K_CUDA(cudaGetLastError());
     return B2K_OK;
