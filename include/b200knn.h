@@ -132,7 +132,7 @@ B2K_API int b2k_search_rows_noalloc(int device, const float* x_dev, int64_t n, i
                                     int64_t* I_dev, void* stream);
 
 /* Tuning / test hooks.  Keys: "path" (0 auto, 1 force the scan kernel, 2 force the
- * tensor-core kernel), "scan_ctas_per_sm", "timing" (0/1), "tensor_cta_group" (1 or 2),
+ * tensor-core kernel), "scan_ctas_per_sm", "timing" (0/1), "tensor_cta_group" (0 auto, 1, 2),
  * "tensor_sep_accum" (0 auto, 1 on, 2 off).  Unknown key -> B2K_EINVAL. */
 B2K_API int b2k_set_option(b2k_index* h, const char* key, int64_t value);
 

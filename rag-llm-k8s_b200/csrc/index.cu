@@ -280,7 +280,7 @@ int b2k_set_option(b2k_index* h, const char* key, int64_t value) {
         if (value < 1 || value > 8) { set_error("option scan_ctas_per_sm must be 1..8"); return B2K_EINVAL; }
         h->opt_scan_ctas_per_sm = (int)value;
     } else if (!strcmp(key, "tensor_cta_group")) {
-        if (value != 1 && value != 2) { set_error("option tensor_cta_group must be 1 or 2"); return B2K_EINVAL; }
+        if (value < 0 || value > 2) { set_error("option tensor_cta_group must be 0 (auto), 1 or 2"); return B2K_EINVAL; }
         h->opt_cta_group = (int)value;
         if (h->k3) k3_set_cta_group(h->k3, h->opt_cta_group);
     } else if (!strcmp(key, "tensor_sep_accum")) {
@@ -455,7 +455,7 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
             if (!h->k3) {
                 rc = k3_create(&h->k3, h->device, h->sm_count);
                 if (!rc) k3_set_timing(h->k3, h->opt_timing != 0);
-                if (!rc && h->opt_cta_group) k3_set_cta_group(h->k3, h->opt_cta_group);
+                if (!rc) k3_set_cta_group(h->k3, h->opt_cta_group);
                 if (!rc) k3_set_sep_mode(h->k3, h->opt_sep);
             }
             if (!rc) h->last_path = 2;

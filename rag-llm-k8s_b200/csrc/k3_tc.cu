@@ -143,11 +143,12 @@ __device__ __forceinline__ void k3_filter_chunk(const uint32_t (&v)[32], const u
 // double buffering (the MMAs of the next tile wait for the epilogue), so it is used for long
 // rows (d >= 512) where the relative cost is a few percent and the error would otherwise
 // exceed 1e-5 of ||q||^2 + ||x||^2 on near-duplicate unit-norm vectors.
-template <int CG, int NS, bool SEP>
+template <int CG, int NS, int MODE>
 __global__ void __launch_bounds__(K3_THREADS, 1)
 k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_ql,
                       const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_xl,
                       const K3Params p) {
+    constexpr bool SEP = (MODE == 1);  // separate accumulator for the cross terms
     using L = K3Smem<CG, NS>;
     extern __shared__ unsigned char smem_raw[];
     unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -577,7 +578,7 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
-static int g_default_cg = 1;  // until the CTA-pair configuration is validated on hardware
+static int g_default_cg = 0;  // 0 = choose per search (k3_cg_for)
 
 struct K3State {
     int device = 0, sm_count = 148;
@@ -585,13 +586,18 @@ struct K3State {
     EncodeTiledFn encode = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     bool timing = false;
-    int sep_mode = 0;  // 0 auto (d >= 512), 1 always, 2 never
+    int sep_mode = 0;  // long-row accuracy: 0 auto (d >= 512: separate accumulator), 1 separate accumulator, 2 off
     bool timed = false;
 };
 
 static int k3_P(int k) { return next_pow2(k + K3_BN); }
 // CG = 1 has shared memory for compaction scratch up to 512 keys per warp; CG = 2 up to 2048.
-static int k3_cg_for(int k, int want) { return (want == 2 || k3_P(k) > 512) ? 2 : 1; }
+// Auto: CTA pairs for long rows (measured faster at d = 1024: 815 vs 782 TFLOP/s) and for long lists.
+static int k3_cg_for(int k, int want, int d) {
+    if (k3_P(k) > 512) return 2;
+    if (want == 1 || want == 2) return want;
+    return d >= 512 ? 2 : 1;
+}
 
 bool k3_supported(int d, int k) {
     // TMA needs a 16-byte row pitch
@@ -607,7 +613,7 @@ struct K3Layout {
 
 static K3Layout k3_layout(int sm_count, int d, int64_t nq, int k, int want_cg) {
     K3Layout L;
-    L.cg = k3_cg_for(k, want_cg);
+    L.cg = k3_cg_for(k, want_cg, d);
     L.ncta = (sm_count / L.cg) * L.cg;
     L.nqb = (int)((nq + K3_BM * L.cg - 1) / (K3_BM * L.cg));
     L.qpc = L.nqb * K3_BM;
@@ -662,7 +668,7 @@ void k3_destroy(K3State* s) {
 void k3_invalidate_maps(K3State*) {}  // maps are re-encoded on every search (host-side, ~1 us each)
 
 void k3_set_timing(K3State* s, bool on) { s->timing = on; }
-void k3_set_cta_group(K3State* s, int cg) { s->cg = cg == 2 ? 2 : 1; }
+void k3_set_cta_group(K3State* s, int cg) { s->cg = (cg == 1 || cg == 2) ? cg : 0; }
 void k3_set_sep_mode(K3State* s, int m) { s->sep_mode = m; }
 
 int k3_last_kernel_ms(K3State* s, float* ms) {
@@ -687,11 +693,11 @@ static int make_map(K3State* s, CUtensorMap* m, const float* base, int64_t rows,
     return B2K_OK;
 }
 
-template <int CG, int NS, bool SEP>
+template <int CG, int NS, int MODE>
 static int launch_k3(const CUtensorMap& mq, const CUtensorMap& mql, const CUtensorMap& mx, const CUtensorMap& mxl,
                      const K3Params& p, int ncta, cudaStream_t st) {
     size_t smem = K3Smem<CG, NS>::bytes(p.P);
-    B2K_CUDA(cudaFuncSetAttribute(k3_tf32x3_topk_kernel<CG, NS, SEP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    B2K_CUDA(cudaFuncSetAttribute(k3_tf32x3_topk_kernel<CG, NS, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(ncta);
     cfg.blockDim = dim3(K3_THREADS);
@@ -704,21 +710,25 @@ static int launch_k3(const CUtensorMap& mq, const CUtensorMap& mql, const CUtens
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    B2K_CUDA(cudaLaunchKernelEx(&cfg, k3_tf32x3_topk_kernel<CG, NS, SEP>, mq, mql, mx, mxl, p));
+    B2K_CUDA(cudaLaunchKernelEx(&cfg, k3_tf32x3_topk_kernel<CG, NS, MODE>, mq, mql, mx, mxl, p));
     count_launch();
     return B2K_OK;
 }
 
-static int launch_k3_any(int cg, int P, bool sep, const CUtensorMap& mq, const CUtensorMap& mql, const CUtensorMap& mx,
+static int launch_k3_any(int cg, int P, int mode, const CUtensorMap& mq, const CUtensorMap& mql, const CUtensorMap& mx,
                          const CUtensorMap& mxl, const K3Params& p, int ncta, cudaStream_t st) {
-    if (sep) {
-        if (cg == 1) return launch_k3<1, 2, true>(mq, mql, mx, mxl, p, ncta, st);
-        if (P <= 512) return launch_k3<2, 3, true>(mq, mql, mx, mxl, p, ncta, st);
-        return launch_k3<2, 2, true>(mq, mql, mx, mxl, p, ncta, st);
+#define B2K_K3_CASE(MODE_)                                                                        \
+    case MODE_:                                                                                   \
+        if (cg == 1) return launch_k3<1, 2, MODE_>(mq, mql, mx, mxl, p, ncta, st);                \
+        if (P <= 512) return launch_k3<2, 3, MODE_>(mq, mql, mx, mxl, p, ncta, st);               \
+        return launch_k3<2, 2, MODE_>(mq, mql, mx, mxl, p, ncta, st);
+    switch (mode) {
+        B2K_K3_CASE(0)
+        B2K_K3_CASE(1)
     }
-    if (cg == 1) return launch_k3<1, 2, false>(mq, mql, mx, mxl, p, ncta, st);
-    if (P <= 512) return launch_k3<2, 3, false>(mq, mql, mx, mxl, p, ncta, st);
-    return launch_k3<2, 2, false>(mq, mql, mx, mxl, p, ncta, st);
+#undef B2K_K3_CASE
+    set_error("tensor kernel: bad accumulator mode %d", mode);
+    return B2K_EINVAL;
 }
 
 int k3_search(K3State* s, const float* x, const float* xlo, const float* norms, int64_t n, int64_t capacity, int d,
@@ -766,7 +776,8 @@ int k3_search(K3State* s, const float* x, const float* xlo, const float* norms, 
     // tightened again.  The full pass then prunes from its first tile: its lists stay far below
     // capacity (no compaction sorts) and K4 has a few k keys per query to merge.
     const int nclusters = L.ncta / L.cg;
-    const bool sep = s->sep_mode == 1 || (s->sep_mode == 0 && d >= 512);
+    // accumulator mode: 0 one accumulator (double-buffered), 1 separate cross-term accumulator
+    const int sep = (s->sep_mode == 1 || (s->sep_mode == 0 && d >= 512)) ? 1 : 0;
     const int cols_a = 64;
     // the first bound only needs ~2048 sampled rows: read every step_a-th list, as long as k of them exist
     int step_a = nclusters / 32 > 0 ? nclusters / 32 : 1;
