@@ -119,8 +119,9 @@ extern "C" int b2k_search_rows_noalloc(int device, const float* x_dev, int64_t n
         for (int64_t q0 = 0; q0 < nq && !rc;) {
             int qt = scan_pick_qt(nq - q0, kk);
             while (qt > 1 && (size_t)grid * qt * kk > max_keys) qt >>= 1;
-            // the ticket must start at zero; the lists need no clearing (each CTA rewrites its slots)
-            e = cudaMemsetAsync(ticket, 0, sizeof(unsigned int), st);
+            // the ticket and the work counter must start at zero; the lists need no clearing (each CTA
+            // rewrites its slots)
+            e = cudaMemsetAsync(ticket, 0, 2 * sizeof(unsigned int), st);
             if (e != cudaSuccess) { set_error("b2k_search_rows_noalloc: %s", cudaGetErrorString(e)); rc = B2K_ECUDA; break; }
             rc = launch_scan(x_dev, q_dev + q0 * (int64_t)d, n, d, qt, kk, grid, lists, ticket, D_dev + q0 * kk,
                              I_dev + q0 * kk, st);
