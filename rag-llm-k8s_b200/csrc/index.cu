@@ -55,7 +55,7 @@ struct b2k_index {
     size_t pin_bytes = 0;
     unsigned int* done = nullptr;
     int opt_path = 0;
-    int opt_scan_ctas_per_sm = 3;  // = resident CTAs/SM of the scan kernel (78 registers x 256 threads)
+    int opt_scan_ctas_per_sm = 4;  // upper bound; each variant is clamped to its own residency (64 regs x 256 threads -> 4)
     int opt_timing = 0;
     int opt_cta_group = 0;  // 0 = library default
     int opt_sep = 0;

@@ -128,13 +128,24 @@ scan_l2_topk_kernel(const float* __restrict__ X, const float* __restrict__ Q, in
                 int64_t rr = rows[u] < row_end ? rows[u] : row_begin;  // clamp: load something valid
                 rp[u] = X + rr * (int64_t)d + cl;
             }
-#pragma unroll 2
-            for (int c0 = 0; c0 < d; c0 += 32) {
-                const bool cok = (c0 + cl) < d;
-                float4 xv[4];
+            // software pipeline: the row segments of the next 32 columns are in flight while the
+            // current ones are consumed (the loop is otherwise load -> wait -> compute per warp,
+            // and the per-iteration barrier keeps the warps of a CTA in step)
+            float4 xv[4];
+            {
+                const bool cok0 = cl < d;
 #pragma unroll
                 for (int u = 0; u < 4; ++u)
-                    xv[u] = cok ? ldg_stream(reinterpret_cast<const float4*>(rp[u] + c0)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    xv[u] = cok0 ? ldg_stream(reinterpret_cast<const float4*>(rp[u])) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+#pragma unroll 1
+            for (int c0 = 0; c0 < d; c0 += 32) {
+                const bool cok = (c0 + cl) < d;
+                const bool nok = (c0 + 32 + cl) < d;
+                float4 xn[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                    xn[u] = nok ? ldg_stream(reinterpret_cast<const float4*>(rp[u] + c0 + 32)) : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
                 for (int q = 0; q < QT; ++q) {
                     float4 qv = cok ? *reinterpret_cast<const float4*>(s.qs + q * dq + c0 + cl)
@@ -148,6 +159,8 @@ scan_l2_topk_kernel(const float* __restrict__ X, const float* __restrict__ Q, in
                         acc[u][q] = fmaf(e, e, acc[u][q]);
                     }
                 }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) xv[u] = xn[u];
             }
 #pragma unroll
             for (int u = 0; u < 4; ++u)
