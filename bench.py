@@ -311,6 +311,7 @@ def main():
             roof["traffic"] = tj["bytes_per_launch"]
             roof["traffic_source"] = tj["source"]
     roof["frac"] = roof["achieved"] / roof["peak"]
+    roof["scope"] = "one GPU (rank 0's shard of %d rows)" % n_local if world > 1 else "the one GPU"
     # single-query scan (the HBM-bound path) on the same index
     t_nq1 = p50_nq1_kernel or p50_nq1
     roof_nq1 = {"bound": "hbm", "kernel": "scan_l2_topk_kernel", "achieved": n_local * d * 4 / (t_nq1 * 1e-3) / 1e9,

@@ -457,3 +457,33 @@ def test_adversarial_row_order(faiss):
         D, I = idx.search(q, 10)
         assert_knn_matches(D, I, x, q, 10, expanded=(path == 2), what="adversarial path=%d" % path)
         assert I.min() >= n - 200                                       # the neighbours are the last rows
+
+
+def test_concurrent_searches_from_threads(faiss):
+    """Flask's dev server is threaded (rag.py:204) and builds an index object per request
+    (rag.py:153): independent handles must not interfere, and concurrent searches on ONE handle
+    (the resident-index cache hands the same object to every request) must be safe."""
+    import threading
+    x = O.synth(1234, 0, 50000, 128)
+    shared = _build(faiss, x)
+    qs = [O.synth(100 + t, 0, 3 if t % 2 else 40, 128) for t in range(8)]
+    refs = [O.search(x, q, 5) for q in qs]
+    errors = []
+
+    def worker(t):
+        try:
+            own = _build(faiss, x[: 20000 + 1000 * t])
+            for _ in range(5):
+                D, I = shared.search(qs[t], 5)
+                assert_knn_matches(D, I, x, qs[t], 5, refs[t][0], refs[t][1], expanded=qs[t].shape[0] >= 20, what="shared t=%d" % t)
+                D, I = own.search(qs[t], 5)
+                assert_knn_matches(D, I, x[: 20000 + 1000 * t], qs[t], 5, expanded=qs[t].shape[0] >= 20, what="own t=%d" % t)
+        except Exception as e:  # noqa: BLE001
+            errors.append((t, repr(e)))
+
+    threads = [threading.Thread(target=worker, args=(t,)) for t in range(8)]
+    for th in threads:
+        th.start()
+    for th in threads:
+        th.join()
+    assert not errors, errors
