@@ -487,3 +487,18 @@ def test_concurrent_searches_from_threads(faiss):
     for th in threads:
         th.join()
     assert not errors, errors
+
+
+@pytest.mark.parametrize("n", [1, 5, 255, 256, 257, 1000])
+@pytest.mark.parametrize("d", [4, 36, 128])
+def test_tensor_path_small_and_ragged(faiss, n, d):
+    """Batched (tensor-core) search on tiny and ragged shapes: fewer rows than one tile, fewer
+    rows than k (padding), row and column counts that are not multiples of the tile."""
+    x = O.synth(41, 0, n, d)
+    q = O.synth(42, 0, 21, d)
+    idx = _build(faiss, x)
+    D, I = idx.search(q, 10)
+    assert idx.stats()["path"] == "tensor"
+    Dr, Ir = O.search(x, q, 10)
+    assert np.array_equal(I < 0, Ir < 0)
+    assert_knn_matches(D, I, x, q, 10, Dr, Ir, expanded=True, what="n=%d d=%d" % (n, d))
