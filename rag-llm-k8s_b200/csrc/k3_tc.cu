@@ -81,7 +81,7 @@ struct K3Smem {
     static constexpr int OFF_SCHED = OFF_BAR + NBAR * 8;       // long long[K3_NSCHED]
     static constexpr int OFF_TMEM = OFF_SCHED + K3_NSCHED * 8;
     static constexpr int OFF_SCRATCH = (OFF_TMEM + 16 + 15) & ~15;  // 4 warps x P keys
-    static size_t bytes(int P) { return (size_t)OFF_SCRATCH + (size_t)4 * P * 8 + 1024; }
+    static size_t bytes(int P) { return (size_t)OFF_SCRATCH + (size_t)4 * P * 8; }
 };
 
 // Consumer side of the unit-id ring: wait for slot `ss`, read the unit, release the slot to the
@@ -98,6 +98,29 @@ __device__ __forceinline__ long long sched_take_warp(uint64_t* sfull, uint64_t* 
         else ptx::mbar_arrive_cluster(&sempty[ss], 0);
     }
     return u;
+}
+
+// Compiler fence on 32 registers: placed right after the NEXT chunk's tcgen05.ld has been issued, it
+// pins every use of `v` below that point, so the filter of this chunk cannot be scheduled above
+// the prefetch (nvcc otherwise sinks the prefetch under the filter and each chunk pays the full
+// TMEM round trip, ~1.8k cycles measured).
+__device__ __forceinline__ void reg_fence32(uint32_t (&v)[32]) {
+    asm volatile("" : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]),
+                      "+r"(v[8]), "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15]),
+                      "+r"(v[16]), "+r"(v[17]), "+r"(v[18]), "+r"(v[19]), "+r"(v[20]), "+r"(v[21]), "+r"(v[22]), "+r"(v[23]),
+                      "+r"(v[24]), "+r"(v[25]), "+r"(v[26]), "+r"(v[27]), "+r"(v[28]), "+r"(v[29]), "+r"(v[30]), "+r"(v[31])
+                 :: "memory");
+}
+
+// v[c] for a run-time c, without local memory: a binary tree of selects over the 32 registers.
+template <int LO, int N>
+__device__ __forceinline__ float reg_select32(const float (&v)[32], int c) {
+    if constexpr (N == 1) {
+        return v[LO];
+    } else {
+        const float a = reg_select32<LO, N / 2>(v, c), b = reg_select32<LO + N / 2, N / 2>(v, c);
+        return (c & (N / 2)) ? b : a;
+    }
 }
 
 // One thread, 32 consecutive accumulator columns of its query row: branch-free filter, then the
@@ -119,18 +142,20 @@ __device__ __forceinline__ void k3_filter_chunk(const uint32_t (&v)[32], const u
             mask |= (s <= t_cmp) ? (1u << (c + j)) : 0u;
         }
     }
-    if (mask) {
-#pragma unroll
-        for (int c = 0; c < 32; ++c) {
-            if (mask & (1u << c)) {
-                const float xv = xn[c];
-                float dist = (qn + xv) - 2.f * ip[c];  // oracle rule (2), then clamp
-                dist = dist < 0.f ? 0.f : dist;
-                if (dist <= tau_eff) {
-                    const u64 key = make_key(dist, row0 + c);
-                    if (key < kth) { list[cnt] = key; ++cnt; }
-                }
-            }
+    // Survivors.  With warm-started thresholds a THREAD sees one every few tiles, but a WARP (32
+    // threads x 32 columns) sees one in most chunks, so this path must be cheap at warp level: a
+    // loop over the set bits (usually one trip for the whole warp), the value picked out of the
+    // registers by a 5-level select tree -- not 32 predicated copies of the body.
+    while (mask) {
+        const int c = __ffs(mask) - 1;
+        mask &= mask - 1;
+        const float ipc = reg_select32<0, 32>(ip, c);
+        const float xv = xn[c];
+        float dist = (qn + xv) - 2.f * ipc;  // oracle rule (2), then clamp
+        dist = dist < 0.f ? 0.f : dist;
+        if (dist <= tau_eff) {
+            const u64 key = make_key(dist, row0 + c);
+            if (key < kth) { list[cnt] = key; ++cnt; }
         }
     }
 }
@@ -150,8 +175,13 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
                       const K3Params p) {
     constexpr bool SEP = (MODE == 1);  // separate accumulator for the cross terms
     using L = K3Smem<CG, NS>;
-    extern __shared__ unsigned char smem_raw[];
-    unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    // No integer round-trip on this pointer: the compiler must keep seeing shared memory here, or
+    // every access through it becomes a generic LD/ST (that cost 2k cycles per 32 accumulator
+    // columns in the epilogue).  The kernel has no static shared memory, so the dynamic window
+    // starts 1024-aligned (SWIZZLE_128B needs that); checked below.
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    unsigned char* smem = smem_raw;
+    if ((ptx::smem_u32(smem) & 1023u) != 0) __trap();
     float* xn_s = reinterpret_cast<float*>(smem + L::OFF_XN);
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + L::OFF_BAR);
     uint64_t* empty = full + NS;
@@ -330,12 +360,16 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
                 ptx::tmem_ld_wait();
                 ptx::tmem_ld_32x32(taddr + c0 + 32, vb);
                 if (SEP) ptx::tmem_ld_32x32(taddr + K3_BN + c0 + 32, wb);
+                reg_fence32(va);
+                if (SEP) reg_fence32(wa);
                 k3_filter_chunk<SEP>(va, wa, xn + c0, t_cmp, qn, tau_eff, kth, row_base + c0, list, cnt);
                 ptx::tmem_ld_wait();
                 if (c0 + 64 < K3_BN) {
                     ptx::tmem_ld_32x32(taddr + c0 + 64, va);
                     if (SEP) ptx::tmem_ld_32x32(taddr + K3_BN + c0 + 64, wa);
                 }
+                reg_fence32(vb);
+                if (SEP) reg_fence32(wb);
                 k3_filter_chunk<SEP>(vb, wb, xn + c0 + 32, t_cmp, qn, tau_eff, kth, row_base + c0 + 32, list, cnt);
             }
             // accumulator drained: hand it back to the MMA warp (of the leader CTA)
