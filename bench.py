@@ -289,13 +289,19 @@ def main():
     n_local = N // world if world > 1 else N
     if stats.get("path") == "tensor":
         k_ms = stats["main_kernel_ms"]
-        flops = 3 * 2.0 * nq * n_local * d
+        screen = stats.get("tensor_mode") == "screen+rerank"
+        nprod = 1 if screen else 3
+        flops = nprod * 2.0 * nq * n_local * d
         peak = pk["bf16_sus"] / 2.0
-        roof = {"bound": "tensor", "kernel": "k3_tf32x3_topk", "achieved": flops / (k_ms * 1e-3) / 1e12, "peak": peak,
+        roof = {"bound": "tensor", "kernel": "k3_tf32x3_topk", "tensor_mode": stats.get("tensor_mode"),
+                "screen_fallbacks": stats.get("screen_fallbacks"),
+                "achieved": flops / (k_ms * 1e-3) / 1e12, "peak": peak,
                 "unit": "TFLOP/s", "traffic": None, "launch_ms": k_ms,
                 "peak_source": "%s bf16 sustained / 2 (TF32 dense; derived, MEASURED_PEAKS.json has no TF32 row)" % pk["source"],
-                "algorithmic": "executed tensor flops = 3 (3xTF32) * 2*nq*N*d per launch",
-                "fp32_equivalent_tflops": flops / 3 / (k_ms * 1e-3) / 1e12, "tf32_cublas_measured": tf32_meas}
+                "algorithmic": "executed tensor flops = %d * 2*nq*N*d per launch (%s)" % (
+                    nprod, "one TF32 product; exact distances come from the fp32 re-rank of the rows inside its error slack"
+                    if screen else "3xTF32"),
+                "fp32_equivalent_tflops": 2.0 * nq * n_local * d / (k_ms * 1e-3) / 1e12, "tf32_cublas_measured": tf32_meas}
     else:
         per_launch_ms = (stats["main_kernel_ms"] / max(stats.get("launches", 1), 1)) if stats.get("main_kernel_ms") \
             else ms_dev / max(launches, 1)

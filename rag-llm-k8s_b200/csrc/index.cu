@@ -59,6 +59,8 @@ struct b2k_index {
     int opt_timing = 0;
     int opt_cta_group = 0;  // 0 = library default
     int opt_sep = 0;
+    int opt_tensor_mode = 0;  // 0 auto (screening + exact re-rank), 1 3xTF32, 2 screening
+    int64_t stat_screen_fallbacks = 0;
     int last_path = 0;
     int sticky = 0;
     K3State* k3 = nullptr;
@@ -71,6 +73,7 @@ struct b2k_index {
 
 static constexpr int64_t MAX_ROWS = 0xFFFFFFFEll;  // row index lives in the low 32 bits of a key
 static constexpr size_t IO_CHUNK = (size_t)64 << 20;
+static constexpr int MAX_NORM_SLOT = 2;  // h->done[0] ticket, [1] scan work counter, [2] bits of the largest squared row norm
 static constexpr int64_t TC_QUERY_CHUNK = 4096;  // queries per tensor-core pass (faiss: distance_compute_blas_query_bs)
 
 namespace {
@@ -176,7 +179,7 @@ int grow(b2k_index* h, int64_t need_rows) {
 // Rows [first, first+n) of h->x are in place: compute their norms (and residual rows).
 int prep_new_rows(b2k_index* h, int64_t first, int64_t n, cudaStream_t st) {
     return launch_row_prep(h->x + first * (int64_t)h->d, n, h->d, h->norms + first,
-                           h->lo_enabled ? h->xlo + first * (int64_t)h->d : nullptr, st);
+                           h->lo_enabled ? h->xlo + first * (int64_t)h->d : nullptr, h->done + MAX_NORM_SLOT, st);
 }
 
 int enable_lo(b2k_index* h, cudaStream_t st) {
@@ -187,7 +190,7 @@ int enable_lo(b2k_index* h, cudaStream_t st) {
     }
     h->lo_enabled = true;
     if (h->k3) k3_invalidate_maps(h->k3);
-    if (h->ntotal > 0) return launch_row_prep(h->x, h->ntotal, h->d, h->norms, h->xlo, st);
+    if (h->ntotal > 0) return launch_row_prep(h->x, h->ntotal, h->d, h->norms, h->xlo, nullptr, st);
     return B2K_OK;
 }
 
@@ -287,6 +290,9 @@ int b2k_set_option(b2k_index* h, const char* key, int64_t value) {
         if (value < 0 || value > 2) { set_error("option tensor_sep_accum must be 0 (auto), 1 (on) or 2 (off)"); return B2K_EINVAL; }
         h->opt_sep = (int)value;
         if (h->k3) k3_set_sep_mode(h->k3, h->opt_sep);
+    } else if (!strcmp(key, "tensor_mode")) {
+        if (value < 0 || value > 2) { set_error("option tensor_mode must be 0 (auto), 1 (3xTF32) or 2 (screening + exact re-rank)"); return B2K_EINVAL; }
+        h->opt_tensor_mode = (int)value;
     } else if (!strcmp(key, "timing")) {
         h->opt_timing = value != 0;
         if (h->k3) k3_set_timing(h->k3, h->opt_timing != 0);
@@ -301,6 +307,8 @@ int b2k_get_stat(b2k_index* h, const char* key, double* out) {
     if (!h || !key || !out) { set_error("b2k_get_stat: null argument"); return B2K_EINVAL; }
     std::lock_guard<std::mutex> lk(h->mu);
     if (!strcmp(key, "last_path")) { *out = h->last_path; return B2K_OK; }
+    if (!strcmp(key, "tensor_mode_used")) { *out = h->k3 ? k3_last_mode(h->k3) : 0; return B2K_OK; }
+    if (!strcmp(key, "screen_fallbacks")) { *out = (double)h->stat_screen_fallbacks; return B2K_OK; }
     if (!strcmp(key, "tensor_kernel_ms")) {
         float ms = 0.f;
         if (!h->k3 || k3_last_kernel_ms(h->k3, &ms)) { set_error("no timed tensor-core kernel yet (set option timing=1)"); return B2K_EINVAL; }
@@ -337,6 +345,7 @@ int b2k_reset(b2k_index* h) {
     h->x = h->norms = h->xlo = nullptr;
     h->ntotal = h->capacity = 0;
     if (h->k3) k3_invalidate_maps(h->k3);
+    B2K_CUDA(cudaMemset(h->done, 0, 256));
     return B2K_OK;
 }
 
@@ -450,21 +459,29 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
     if (h->ntotal == 0) {
         rc = launch_fill_empty(Dd, Id, nq * kk, st);
     } else if (want_tc) {
-        rc = enable_lo(h, st);
-        if (!rc) {
-            if (!h->k3) {
-                rc = k3_create(&h->k3, h->device, h->sm_count);
-                if (!rc) k3_set_timing(h->k3, h->opt_timing != 0);
-                if (!rc) k3_set_cta_group(h->k3, h->opt_cta_group);
-                if (!rc) k3_set_sep_mode(h->k3, h->opt_sep);
-            }
-            if (!rc) h->last_path = 2;
-            // like faiss (query blocks of 4096), long batches go through in chunks: the candidate-list
-            // scratch is sized per chunk and one pass over the rows per chunk is still compute-bound
-            for (int64_t q0 = 0; q0 < nq && !rc; q0 += TC_QUERY_CHUNK) {
-                const int64_t nqc = nq - q0 < TC_QUERY_CHUNK ? nq - q0 : TC_QUERY_CHUNK;
-                rc = k3_search(h->k3, h->x, h->xlo, h->norms, h->ntotal, h->capacity, h->d, qd + q0 * (int64_t)h->d, nqc,
-                               kk, Dd + q0 * kk, Id + q0 * kk, ws_tail, st);
+        const bool screen = h->opt_tensor_mode != 1;
+        if (!screen) rc = enable_lo(h, st);
+        if (!rc && !h->k3) {
+            rc = k3_create(&h->k3, h->device, h->sm_count);
+            if (!rc) k3_set_timing(h->k3, h->opt_timing != 0);
+            if (!rc) k3_set_cta_group(h->k3, h->opt_cta_group);
+            if (!rc) k3_set_sep_mode(h->k3, h->opt_sep);
+        }
+        if (!rc) h->last_path = 2;
+        // like faiss (query blocks of 4096), long batches go through in chunks: the candidate-list
+        // scratch is sized per chunk and one pass over the rows per chunk is still compute-bound
+        for (int64_t q0 = 0; q0 < nq && !rc; q0 += TC_QUERY_CHUNK) {
+            const int64_t nqc = nq - q0 < TC_QUERY_CHUNK ? nq - q0 : TC_QUERY_CHUNK;
+            int overflowed = 0;
+            rc = k3_search(h->k3, h->x, h->xlo, h->norms, h->done + MAX_NORM_SLOT, h->ntotal, h->capacity, h->d,
+                           qd + q0 * (int64_t)h->d, nqc, kk, Dd + q0 * kk, Id + q0 * kk, ws_tail, st, screen ? 0 : 1,
+                           &overflowed);
+            if (!rc && overflowed) {
+                // masses of near-duplicates around the k-th neighbour: repeat this chunk with 3xTF32
+                ++h->stat_screen_fallbacks;
+                rc = enable_lo(h, st);
+                if (!rc) rc = k3_search(h->k3, h->x, h->xlo, h->norms, h->done + MAX_NORM_SLOT, h->ntotal, h->capacity, h->d,
+                                        qd + q0 * (int64_t)h->d, nqc, kk, Dd + q0 * kk, Id + q0 * kk, ws_tail, st, 1, nullptr);
             }
         }
     } else {

@@ -18,11 +18,21 @@ __device__ __forceinline__ float tf32_residual(float x) {
     return x - hi;  // exact: at most 13 significant bits
 }
 
+// Largest finite squared norm seen, kept as float bits (non-negative floats order like unsigned
+// integers): one atomic per warp.  The tensor-core screening pass sizes its error slack with it.
+__device__ __forceinline__ void publish_max(float vmax, unsigned int* max_norm_bits, int lane) {
+    if (!max_norm_bits) return;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) vmax = fmaxf(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
+    if (lane == 0 && vmax > 0.f) atomicMax(max_norm_bits, __float_as_uint(vmax));
+}
+
 // 8 lanes per row (128 B per request), 4 rows per warp; d % 4 == 0 path.
 __global__ void __launch_bounds__(256)
 row_prep_vec_kernel(const float* __restrict__ X, int64_t n, int d, float* __restrict__ norms,
-                    float* __restrict__ xlo) {
+                    float* __restrict__ xlo, unsigned int* __restrict__ max_norm_bits) {
     const int lane = threadIdx.x & 31;
+    float vmax = 0.f;
     const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
     const int g = lane >> 3, cl = (lane & 7) * 4;
@@ -45,14 +55,17 @@ row_prep_vec_kernel(const float* __restrict__ X, int64_t n, int d, float* __rest
         acc += __shfl_xor_sync(0xffffffffu, acc, 2);
         acc += __shfl_xor_sync(0xffffffffu, acc, 4);
         if (row < n && (lane & 7) == 0) norms[row] = acc;
+        if (row < n && acc <= FLT_MAX) vmax = fmaxf(vmax, acc);  // finite norms only (NaN / inf rows never match)
     }
+    publish_max(vmax, max_norm_bits, lane);
 }
 
 // any d: one warp per row.
 __global__ void __launch_bounds__(256)
 row_prep_any_kernel(const float* __restrict__ X, int64_t n, int d, float* __restrict__ norms,
-                    float* __restrict__ xlo) {
+                    float* __restrict__ xlo, unsigned int* __restrict__ max_norm_bits) {
     const int lane = threadIdx.x & 31;
+    float vmax = 0.f;
     const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
     for (int64_t row = warp; row < n; row += nwarps) {
@@ -66,18 +79,21 @@ row_prep_any_kernel(const float* __restrict__ X, int64_t n, int d, float* __rest
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
         if (lane == 0) norms[row] = acc;
+        if (acc <= FLT_MAX) vmax = fmaxf(vmax, acc);
     }
+    publish_max(vmax, max_norm_bits, lane);
 }
 
-int launch_row_prep(const float* X, int64_t n, int d, float* norms, float* xlo, cudaStream_t st) {
+int launch_row_prep(const float* X, int64_t n, int d, float* norms, float* xlo, unsigned int* max_norm_bits,
+                    cudaStream_t st) {
     if (n <= 0) return B2K_OK;
     const bool vec = (d % 4 == 0) && ((reinterpret_cast<uintptr_t>(X) & 15) == 0) &&
                      (xlo == nullptr || (reinterpret_cast<uintptr_t>(xlo) & 15) == 0);
     int64_t rows_per_block = vec ? 32 : 8;
     int64_t blocks = (n + rows_per_block - 1) / rows_per_block;
     if (blocks > 148 * 16) blocks = 148 * 16;
-    if (vec) row_prep_vec_kernel<<<(unsigned)blocks, 256, 0, st>>>(X, n, d, norms, xlo);
-    else row_prep_any_kernel<<<(unsigned)blocks, 256, 0, st>>>(X, n, d, norms, xlo);
+    if (vec) row_prep_vec_kernel<<<(unsigned)blocks, 256, 0, st>>>(X, n, d, norms, xlo, max_norm_bits);
+    else row_prep_any_kernel<<<(unsigned)blocks, 256, 0, st>>>(X, n, d, norms, xlo, max_norm_bits);
     count_launch();
     B2K_CUDA(cudaGetLastError());
     return B2K_OK;

@@ -62,6 +62,8 @@ struct K3Params {
     u64* kth;           // [ncta][qpc]
     u64* cand;          // [ncta][qpc][P]
     u64* next_unit;     // dynamic scheduler: next unit to hand out
+    const float* slack2;     // [nq] screening: 2 * (bound on |approximate - exact distance|) per query
+    unsigned int* overflow;  // screening: set when a list cannot hold every key inside the slack
     int static_mode;    // 1: warm-start pass, CTA (pair) c takes tiles static_tile0 + c*static_tpc + [0,static_tpc), all query blocks
     int static_tpc;
     int tile_cols;      // columns (rows of the tile) the epilogue looks at: 256, or fewer in the first warm-start pass
@@ -70,11 +72,13 @@ struct K3Params {
 
 static constexpr int K3_NSCHED = 4;  // depth of the unit-id ring between the scheduler and the other roles
 
-template <int CG, int NS>
+template <int CG, int NS, int MODE>
 struct K3Smem {
     static constexpr int B_ROWS = K3_BN / CG;
     static constexpr int B_BYTES = B_ROWS * K3_BK * 4;
-    static constexpr int STAGE_BYTES = 2 * K3_A_BYTES + 2 * B_BYTES;
+    static constexpr int NPART = MODE == 2 ? 1 : 2;  // hi only (screening), or hi + lo (3xTF32)
+    static constexpr int OFF_B = NPART * K3_A_BYTES;  // stage = [Q_hi][Q_lo?][X_hi][X_lo?]
+    static constexpr int STAGE_BYTES = NPART * (K3_A_BYTES + B_BYTES);
     static constexpr int OFF_XN = NS * STAGE_BYTES;            // float[2][256]
     static constexpr int OFF_BAR = OFF_XN + 2 * K3_BN * 4;     // full[NS] empty[NS] tfull[2] tempty[2] sfull[4] sempty[4]
     static constexpr int NBAR = 2 * NS + 4 + 2 * K3_NSCHED;
@@ -174,7 +178,8 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
                       const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_xl,
                       const K3Params p) {
     constexpr bool SEP = (MODE == 1);  // separate accumulator for the cross terms
-    using L = K3Smem<CG, NS>;
+    constexpr bool SCREEN = (MODE == 2);  // one TF32 product + error slack; exact distances come from the re-rank kernel
+    using L = K3Smem<CG, NS, MODE>;
     // No integer round-trip on this pointer: the compiler must keep seeing shared memory here, or
     // every access through it becomes a generic LD/ST (that cost 2k cycles per 32 accumulator
     // columns in the epilogue).  The kernel has no static shared memory, so the dynamic window
@@ -255,16 +260,16 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
                     if (CG == 1) {
                         ptx::mbar_arrive_expect_tx(&full[stage], L::STAGE_BYTES);
                         ptx::tma_load_2d(sb, &tm_q, &full[stage], kc * K3_BK, qrow0);
-                        ptx::tma_load_2d(sb + K3_A_BYTES, &tm_ql, &full[stage], kc * K3_BK, qrow0);
-                        ptx::tma_load_2d(sb + 2 * K3_A_BYTES, &tm_x, &full[stage], kc * K3_BK, (int)xrow0);
-                        ptx::tma_load_2d(sb + 2 * K3_A_BYTES + L::B_BYTES, &tm_xl, &full[stage], kc * K3_BK, (int)xrow0);
+                        if (!SCREEN) ptx::tma_load_2d(sb + K3_A_BYTES, &tm_ql, &full[stage], kc * K3_BK, qrow0);
+                        ptx::tma_load_2d(sb + L::OFF_B, &tm_x, &full[stage], kc * K3_BK, (int)xrow0);
+                        if (!SCREEN) ptx::tma_load_2d(sb + L::OFF_B + L::B_BYTES, &tm_xl, &full[stage], kc * K3_BK, (int)xrow0);
                     } else {
                         if (rank == 0) ptx::mbar_arrive_expect_tx(&full[stage], 2 * L::STAGE_BYTES);
                         else ptx::mbar_arrive_cluster(&full[stage], 0);
                         ptx::tma_load_2d_pair(sb, &tm_q, &full[stage], kc * K3_BK, qrow0);
-                        ptx::tma_load_2d_pair(sb + K3_A_BYTES, &tm_ql, &full[stage], kc * K3_BK, qrow0);
-                        ptx::tma_load_2d_pair(sb + 2 * K3_A_BYTES, &tm_x, &full[stage], kc * K3_BK, (int)xrow0);
-                        ptx::tma_load_2d_pair(sb + 2 * K3_A_BYTES + L::B_BYTES, &tm_xl, &full[stage], kc * K3_BK, (int)xrow0);
+                        if (!SCREEN) ptx::tma_load_2d_pair(sb + K3_A_BYTES, &tm_ql, &full[stage], kc * K3_BK, qrow0);
+                        ptx::tma_load_2d_pair(sb + L::OFF_B, &tm_x, &full[stage], kc * K3_BK, (int)xrow0);
+                        if (!SCREEN) ptx::tma_load_2d_pair(sb + L::OFF_B + L::B_BYTES, &tm_xl, &full[stage], kc * K3_BK, (int)xrow0);
                     }
                     if (++stage == NS) { stage = 0; phase ^= 1; }
                 }
@@ -291,14 +296,18 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
                         const uint32_t sb = ptx::smem_u32(smem + stage * L::STAGE_BYTES);
                         const uint64_t a_hi = ptx::umma_desc_k_sw128(sb);
                         const uint64_t a_lo = ptx::umma_desc_k_sw128(sb + K3_A_BYTES);
-                        const uint64_t b_hi = ptx::umma_desc_k_sw128(sb + 2 * K3_A_BYTES);
-                        const uint64_t b_lo = ptx::umma_desc_k_sw128(sb + 2 * K3_A_BYTES + L::B_BYTES);
+                        const uint64_t b_hi = ptx::umma_desc_k_sw128(sb + L::OFF_B);
+                        const uint64_t b_lo = ptx::umma_desc_k_sw128(sb + L::OFF_B + L::B_BYTES);
 #pragma unroll
                         for (int ks = 0; ks < K3_BK / 8; ++ks) {
                             const uint64_t off = (uint64_t)(ks * 32 >> 4);  // 8 fp32 = 32 bytes along K
-                            ptx::mma_tf32<CG>(d_corr, a_lo + off, b_hi + off, idesc, (kc | ks) != 0);  // small terms first
-                            ptx::mma_tf32<CG>(d_corr, a_hi + off, b_lo + off, idesc, 1u);
-                            ptx::mma_tf32<CG>(d_tmem, a_hi + off, b_hi + off, idesc, SEP ? (uint32_t)((kc | ks) != 0) : 1u);
+                            if constexpr (SCREEN) {
+                                ptx::mma_tf32<CG>(d_tmem, a_hi + off, b_hi + off, idesc, (kc | ks) != 0);
+                            } else {
+                                ptx::mma_tf32<CG>(d_corr, a_lo + off, b_hi + off, idesc, (kc | ks) != 0);  // small terms first
+                                ptx::mma_tf32<CG>(d_corr, a_hi + off, b_lo + off, idesc, 1u);
+                                ptx::mma_tf32<CG>(d_tmem, a_hi + off, b_hi + off, idesc, SEP ? (uint32_t)((kc | ks) != 0) : 1u);
+                            }
                         }
                         ptx::mma_commit<CG>(&empty[stage]);            // smem slot free once these MMAs retire
                         if (kc == nkc - 1) ptx::mma_commit<CG>(&tfull[as]);  // accumulator complete
@@ -332,7 +341,11 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
             float tau = p.tau[sidx];
             u64 kth = p.kth[sidx];
             const float qn = valid ? p.qn[qi] : 0.f;
-            const float tau_eff = valid ? fminf(tau, __uint_as_float(__ldcg(p.gts + qi))) : 0.f;
+            const float slack = (SCREEN && valid) ? p.slack2[qi] : 0.f;
+            // exact modes: tau is (an upper bound of) the k-th exact distance.  Screening: tau bounds the
+            // k-th APPROXIMATE distance and every key within 2*sigma of it must be kept (see k3_search).
+            const float tau_eff = valid ? fminf(tau, __uint_as_float(__ldcg(p.gts + qi))) + slack : 0.f;
+            const u64 kth_eff = SCREEN ? KEY_EMPTY : kth;
             // filter threshold on s = ||x||^2 - 2 ip, widened by a few ulps so it never rejects a
             // candidate the exact test below would accept
             const float t_cmp = valid ? (tau_eff - qn) + 2e-6f * (fabsf(tau_eff) + qn) : -INF;
@@ -362,7 +375,7 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
                 if (SEP) ptx::tmem_ld_32x32(taddr + K3_BN + c0 + 32, wb);
                 reg_fence32(va);
                 if (SEP) reg_fence32(wa);
-                k3_filter_chunk<SEP>(va, wa, xn + c0, t_cmp, qn, tau_eff, kth, row_base + c0, list, cnt);
+                k3_filter_chunk<SEP>(va, wa, xn + c0, t_cmp, qn, tau_eff, kth_eff, row_base + c0, list, cnt);
                 ptx::tmem_ld_wait();
                 if (c0 + 64 < K3_BN) {
                     ptx::tmem_ld_32x32(taddr + c0 + 64, va);
@@ -370,7 +383,7 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
                 }
                 reg_fence32(vb);
                 if (SEP) reg_fence32(wb);
-                k3_filter_chunk<SEP>(vb, wb, xn + c0 + 32, t_cmp, qn, tau_eff, kth, row_base + c0 + 32, list, cnt);
+                k3_filter_chunk<SEP>(vb, wb, xn + c0 + 32, t_cmp, qn, tau_eff, kth_eff, row_base + c0 + 32, list, cnt);
             }
             // accumulator drained: hand it back to the MMA warp (of the leader CTA)
             ptx::tc_fence_before();
@@ -393,7 +406,20 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
                 for (int i = lane; i < Ps; i += 32) scr[i] = i < c ? __ldcg(lst + i) : KEY_EMPTY;
                 __syncwarp();
                 warp_bitonic_sort(scr, Ps, lane);
-                const int nc = c < p.k ? c : p.k;
+                int nc = c < p.k ? c : p.k;
+                if (SCREEN && c >= p.k) {
+                    // keep every key within the slack of this list's k-th approximate distance
+                    const float thr = key_dist(scr[p.k - 1]) + __shfl_sync(0xffffffffu, slack, Lq);
+                    int le = 0;
+                    for (int i = lane; i < c; i += 32) le += key_dist(scr[i]) <= thr ? 1 : 0;
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) le += __shfl_xor_sync(0xffffffffu, le, o);
+                    nc = le;
+                    if (nc > p.P - K3_BN) {  // cannot make room for the next tile without dropping candidates
+                        if (lane == 0) atomicExch(p.overflow, 1u);
+                        nc = p.P - K3_BN;
+                    }
+                }
                 for (int i = lane; i < nc; i += 32) lst[i] = scr[i];
                 const u64 newkth = scr[p.k - 1 < Ps ? p.k - 1 : 0];
                 __syncwarp();
@@ -426,9 +452,9 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
 
 // ---- state initialisation -------------------------------------------------------------------
 __global__ void k3_init_kernel(int64_t nslots, int* cnt, float* tau, u64* kth, int64_t nq, unsigned int* gts,
-                               u64* next_unit) {
+                               u64* next_unit, unsigned int* overflow) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i == 0) *next_unit = 0;
+    if (i == 0) { *next_unit = 0; if (overflow) *overflow = 0; }
     if (i < nslots) { cnt[i] = 0; tau[i] = FLT_MAX; kth[i] = (u64)FLT_MAX_BITS << 32; }
     if (gts && i < nq) gts[i] = FLT_MAX_BITS;
 }
@@ -607,6 +633,74 @@ k4_merge_kernel(const K3Params p, int cg, int ncta, int threshold_only, int list
     }
 }
 
+// ---- screening support: per-query slack, and K6, the exact re-rank ---------------------------
+// Screening mode runs ONE TF32 product per 8 columns instead of three.  A kind::tf32 MMA reads
+// q and x with their low 13 mantissa bits ignored, so |q.x - (q.x)_tf32| <= 2^-9 * sum|q_t||x_t|
+// <= 2^-9 |q||x| (Cauchy-Schwarz), and the approximate distance d~ = |q|^2 + |x|^2 - 2 (q.x)_tf32
+// is within  sigma_q = c * 2^-8 * |q| * max_rows|x|  of the exact one (c = 1.02 + 8e-6 d also
+// covers the accumulator truncation, ~d/8 * 2^-23).  If T is (an upper bound of) the k-th smallest
+// d~, every exact top-k row has d~ <= T + 2 sigma_q.  The lists therefore keep every key with
+// d~ <= T + 2 sigma_q, and K6 computes the exact fp32 distance (direct differences, as the scan
+// kernel does) of those few hundred rows per query and selects the final k.  The result is exact;
+// the tensor cores only decide which rows are worth an exact look.
+__global__ void k3_slack_kernel(int64_t nq, const float* __restrict__ qn, const unsigned int* __restrict__ max_norm_bits,
+                                float coef, float* __restrict__ slack2) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < nq) slack2[i] = coef * sqrtf(qn[i]) * sqrtf(__uint_as_float(*max_norm_bits));
+}
+
+__global__ void __launch_bounds__(K4_THREADS)
+k6_rerank_kernel(const K3Params p, int cg, int ncta, const float* __restrict__ X, const float* __restrict__ Q,
+                 float* __restrict__ D, int64_t* __restrict__ I) {
+    extern __shared__ __align__(16) unsigned char k4_smem_raw[];
+    K4Smem& sm = *reinterpret_cast<K4Smem*>(k4_smem_raw);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int64_t qi = blockIdx.x;
+    const int bq = K3_BM * cg;
+    const int qb = (int)(qi / bq);
+    const int r = (int)(qi - (int64_t)qb * bq) / K3_BM;
+    const int row = (int)(qi % K3_BM);
+    const int k = p.k, d = p.d;
+    // gts holds the k-th smallest approximate distance (K4 in threshold mode ran over the full pass)
+    const float bound = __uint_as_float(p.gts[qi]) + p.slack2[qi];
+    const u64 kbound = bound < FLT_MAX ? (((u64)__float_as_uint(bound) << 32) | 0xffffffffull)
+                                       : (((u64)FLT_MAX_BITS << 32) - 1);
+    const int total = k4_gather(p, cg, ncta, cg, r, qb, row, kbound, sm);
+    if (total > K4_P) {  // more rows inside the slack than the buffer holds: the host reruns exactly
+        if (tid == 0) atomicExch(p.overflow, 1u);
+        return;
+    }
+    // exact distances: one warp per candidate, 128-bit loads, fixed summation order
+    const float* qv = Q + qi * (int64_t)d;
+    for (int c = warp; c < total; c += K4_THREADS / 32) {
+        const uint32_t xr = key_row(sm.buf[c]);
+        const float* xv = X + (int64_t)xr * d;
+        float acc = 0.f;
+        for (int t = lane * 4; t < d; t += 128) {
+            const float4 a = __ldg(reinterpret_cast<const float4*>(qv + t));
+            const float4 b = ldg_stream(reinterpret_cast<const float4*>(xv + t));
+            const float e0 = a.x - b.x, e1 = a.y - b.y, e2 = a.z - b.z, e3 = a.w - b.w;
+            acc = fmaf(e0, e0, acc); acc = fmaf(e1, e1, acc); acc = fmaf(e2, e2, acc); acc = fmaf(e3, e3, acc);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        __syncwarp();
+        if (lane == 0) sm.buf[c] = acc < FLT_MAX ? make_key(acc, xr) : KEY_EMPTY;
+    }
+    __syncthreads();
+    k4_sort(sm.buf, total, K4_P);
+    for (int j = tid; j < k; j += K4_THREADS) {
+        const u64 key = j < total ? sm.buf[j] : KEY_EMPTY;
+        if (key != KEY_EMPTY) {
+            D[qi * k + j] = key_dist(key);
+            I[qi * k + j] = (int64_t)key_row(key);
+        } else {
+            D[qi * k + j] = FLT_MAX;
+            I[qi * k + j] = -1;
+        }
+    }
+}
+
 // ---- host side ----------------------------------------------------------------------------------
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -619,7 +713,9 @@ struct K3State {
     int cg = g_default_cg;
     EncodeTiledFn encode = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    unsigned int* flag_host = nullptr;  // pinned: overflow flag of the screening mode
     bool timing = false;
+    int last_mode = 0;  // 1 = 3xTF32, 2 = screening + re-rank (what the last search ran)
     int sep_mode = 0;  // long-row accuracy: 0 auto (d >= 512: separate accumulator), 1 separate accumulator, 2 off
     bool timed = false;
 };
@@ -627,9 +723,10 @@ struct K3State {
 static int k3_P(int k) { return next_pow2(k + K3_BN); }
 // CG = 1 has shared memory for compaction scratch up to 512 keys per warp; CG = 2 up to 2048.
 // Auto: CTA pairs for long rows (measured faster at d = 1024: 815 vs 782 TFLOP/s) and for long lists.
-static int k3_cg_for(int k, int want, int d) {
+static int k3_cg_for(int k, int want, int d, bool screen) {
+    if (want == 1 || want == 2) return (want == 1 && !screen && k3_P(k) > 512) ? 2 : want;
+    if (screen) return 1;  // measured: 8.9 vs 15.9 ms at d = 1024, 13.2 vs 20.8 ms at d = 384 (pairs)
     if (k3_P(k) > 512) return 2;
-    if (want == 1 || want == 2) return want;
     return d >= 512 ? 2 : 1;
 }
 
@@ -642,12 +739,12 @@ void k3_set_cta_group(K3State* s, int cg);
 
 struct K3Layout {
     int cg, ncta, nqb, qpc, P;
-    size_t off_qlo, off_qn, off_gts, off_next, off_cnt, off_tau, off_kth, off_cand, total;
+    size_t off_qlo, off_qn, off_gts, off_slack, off_next, off_cnt, off_tau, off_kth, off_cand, total;
 };
 
-static K3Layout k3_layout(int sm_count, int d, int64_t nq, int k, int want_cg) {
+static K3Layout k3_layout(int sm_count, int d, int64_t nq, int k, int want_cg, bool screen) {
     K3Layout L;
-    L.cg = k3_cg_for(k, want_cg, d);
+    L.cg = k3_cg_for(k, want_cg, d, screen);
     L.ncta = (sm_count / L.cg) * L.cg;
     L.nqb = (int)((nq + K3_BM * L.cg - 1) / (K3_BM * L.cg));
     L.qpc = L.nqb * K3_BM;
@@ -657,7 +754,8 @@ static K3Layout k3_layout(int sm_count, int d, int64_t nq, int k, int want_cg) {
     L.off_qlo = o; o += al((size_t)nq * d * 4);
     L.off_qn = o; o += al((size_t)nq * 4);
     L.off_gts = o; o += al((size_t)nq * 4);
-    L.off_next = o; o += 256;
+    L.off_slack = o; o += al((size_t)nq * 4);
+    L.off_next = o; o += 256;  // [0] scheduler counter (u64), [16] overflow flag
     size_t slots = (size_t)L.ncta * L.qpc;
     L.off_cnt = o; o += al(slots * 4);
     L.off_tau = o; o += al(slots * 4);
@@ -669,7 +767,7 @@ static K3Layout k3_layout(int sm_count, int d, int64_t nq, int k, int want_cg) {
 
 size_t k3_scratch_bytes(int sm_count, int d, int64_t nq, int k) {
     // sized for either CTA-group configuration
-    size_t a = k3_layout(sm_count, d, nq, k, 1).total, b = k3_layout(sm_count, d, nq, k, 2).total;
+    size_t a = k3_layout(sm_count, d, nq, k, 1, true).total, b = k3_layout(sm_count, d, nq, k, 2, false).total;
     return a > b ? a : b;
 }
 
@@ -688,6 +786,12 @@ int k3_create(K3State** out, int device, int sm_count) {
     s->encode = (EncodeTiledFn)fn;
     cudaEventCreate(&s->ev0);
     cudaEventCreate(&s->ev1);
+    if (cudaMallocHost(reinterpret_cast<void**>(&s->flag_host), 64) != cudaSuccess) {
+        set_error("cudaMallocHost failed");
+        cudaEventDestroy(s->ev0); cudaEventDestroy(s->ev1);
+        delete s;
+        return B2K_ENOMEM;
+    }
     *out = s;
     return B2K_OK;
 }
@@ -696,6 +800,7 @@ void k3_destroy(K3State* s) {
     if (!s) return;
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
+    if (s->flag_host) cudaFreeHost(s->flag_host);
     delete s;
 }
 
@@ -704,6 +809,7 @@ void k3_invalidate_maps(K3State*) {}  // maps are re-encoded on every search (ho
 void k3_set_timing(K3State* s, bool on) { s->timing = on; }
 void k3_set_cta_group(K3State* s, int cg) { s->cg = (cg == 1 || cg == 2) ? cg : 0; }
 void k3_set_sep_mode(K3State* s, int m) { s->sep_mode = m; }
+int k3_last_mode(const K3State* s) { return s->last_mode; }
 
 int k3_last_kernel_ms(K3State* s, float* ms) {
     if (!s->timed) return B2K_EINVAL;
@@ -730,7 +836,7 @@ static int make_map(K3State* s, CUtensorMap* m, const float* base, int64_t rows,
 template <int CG, int NS, int MODE>
 static int launch_k3(const CUtensorMap& mq, const CUtensorMap& mql, const CUtensorMap& mx, const CUtensorMap& mxl,
                      const K3Params& p, int ncta, cudaStream_t st) {
-    size_t smem = K3Smem<CG, NS>::bytes(p.P);
+    size_t smem = K3Smem<CG, NS, MODE>::bytes(p.P);
     B2K_CUDA(cudaFuncSetAttribute(k3_tf32x3_topk_kernel<CG, NS, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(ncta);
@@ -761,14 +867,26 @@ static int launch_k3_any(int cg, int P, int mode, const CUtensorMap& mq, const C
         B2K_K3_CASE(1)
     }
 #undef B2K_K3_CASE
+    if (mode == 2) {  // screening: one operand pair per stage (48 KB / 32 KB), deeper rings
+        if (cg == 1) {
+            if (P <= 512) return launch_k3<1, 4, 2>(mq, mql, mx, mxl, p, ncta, st);
+            return launch_k3<1, 2, 2>(mq, mql, mx, mxl, p, ncta, st);  // 2048-key compaction scratch needs the room
+        }
+        if (P <= 512) return launch_k3<2, 6, 2>(mq, mql, mx, mxl, p, ncta, st);
+        return launch_k3<2, 4, 2>(mq, mql, mx, mxl, p, ncta, st);
+    }
     set_error("tensor kernel: bad accumulator mode %d", mode);
     return B2K_EINVAL;
 }
 
-int k3_search(K3State* s, const float* x, const float* xlo, const float* norms, int64_t n, int64_t capacity, int d,
-              const float* q, int64_t nq, int k, float* D, int64_t* I, unsigned char* scratch, cudaStream_t st) {
+int k3_search(K3State* s, const float* x, const float* xlo, const float* norms, const unsigned int* max_norm_bits,
+              int64_t n, int64_t capacity, int d, const float* q, int64_t nq, int k, float* D, int64_t* I,
+              unsigned char* scratch, cudaStream_t st, int exact, int* overflowed) {
     (void)capacity;
-    K3Layout L = k3_layout(s->sm_count, d, nq, k, s->cg);
+    const bool screen = !exact;
+    if (overflowed) *overflowed = 0;
+    s->last_mode = screen ? 2 : 1;
+    K3Layout L = k3_layout(s->sm_count, d, nq, k, s->cg, !exact);
     float* qlo = reinterpret_cast<float*>(scratch + L.off_qlo);
     K3Params p;
     p.n = n; p.d = d; p.nq = nq; p.k = k; p.P = L.P; p.nqb = L.nqb; p.qpc = L.qpc;
@@ -782,26 +900,34 @@ int k3_search(K3State* s, const float* x, const float* xlo, const float* norms, 
     p.kth = reinterpret_cast<u64*>(scratch + L.off_kth);
     p.cand = reinterpret_cast<u64*>(scratch + L.off_cand);
     p.next_unit = reinterpret_cast<u64*>(scratch + L.off_next);
+    p.overflow = reinterpret_cast<unsigned int*>(scratch + L.off_next + 16);
+    p.slack2 = reinterpret_cast<float*>(scratch + L.off_slack);
     p.static_mode = 0;
     p.static_tpc = 1;
     p.static_tile0 = 0;
     p.tile_cols = K3_BN;
 
-    // queries: norms + TF32 residual rows (K1 reused), list state reset
-    int rc = launch_row_prep(q, nq, d, const_cast<float*>(p.qn), qlo, st);
+    // queries: norms (+ TF32 residual rows for the exact mode; K1 reused), screening slack, list state reset
+    int rc = launch_row_prep(q, nq, d, const_cast<float*>(p.qn), screen ? nullptr : qlo, nullptr, st);
     if (rc) return rc;
+    if (screen) {
+        const float coef = 2.f * (1.02f + 8e-6f * (float)d) / 256.f;  // 2 * sigma_q / (|q| * max|x|), see k3_slack_kernel
+        k3_slack_kernel<<<(unsigned)((nq + 255) / 256), 256, 0, st>>>(nq, p.qn, max_norm_bits, coef, const_cast<float*>(p.slack2));
+        count_launch();
+        B2K_CUDA(cudaGetLastError());
+    }
     const int64_t nslots = (int64_t)L.ncta * L.qpc;
     const int64_t ninit = nslots > nq ? nslots : nq;
-    k3_init_kernel<<<(unsigned)((ninit + 255) / 256), 256, 0, st>>>(nslots, p.cnt, p.tau, p.kth, nq, p.gts, p.next_unit);
+    k3_init_kernel<<<(unsigned)((ninit + 255) / 256), 256, 0, st>>>(nslots, p.cnt, p.tau, p.kth, nq, p.gts, p.next_unit, p.overflow);
     count_launch();
     B2K_CUDA(cudaGetLastError());
 
     B2K_CUDA(cudaFuncSetAttribute(k4_merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(K4Smem)));
     CUtensorMap mq, mql, mx, mxl;
     if ((rc = make_map(s, &mq, q, nq, d, K3_BM))) return rc;
-    if ((rc = make_map(s, &mql, qlo, nq, d, K3_BM))) return rc;
+    if ((rc = make_map(s, &mql, screen ? q : qlo, nq, d, K3_BM))) return rc;
     if ((rc = make_map(s, &mx, x, n, d, K3_BN / L.cg))) return rc;
-    if ((rc = make_map(s, &mxl, xlo, n, d, K3_BN / L.cg))) return rc;
+    if ((rc = make_map(s, &mxl, screen ? x : xlo, n, d, K3_BN / L.cg))) return rc;
 
     // Warm start.  Round A: the first 64 rows of one tile per CTA (pair) with open thresholds --
     // every key is kept, so the pass is kept small; per query the k-th smallest distance of that
@@ -810,8 +936,9 @@ int k3_search(K3State* s, const float* x, const float* xlo, const float* norms, 
     // tightened again.  The full pass then prunes from its first tile: its lists stay far below
     // capacity (no compaction sorts) and K4 has a few k keys per query to merge.
     const int nclusters = L.ncta / L.cg;
-    // accumulator mode: 0 one accumulator (double-buffered), 1 separate cross-term accumulator
-    const int sep = (s->sep_mode == 1 || (s->sep_mode == 0 && d >= 512)) ? 1 : 0;
+    // kernel mode: 0 3xTF32 in one accumulator (double-buffered), 1 3xTF32 with a separate cross-term
+    // accumulator, 2 screening (one product; exact distances from the re-rank kernel)
+    const int sep = screen ? 2 : (s->sep_mode == 1 || (s->sep_mode == 0 && d >= 512)) ? 1 : 0;
     const int cols_a = 64;
     // the first bound only needs ~2048 sampled rows: read every step_a-th list, as long as k of them exist
     int step_a = nclusters / 32 > 0 ? nclusters / 32 : 1;
@@ -827,7 +954,7 @@ int k3_search(K3State* s, const float* x, const float* xlo, const float* norms, 
         rc = launch_k3_any(L.cg, L.P, sep, mq, mql, mx, mxl, pre, L.ncta, st);
         if (rc) return rc;
         k4_merge_kernel<<<(unsigned)nq, K4_THREADS, sizeof(K4Smem), st>>>(pre, L.cg, L.ncta, 1, step_a, nullptr, nullptr);
-        k3_init_kernel<<<(unsigned)((nslots + 255) / 256), 256, 0, st>>>(nslots, p.cnt, p.tau, p.kth, nq, nullptr, p.next_unit);
+        k3_init_kernel<<<(unsigned)((nslots + 255) / 256), 256, 0, st>>>(nslots, p.cnt, p.tau, p.kth, nq, nullptr, p.next_unit, nullptr);
         count_launch(2);
         B2K_CUDA(cudaGetLastError());
         // rows the second round should cover so that the full pass leaves ~<= 64 keys per list
@@ -844,7 +971,7 @@ int k3_search(K3State* s, const float* x, const float* xlo, const float* norms, 
             rc = launch_k3_any(L.cg, L.P, sep, mq, mql, mx, mxl, pre, L.ncta, st);
             if (rc) return rc;
             k4_merge_kernel<<<(unsigned)nq, K4_THREADS, sizeof(K4Smem), st>>>(pre, L.cg, L.ncta, 1, 1, nullptr, nullptr);
-            k3_init_kernel<<<(unsigned)((nslots + 255) / 256), 256, 0, st>>>(nslots, p.cnt, p.tau, p.kth, nq, nullptr, p.next_unit);
+            k3_init_kernel<<<(unsigned)((nslots + 255) / 256), 256, 0, st>>>(nslots, p.cnt, p.tau, p.kth, nq, nullptr, p.next_unit, nullptr);
             count_launch(2);
             B2K_CUDA(cudaGetLastError());
         }
@@ -855,9 +982,24 @@ int k3_search(K3State* s, const float* x, const float* xlo, const float* norms, 
     if (rc) return rc;
     if (s->timing) { B2K_CUDA(cudaEventRecord(s->ev1, st)); s->timed = true; }
 
-    k4_merge_kernel<<<(unsigned)nq, K4_THREADS, sizeof(K4Smem), st>>>(p, L.cg, L.ncta, 0, 1, D, I);
-    count_launch();
+    if (!screen) {
+        k4_merge_kernel<<<(unsigned)nq, K4_THREADS, sizeof(K4Smem), st>>>(p, L.cg, L.ncta, 0, 1, D, I);
+        count_launch();
+        B2K_CUDA(cudaGetLastError());
+        return B2K_OK;
+    }
+    // screening: the exact k-th smallest approximate distance per query, then the exact re-rank of
+    // everything within the slack of it
+    B2K_CUDA(cudaFuncSetAttribute(k6_rerank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(K4Smem)));
+    k4_merge_kernel<<<(unsigned)nq, K4_THREADS, sizeof(K4Smem), st>>>(p, L.cg, L.ncta, 1, 1, nullptr, nullptr);
+    k6_rerank_kernel<<<(unsigned)nq, K4_THREADS, sizeof(K4Smem), st>>>(p, L.cg, L.ncta, x, q, D, I);
+    count_launch(2);
     B2K_CUDA(cudaGetLastError());
+    // a list or the re-rank buffer could not hold every row inside the slack (masses of near-
+    // duplicates around the k-th neighbour): the caller repeats the search in the exact mode
+    B2K_CUDA(cudaMemcpyAsync(s->flag_host, p.overflow, sizeof(unsigned int), cudaMemcpyDeviceToHost, st));
+    B2K_CUDA(cudaStreamSynchronize(st));
+    if (overflowed) *overflowed = (int)*s->flag_host;
     return B2K_OK;
 }
 

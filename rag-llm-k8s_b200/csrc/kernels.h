@@ -5,7 +5,9 @@
 namespace b2k {
 
 // K1 (k1_prep.cu): per-row squared norms (+ optional TF32 residual rows) for rows [0,n) of X.
-int launch_row_prep(const float* X, int64_t n, int d, float* norms, float* xlo, cudaStream_t st);
+// max_norm_bits (nullable): float bits of the largest finite squared norm, updated with atomicMax.
+int launch_row_prep(const float* X, int64_t n, int d, float* norms, float* xlo, unsigned int* max_norm_bits,
+                    cudaStream_t st);
 int launch_synth(uint64_t seed, int64_t row0, int64_t nrows, int d, float* out, cudaStream_t st);
 
 // K2 (k2_scan.cu)

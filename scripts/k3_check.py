@@ -12,11 +12,13 @@ args = sys.argv[1:]
 cg = 1
 unit = False
 sep = 0
+tmode = 0
 while args and "=" in args[0]:
     kx, v = args.pop(0).split("=")
     if kx == "cg": cg = int(v)
     if kx == "unit": unit = bool(int(v))
     if kx == "sep": sep = int(v)
+    if kx == "mode": tmode = int(v)
 cases = [(1000, 64, 128, 10), (5000, 384, 40, 10), (100000, 384, 300, 100), (70000, 100, 1024, 5), (3001, 1024, 129, 37)]
 if args:
     cases = [tuple(int(v) for v in a.split(",")) for a in args]
@@ -28,7 +30,7 @@ for (n, d, nq, k) in cases:
     else:
         x = None; q = b200knn.synth(5678, 0, nq, d).cpu().numpy()
         idx = b200knn.IndexFlatL2(d); idx.reserve(n); idx.add_synthetic(n, 1234, 0)
-    idx.set_option("path", 2); idx.set_option("timing", 1); idx.set_option("tensor_cta_group", cg); idx.set_option("tensor_sep_accum", sep)
+    idx.set_option("path", 2); idx.set_option("timing", 1); idx.set_option("tensor_cta_group", cg); idx.set_option("tensor_sep_accum", sep); idx.set_option("tensor_mode", tmode)
     D, I = idx.search(q, k)
     t0 = time.time(); D, I = idx.search(q, k); t1 = time.time()
     st = idx.stats()
@@ -41,7 +43,7 @@ for (n, d, nq, k) in cases:
         ok = It >= 0
         rel = (np.abs(D - Dt)[ok] / scale[ok]).max()
         relo = (np.abs(Dr - Dt)[ok] / scale[ok]).max()
-        print("sep=%d " % sep, end=""); print("cg=%d n=%d d=%d nq=%d k=%d  ids==oracle %.5f ids==f64 %.5f  max rel err (vs cancel scale) %.3g (oracle %.3g)  kernel %.3f ms = %.0f TF/s, call %.1f ms" % (
+        print("mode=%d sep=%d " % (tmode, sep), end=""); print("cg=%d n=%d d=%d nq=%d k=%d  ids==oracle %.5f ids==f64 %.5f  max rel err (vs cancel scale) %.3g (oracle %.3g)  kernel %.3f ms = %.0f TF/s, call %.1f ms" % (
             cg, n, d, nq, k, (I == Ir).mean(), (I == It).mean(), rel, relo, st["main_kernel_ms"], tf, (t1 - t0) * 1e3), flush=True)
     else:
-        print("cg=%d n=%d d=%d nq=%d k=%d  kernel %.3f ms = %.0f TF/s, call %.1f ms" % (cg, n, d, nq, k, st["main_kernel_ms"], tf, (t1 - t0) * 1e3), flush=True)
+        print("mode=%d cg=%d n=%d d=%d nq=%d k=%d  kernel %.3f ms, call %.1f ms" % (tmode, cg, n, d, nq, k, st["main_kernel_ms"], (t1 - t0) * 1e3), flush=True)

@@ -294,11 +294,13 @@ def test_one_million_rows_nq1_k10(faiss):
     assert np.array_equal(Im, I) and np.array_equal(Dm, D)
 
 
-@pytest.mark.parametrize("cg,sep,k", [(1, 2, 10), (1, 1, 10), (2, 2, 100), (2, 1, 100), (2, 2, 700), (2, 1, 1024)])
-def test_tensor_kernel_variants(faiss, cg, sep, k):
-    """Every instantiation of the tcgen05 kernel (one CTA / CTA pair, shared / separate cross-term
-    accumulator, 3-stage / 2-stage ring for long lists) against the oracle's expansion numerics,
-    on N(0,1) rows and on unit-norm rows with planted duplicates (the rag.py distribution)."""
+@pytest.mark.parametrize("mode,cg,sep,k", [(1, 1, 2, 10), (1, 1, 1, 10), (1, 2, 2, 100), (1, 2, 1, 100), (1, 2, 2, 700),
+                                           (1, 2, 1, 1024), (2, 1, 0, 10), (2, 1, 0, 700), (2, 2, 0, 100), (2, 2, 0, 1024)])
+def test_tensor_kernel_variants(faiss, mode, cg, sep, k):
+    """Every instantiation of the tcgen05 kernel -- 3xTF32 (one CTA / CTA pair, shared / separate
+    cross-term accumulator, short / long lists) and TF32 screening + exact re-rank -- against the
+    oracle's expansion numerics, on N(0,1) rows and on unit-norm rows with planted duplicates (the
+    rag.py distribution)."""
     rng = np.random.default_rng(cg * 10 + sep)
     for unit in (False, True):
         x = O.synth(31, 0, 40000, 256)
@@ -308,12 +310,32 @@ def test_tensor_kernel_variants(faiss, cg, sep, k):
             q[:8] = x[rng.integers(0, 40000, 8)]          # self matches: true distance 0
         idx = _build(faiss, x)
         idx.set_option("path", 2)
+        idx.set_option("tensor_mode", mode)
         idx.set_option("tensor_cta_group", cg)
         idx.set_option("tensor_sep_accum", sep)
         D, I = idx.search(q, k)
-        assert idx.stats()["path"] == "tensor"
+        st = idx.stats()
+        assert st["path"] == "tensor" and st["tensor_mode"] == {1: "3xtf32", 2: "screen+rerank"}[mode]
         assert np.all(D >= 0.0)
-        assert_knn_matches(D, I, x, q, k, expanded=True, what="cg=%d sep=%d k=%d unit=%s" % (cg, sep, k, unit))
+        if mode == 2 and unit:
+            assert np.all(D[:8, 0] == 0.0)                # exact re-rank: a stored query is at distance exactly 0
+        assert_knn_matches(D, I, x, q, k, expanded=True, what="mode=%d cg=%d sep=%d k=%d unit=%s" % (mode, cg, sep, k, unit))
+
+
+def test_screening_falls_back_when_the_slack_zone_overflows(faiss):
+    """Screening keeps every row whose approximate distance is within the error slack of the k-th;
+    thousands of rows at (almost) the same distance do not fit its lists, and the search must then
+    repeat itself in the 3xTF32 mode instead of dropping candidates."""
+    rng = np.random.default_rng(0)
+    base = rng.standard_normal((1, 64)).astype(np.float32)
+    x = np.repeat(base, 20000, 0) + rng.standard_normal((20000, 64)).astype(np.float32) * 1e-6   # near-duplicates
+    x[::1000] = rng.standard_normal((20, 64)).astype(np.float32)
+    q = rng.standard_normal((30, 64)).astype(np.float32)
+    idx = _build(faiss, x)
+    D, I = idx.search(q, 10)
+    st = idx.stats()
+    assert st["path"] == "tensor" and st["screen_fallbacks"] >= 1 and st["tensor_mode"] == "3xtf32"
+    assert_knn_matches(D, I, x, q, 10, expanded=True, what="overflow fallback")
 
 
 def test_full_size_c3_properties(faiss):
