@@ -524,3 +524,25 @@ def test_tensor_path_small_and_ragged(faiss, n, d):
     Dr, Ir = O.search(x, q, 10)
     assert np.array_equal(I < 0, Ir < 0)
     assert_knn_matches(D, I, x, q, 10, Dr, Ir, expanded=True, what="n=%d d=%d" % (n, d))
+
+
+def test_nonfinite_rows_and_queries_on_the_tensor_path(faiss):
+    """inf / NaN rows are never selected and do not disturb their neighbours in the tile; a NaN
+    query gets all padding (no distance is < FLT_MAX), the other queries are unaffected."""
+    x = O.synth(51, 0, 3000, 64)
+    x[5, 3] = np.inf
+    x[17, 0] = np.nan
+    x[300] = np.inf
+    q = O.synth(52, 0, 24, 64)
+    q[7, 1] = np.nan
+    for mode in (2, 1):
+        idx = _build(faiss, x)
+        idx.set_option("tensor_mode", mode)
+        D, I = idx.search(q, 8)
+        assert idx.stats()["path"] == "tensor"
+        assert not np.isin(I, [5, 17, 300]).any()
+        assert np.all(I[7] == -1) and np.all(D[7] == O.FLT_MAX)
+        ok = [i for i in range(24) if i != 7]
+        xs = x.copy()
+        xs[[5, 17, 300]] = 1e6                       # far away, finite: same neighbours for the oracle
+        assert_knn_matches(D[ok], I[ok], xs, q[ok], 8, expanded=True, what="nonfinite mode=%d" % mode)
