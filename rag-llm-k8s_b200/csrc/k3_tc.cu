@@ -66,6 +66,7 @@ struct K3Params {
     unsigned int* overflow;  // screening: set when a list cannot hold every key inside the slack
     int static_mode;    // 1: warm-start pass, CTA (pair) c takes tiles static_tile0 + c*static_tpc + [0,static_tpc), all query blocks
     int static_tpc;
+    int static_qb_mod;  // warm-start pass: CTA (pair) c only takes the query blocks qb with qb % static_qb_mod == c % static_qb_mod
     int tile_cols;      // columns (rows of the tile) the epilogue looks at: 256, or fewer in the first warm-start pass
     int64_t static_tile0;
 };
@@ -231,9 +232,14 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
                     // moment work on neighbouring database tiles and share them through L2
                     ptx::mbar_wait(&sempty[ss], sph ^ 1);
                     if (p.static_mode) {
-                        u = static_i < p.nqb * p.static_tpc
-                                ? (p.static_tile0 + (long long)(blockIdx.x / CG) * p.static_tpc) * p.nqb + static_i
-                                : -1;
+                        const int c = blockIdx.x / CG, G = p.static_qb_mod;
+                        const int mine = (p.nqb - (c % G) + G - 1) / G;  // query blocks of this CTA (pair)
+                        if (static_i < mine * p.static_tpc) {
+                            const int j = static_i / mine, qb = (c % G) + (static_i - j * mine) * G;
+                            u = (p.static_tile0 + (long long)c * p.static_tpc + j) * p.nqb + qb;
+                        } else {
+                            u = -1;
+                        }
                         ++static_i;
                     } else {
                         u = (long long)atomicAdd(p.next_unit, 1ull);
@@ -904,6 +910,7 @@ int k3_search(K3State* s, const float* x, const float* xlo, const float* norms, 
     p.slack2 = reinterpret_cast<float*>(scratch + L.off_slack);
     p.static_mode = 0;
     p.static_tpc = 1;
+    p.static_qb_mod = 1;
     p.static_tile0 = 0;
     p.tile_cols = K3_BN;
 
@@ -940,20 +947,22 @@ int k3_search(K3State* s, const float* x, const float* xlo, const float* norms, 
     // accumulator, 2 screening (one product; exact distances from the re-rank kernel)
     const int sep = screen ? 2 : (s->sep_mode == 1 || (s->sep_mode == 0 && d >= 512)) ? 1 : 0;
     const int cols_a = 64;
-    // the first bound only needs ~2048 sampled rows: read every step_a-th list, as long as k of them exist
-    int step_a = nclusters / 32 > 0 ? nclusters / 32 : 1;
-    while (step_a > 1 && (int64_t)(nclusters / step_a) * cols_a < 4 * (int64_t)k) --step_a;
     if (ntiles >= 2 * (int64_t)nclusters && (int64_t)nclusters * cols_a >= 2 * (int64_t)k) {
         K3Params pre = p;
         pre.static_mode = 1;
         pre.static_tpc = 1;
         pre.static_tile0 = 0;
         pre.tile_cols = cols_a;
+        // every key of this pass is kept, so it is made as small as a usable bound allows: each CTA
+        // (pair) only serves every G-th query block, leaving nclusters / G lists of 64 keys per query
+        int G = (int)(((int64_t)nclusters * cols_a) / (12 * (int64_t)k));
+        G = G < 1 ? 1 : (G > L.nqb ? L.nqb : G);
+        pre.static_qb_mod = G;
         pre.nunits = (int64_t)nclusters * L.nqb;
         pre.n = (int64_t)nclusters * K3_BN;
         rc = launch_k3_any(L.cg, L.P, sep, mq, mql, mx, mxl, pre, L.ncta, st);
         if (rc) return rc;
-        k4_merge_kernel<<<(unsigned)nq, K4_THREADS, sizeof(K4Smem), st>>>(pre, L.cg, L.ncta, 1, step_a, nullptr, nullptr);
+        k4_merge_kernel<<<(unsigned)nq, K4_THREADS, sizeof(K4Smem), st>>>(pre, L.cg, L.ncta, 1, 1, nullptr, nullptr);
         k3_init_kernel<<<(unsigned)((nslots + 255) / 256), 256, 0, st>>>(nslots, p.cnt, p.tau, p.kth, nq, nullptr, p.next_unit, nullptr);
         count_launch(2);
         B2K_CUDA(cudaGetLastError());
@@ -964,6 +973,7 @@ int k3_search(K3State* s, const float* x, const float* xlo, const float* norms, 
         if (tpc > 16) tpc = 16;
         if (ntiles >= (int64_t)(tpc + 1) * nclusters * 2) {
             pre.static_tpc = tpc;
+            pre.static_qb_mod = 1;
             pre.static_tile0 = nclusters;
             pre.tile_cols = K3_BN;
             pre.n = (int64_t)nclusters * (tpc + 1) * K3_BN;
