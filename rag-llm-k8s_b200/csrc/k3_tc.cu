@@ -334,34 +334,79 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
         int as = 0, ss = 0, xb = 0;
         uint32_t aphase = 0, sph = 0;
         const float INF = __int_as_float(0x7f800000);
-        for (;;) {
+
+        // Per-unit inputs are fetched one unit ahead: the squared norms of the next tile go to the
+        // other half of xn_s with cp.async while this tile is filtered, and the list state of the
+        // next query block is loaded early (or simply kept in registers when the block repeats).
+        // Without this the epilogue paid two global-memory round trips (~1.9k cycles) per unit.
+        struct QState { int cnt; float tau; u64 kth; float qn, slack; unsigned int gts; };
+        auto take = [&]() -> long long {
             const long long u = sched_take_warp<CG>(sfull, sempty, sched_u, ss, sph, rank, lane);
             if (++ss == K3_NSCHED) { ss = 0; sph ^= 1; }
-            if (u < 0) break;
+            return u;
+        };
+        auto next_is_ready = [&]() -> bool {
+            return CG == 1 ? ptx::mbar_try_wait(&sfull[ss], sph) : ptx::mbar_try_wait_cluster(&sfull[ss], sph);
+        };
+        auto issue_norms = [&](long long u, float* dst) {
             const int64_t t = u / p.nqb;
-            const int qb = (int)(u - t * p.nqb);
-            const int64_t qi = (int64_t)qb * (K3_BM * CG) + (int64_t)rank * K3_BM + row;
+            for (int j = epi_tid; j < K3_BN; j += K3_EPI_THREADS) {
+                const int64_t r = t * K3_BN + j;
+                if (r < p.n && j < p.tile_cols) ptx::cp_async_4(dst + j, p.norms + r);
+                else dst[j] = INF;
+            }
+        };
+        auto sidx_of = [&](int qb) -> int64_t { return (int64_t)blockIdx.x * p.qpc + (int64_t)qb * K3_BM + row; };
+        auto qi_of = [&](int qb) -> int64_t { return (int64_t)qb * (K3_BM * CG) + (int64_t)rank * K3_BM + row; };
+        auto load_state = [&](int qb, QState& S) {
+            const int64_t sidx = sidx_of(qb), qi = qi_of(qb);
             const bool valid = qi < p.nq;
-            const int64_t sidx = (int64_t)blockIdx.x * p.qpc + (int64_t)qb * K3_BM + row;
-            int cnt = p.cnt[sidx];
-            float tau = p.tau[sidx];
-            u64 kth = p.kth[sidx];
-            const float qn = valid ? p.qn[qi] : 0.f;
-            const float slack = (SCREEN && valid) ? p.slack2[qi] : 0.f;
+            S.cnt = p.cnt[sidx];
+            S.tau = p.tau[sidx];
+            S.kth = p.kth[sidx];
+            S.qn = valid ? p.qn[qi] : 0.f;
+            S.slack = (SCREEN && valid) ? p.slack2[qi] : 0.f;
+            S.gts = valid ? __ldcg(p.gts + qi) : 0u;
+        };
+
+        long long cur = take();
+        QState S;
+        if (cur >= 0) {
+            issue_norms(cur, xn_s);
+            load_state((int)(cur % p.nqb), S);
+        }
+        while (cur >= 0) {
+            const int64_t t = cur / p.nqb;
+            const int qb = (int)(cur - t * p.nqb);
+            const int64_t qi = qi_of(qb);
+            const bool valid = qi < p.nq;
+            const int64_t sidx = sidx_of(qb);
+            int cnt = S.cnt;
+            float tau = S.tau;
+            u64 kth = S.kth;
+            const float qn = S.qn, slack = S.slack;
             // exact modes: tau is (an upper bound of) the k-th exact distance.  Screening: tau bounds the
             // k-th APPROXIMATE distance and every key within 2*sigma of it must be kept (see k3_search).
-            const float tau_eff = valid ? fminf(tau, __uint_as_float(__ldcg(p.gts + qi))) + slack : 0.f;
+            const float tau_eff = valid ? fminf(tau, __uint_as_float(S.gts)) + slack : 0.f;
             const u64 kth_eff = SCREEN ? KEY_EMPTY : kth;
             // filter threshold on s = ||x||^2 - 2 ip, widened by a few ulps so it never rejects a
             // candidate the exact test below would accept
             const float t_cmp = valid ? (tau_eff - qn) + 2e-6f * (fabsf(tau_eff) + qn) : -INF;
             float* xn = xn_s + xb * K3_BN;
-            xb ^= 1;
-            for (int j = epi_tid; j < K3_BN; j += K3_EPI_THREADS) {
-                const int64_t r = t * K3_BN + j;
-                xn[j] = (r < p.n && j < p.tile_cols) ? p.norms[r] : INF;
+            ptx::cp_async_wait_all();
+            asm volatile("bar.sync 1, 128;" ::: "memory");  // this tile's norms are in place for all four warps
+
+            // look one unit ahead if the scheduler has already published it
+            long long nxt = -2;
+            QState N;
+            bool n_loaded = false;
+            if (next_is_ready()) {
+                nxt = take();
+                if (nxt >= 0) {
+                    issue_norms(nxt, xn_s + (xb ^ 1) * K3_BN);
+                    if ((int)(nxt % p.nqb) != qb) { load_state((int)(nxt % p.nqb), N); n_loaded = true; }
+                }
             }
-            asm volatile("bar.sync 1, 128;" ::: "memory");
 
             ptx::mbar_wait(&tfull[as], aphase);
             ptx::tc_fence_after();
@@ -438,12 +483,32 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
                     }
                 }
             }
-            p.cnt[sidx] = cnt;
-            p.tau[sidx] = tau;
-            p.kth[sidx] = kth;
+
+            // hand over to the next unit
+            if (nxt == -2) {  // the scheduler had not published it yet: take it now (blocking)
+                nxt = take();
+                if (nxt >= 0) issue_norms(nxt, xn_s + (xb ^ 1) * K3_BN);
+            }
+            const int nqb_next = nxt >= 0 ? (int)(nxt % p.nqb) : -1;
+            if (nqb_next == qb) {
+                // same query block again: the list state stays in registers, only the shared bound is refreshed
+                S.cnt = cnt; S.tau = tau; S.kth = kth;
+                S.gts = valid ? __ldcg(p.gts + qi) : 0u;
+            } else {
+                p.cnt[sidx] = cnt;
+                p.tau[sidx] = tau;
+                p.kth[sidx] = kth;
+                if (nxt >= 0) {
+                    if (n_loaded) S = N;
+                    else load_state(nqb_next, S);
+                }
+            }
+            cur = nxt;
+            xb ^= 1;
             if (SEP) { aphase ^= 1; }
             else { as ^= 1; if (as == 0) aphase ^= 1; }
         }
+        ptx::cp_async_wait_all();
     }
 
     // ---- teardown ----
