@@ -134,14 +134,17 @@ B2K_API int b2k_search_rows_noalloc(int device, const float* x_dev, int64_t n, i
 /* Tuning / test hooks.  Keys: "path" (0 auto, 1 force the scan kernel, 2 force the
  * tensor-core kernel), "scan_ctas_per_sm", "timing" (0/1), "tensor_cta_group" (0 auto, 1, 2),
  * "tensor_sep_accum" (0 auto, 1 on, 2 off), "tensor_mode" (0 auto = 2, 1 = 3xTF32 products,
- * 2 = one TF32 product as a screen + exact fp32 re-rank of the rows inside its error slack).
+ * 2 = one TF32 product as a screen + exact fp32 re-rank of the rows inside its error slack,
+ * 3 = the same screen on bf16 copies of the rows (kept next to the fp32 rows, +50% memory;
+ * needs d % 8 == 0, else 2 serves)), "tensor_segments" (1 default: the main pass runs in
+ * segments with the k-th-distance bound refreshed in between; 0: one launch).
  * Unknown key -> B2K_EINVAL. */
 B2K_API int b2k_set_option(b2k_index* h, const char* key, int64_t value);
 
 /* Read-back of measurements / state.  Keys: "last_path" (1 = scan kernel, 2 = tensor-core
  * kernel served the last search), "tensor_kernel_ms" (CUDA-event duration of the last
  * tensor-core main kernel; needs option "timing" = 1; synchronises on that kernel),
- * "tensor_mode_used" (1 / 2), "screen_fallbacks" (searches repeated in 3xTF32 mode because the
+ * "tensor_mode_used" (1 / 2 / 3), "screen_fallbacks" (searches repeated in 3xTF32 mode because the
  * slack zone overflowed), "scan_kernel_ms" / "scan_launches" (the same for the scan kernel launches of the last
  * scan-path search). */
 B2K_API int b2k_get_stat(b2k_index* h, const char* key, double* out);

@@ -47,6 +47,8 @@ struct b2k_index {
     float* norms = nullptr;
     float* xlo = nullptr;
     bool lo_enabled = false;
+    void* xbf = nullptr;  // bf16 copies of the rows (bf16 screening mode), allocated on first use
+    bool bf_enabled = false;
     cudaStream_t stream = nullptr;
     mutable std::mutex mu;
     void* ws = nullptr;
@@ -59,7 +61,8 @@ struct b2k_index {
     int opt_timing = 0;
     int opt_cta_group = 0;  // 0 = library default
     int opt_sep = 0;
-    int opt_tensor_mode = 0;  // 0 auto (screening + exact re-rank), 1 3xTF32, 2 screening
+    int opt_segments = 1;
+    int opt_tensor_mode = 0;  // 0 auto (TF32 screening + exact re-rank), 1 3xTF32, 2 TF32 screening, 3 bf16 screening
     int64_t stat_screen_fallbacks = 0;
     int last_path = 0;
     int sticky = 0;
@@ -74,6 +77,7 @@ struct b2k_index {
 static constexpr int64_t MAX_ROWS = 0xFFFFFFFEll;  // row index lives in the low 32 bits of a key
 static constexpr size_t IO_CHUNK = (size_t)64 << 20;
 static constexpr int MAX_NORM_SLOT = 2;  // h->done[0] ticket, [1] scan work counter, [2] bits of the largest squared row norm
+static constexpr int MAX_ERR_SLOT = 3;   // [3] bits of the largest squared bf16 rounding-error norm of a row
 static constexpr int64_t TC_QUERY_CHUNK = 4096;  // queries per tensor-core pass (faiss: distance_compute_blas_query_bs)
 
 namespace {
@@ -149,6 +153,7 @@ int grow(b2k_index* h, int64_t need_rows) {
     if (cap < 1024) cap = 1024;
     if (cap > MAX_ROWS) cap = MAX_ROWS;
     float *nx = nullptr, *nn = nullptr, *nl = nullptr;
+    void* nb = nullptr;
     size_t row_bytes = (size_t)h->d * sizeof(float);
     cudaError_t e = cudaMalloc(&nx, (size_t)cap * row_bytes);
     if (e != cudaSuccess && cap > need_rows) {  // doubling did not fit: take exactly what is needed
@@ -158,9 +163,10 @@ int grow(b2k_index* h, int64_t need_rows) {
     }
     if (e == cudaSuccess) e = cudaMalloc(&nn, (size_t)cap * sizeof(float));
     if (e == cudaSuccess && h->lo_enabled) e = cudaMalloc(&nl, (size_t)cap * row_bytes);
+    if (e == cudaSuccess && h->bf_enabled) e = cudaMalloc(&nb, (size_t)cap * row_bytes / 2);
     if (e != cudaSuccess) {
         cudaGetLastError();
-        cudaFree(nx); cudaFree(nn); cudaFree(nl);
+        cudaFree(nx); cudaFree(nn); cudaFree(nl); cudaFree(nb);
         set_error("cudaMalloc for %lld rows x %d failed: %s", (long long)cap, h->d, cudaGetErrorString(e));
         return B2K_ENOMEM;
     }
@@ -168,18 +174,23 @@ int grow(b2k_index* h, int64_t need_rows) {
         B2K_CUDA(cudaMemcpyAsync(nx, h->x, (size_t)h->ntotal * row_bytes, cudaMemcpyDeviceToDevice, h->stream));
         B2K_CUDA(cudaMemcpyAsync(nn, h->norms, (size_t)h->ntotal * sizeof(float), cudaMemcpyDeviceToDevice, h->stream));
         if (nl) B2K_CUDA(cudaMemcpyAsync(nl, h->xlo, (size_t)h->ntotal * row_bytes, cudaMemcpyDeviceToDevice, h->stream));
+        if (nb) B2K_CUDA(cudaMemcpyAsync(nb, h->xbf, (size_t)h->ntotal * row_bytes / 2, cudaMemcpyDeviceToDevice, h->stream));
         B2K_CUDA(cudaStreamSynchronize(h->stream));
     }
-    cudaFree(h->x); cudaFree(h->norms); cudaFree(h->xlo);
-    h->x = nx; h->norms = nn; h->xlo = nl; h->capacity = cap;
+    cudaFree(h->x); cudaFree(h->norms); cudaFree(h->xlo); cudaFree(h->xbf);
+    h->x = nx; h->norms = nn; h->xlo = nl; h->xbf = nb; h->capacity = cap;
     if (h->k3) k3_invalidate_maps(h->k3);
     return B2K_OK;
 }
 
 // Rows [first, first+n) of h->x are in place: compute their norms (and residual rows).
 int prep_new_rows(b2k_index* h, int64_t first, int64_t n, cudaStream_t st) {
-    return launch_row_prep(h->x + first * (int64_t)h->d, n, h->d, h->norms + first,
-                           h->lo_enabled ? h->xlo + first * (int64_t)h->d : nullptr, h->done + MAX_NORM_SLOT, st);
+    int rc = launch_row_prep(h->x + first * (int64_t)h->d, n, h->d, h->norms + first,
+                             h->lo_enabled ? h->xlo + first * (int64_t)h->d : nullptr, h->done + MAX_NORM_SLOT, st);
+    if (!rc && h->bf_enabled)
+        rc = launch_row_bf16(h->x + first * (int64_t)h->d, n, h->d,
+                             static_cast<unsigned short*>(h->xbf) + first * (int64_t)h->d, nullptr, h->done + MAX_ERR_SLOT, st);
+    return rc;
 }
 
 int enable_lo(b2k_index* h, cudaStream_t st) {
@@ -191,6 +202,18 @@ int enable_lo(b2k_index* h, cudaStream_t st) {
     h->lo_enabled = true;
     if (h->k3) k3_invalidate_maps(h->k3);
     if (h->ntotal > 0) return launch_row_prep(h->x, h->ntotal, h->d, h->norms, h->xlo, nullptr, st);
+    return B2K_OK;
+}
+
+// bf16 copies of the rows for the bf16 screening mode (half the size of the rows themselves).
+int enable_bf(b2k_index* h, cudaStream_t st) {
+    if (h->bf_enabled) return B2K_OK;
+    if (h->capacity > 0) {
+        cudaError_t e = cudaMalloc(&h->xbf, (size_t)h->capacity * h->d * 2);
+        if (e != cudaSuccess) { cudaGetLastError(); set_error("cudaMalloc for bf16 rows failed: %s", cudaGetErrorString(e)); return B2K_ENOMEM; }
+    }
+    h->bf_enabled = true;
+    if (h->ntotal > 0) return launch_row_bf16(h->x, h->ntotal, h->d, h->xbf, nullptr, h->done + MAX_ERR_SLOT, st);
     return B2K_OK;
 }
 
@@ -259,7 +282,7 @@ int b2k_destroy(b2k_index* h) {
     DeviceGuard g(h->device);
     cudaDeviceSynchronize();
     if (h->k3) k3_destroy(h->k3);
-    cudaFree(h->x); cudaFree(h->norms); cudaFree(h->xlo); cudaFree(h->ws); cudaFree(h->done);
+    cudaFree(h->x); cudaFree(h->norms); cudaFree(h->xlo); cudaFree(h->xbf); cudaFree(h->ws); cudaFree(h->done);
     if (h->pin) cudaFreeHost(h->pin);
     if (h->ev_rows) cudaEventDestroy(h->ev_rows);
     if (h->ev_ws) cudaEventDestroy(h->ev_ws);
@@ -291,8 +314,12 @@ int b2k_set_option(b2k_index* h, const char* key, int64_t value) {
         h->opt_sep = (int)value;
         if (h->k3) k3_set_sep_mode(h->k3, h->opt_sep);
     } else if (!strcmp(key, "tensor_mode")) {
-        if (value < 0 || value > 2) { set_error("option tensor_mode must be 0 (auto), 1 (3xTF32) or 2 (screening + exact re-rank)"); return B2K_EINVAL; }
+        if (value < 0 || value > 3) { set_error("option tensor_mode must be 0 (auto), 1 (3xTF32), 2 (TF32 screening + exact re-rank) or 3 (bf16 screening + exact re-rank)"); return B2K_EINVAL; }
         h->opt_tensor_mode = (int)value;
+    } else if (!strcmp(key, "tensor_segments")) {
+        if (value < 0 || value > 1) { set_error("option tensor_segments must be 0 (one launch) or 1 (segments with bound refreshes)"); return B2K_EINVAL; }
+        h->opt_segments = (int)value;
+        if (h->k3) k3_set_segments(h->k3, h->opt_segments);
     } else if (!strcmp(key, "timing")) {
         h->opt_timing = value != 0;
         if (h->k3) k3_set_timing(h->k3, h->opt_timing != 0);
@@ -341,8 +368,9 @@ int b2k_reset(b2k_index* h) {
     std::lock_guard<std::mutex> lk(h->mu);
     DeviceGuard g(h->device);
     B2K_CUDA(cudaDeviceSynchronize());
-    cudaFree(h->x); cudaFree(h->norms); cudaFree(h->xlo);
+    cudaFree(h->x); cudaFree(h->norms); cudaFree(h->xlo); cudaFree(h->xbf);
     h->x = h->norms = h->xlo = nullptr;
+    h->xbf = nullptr;
     h->ntotal = h->capacity = 0;
     if (h->k3) k3_invalidate_maps(h->k3);
     B2K_CUDA(cudaMemset(h->done, 0, 256));
@@ -459,13 +487,18 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
     if (h->ntotal == 0) {
         rc = launch_fill_empty(Dd, Id, nq * kk, st);
     } else if (want_tc) {
-        const bool screen = h->opt_tensor_mode != 1;
-        if (!screen) rc = enable_lo(h, st);
+        // 1 = 3xTF32, 2 = TF32 screening, 3 = bf16 screening (rows need a 16-byte bf16 pitch; if the bf16
+        // copies do not fit in memory the TF32 screening serves instead)
+        int mode = h->opt_tensor_mode == 0 ? 2 : h->opt_tensor_mode;
+        if (mode == 3 && h->d % 8 != 0) mode = 2;
+        if (mode == 3 && enable_bf(h, st) != B2K_OK) mode = 2;
+        if (mode == 1) rc = enable_lo(h, st);
         if (!rc && !h->k3) {
             rc = k3_create(&h->k3, h->device, h->sm_count);
             if (!rc) k3_set_timing(h->k3, h->opt_timing != 0);
             if (!rc) k3_set_cta_group(h->k3, h->opt_cta_group);
             if (!rc) k3_set_sep_mode(h->k3, h->opt_sep);
+            if (!rc) k3_set_segments(h->k3, h->opt_segments);
         }
         if (!rc) h->last_path = 2;
         // like faiss (query blocks of 4096), long batches go through in chunks: the candidate-list
@@ -473,15 +506,15 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
         for (int64_t q0 = 0; q0 < nq && !rc; q0 += TC_QUERY_CHUNK) {
             const int64_t nqc = nq - q0 < TC_QUERY_CHUNK ? nq - q0 : TC_QUERY_CHUNK;
             int overflowed = 0;
-            rc = k3_search(h->k3, h->x, h->xlo, h->norms, h->done + MAX_NORM_SLOT, h->ntotal, h->capacity, h->d,
-                           qd + q0 * (int64_t)h->d, nqc, kk, Dd + q0 * kk, Id + q0 * kk, ws_tail, st, screen ? 0 : 1,
-                           &overflowed);
+            rc = k3_search(h->k3, h->x, h->xlo, h->xbf, h->norms, h->done + MAX_NORM_SLOT, h->done + MAX_ERR_SLOT, h->ntotal,
+                           h->d, qd + q0 * (int64_t)h->d, nqc, kk, Dd + q0 * kk, Id + q0 * kk, ws_tail, st, mode, &overflowed);
             if (!rc && overflowed) {
                 // masses of near-duplicates around the k-th neighbour: repeat this chunk with 3xTF32
                 ++h->stat_screen_fallbacks;
                 rc = enable_lo(h, st);
-                if (!rc) rc = k3_search(h->k3, h->x, h->xlo, h->norms, h->done + MAX_NORM_SLOT, h->ntotal, h->capacity, h->d,
-                                        qd + q0 * (int64_t)h->d, nqc, kk, Dd + q0 * kk, Id + q0 * kk, ws_tail, st, 1, nullptr);
+                if (!rc) rc = k3_search(h->k3, h->x, h->xlo, h->xbf, h->norms, h->done + MAX_NORM_SLOT, h->done + MAX_ERR_SLOT,
+                                        h->ntotal, h->d, qd + q0 * (int64_t)h->d, nqc, kk, Dd + q0 * kk, Id + q0 * kk, ws_tail,
+                                        st, 1, nullptr);
             }
         }
     } else {

@@ -8,6 +8,8 @@
 //     x = hi + lo,  hi = x with the low 13 mantissa bits cleared (what a kind::tf32 MMA
 //     reads from a raw fp32 operand), lo = x - hi (exact in fp32).
 // Roofline: HBM; algorithmic bytes per row = d*4 read (+ d*4 written when lo is emitted).
+#include <cuda_bf16.h>
+
 #include "common.cuh"
 #include "kernels.h"
 
@@ -94,6 +96,58 @@ int launch_row_prep(const float* X, int64_t n, int d, float* norms, float* xlo, 
     if (blocks > 148 * 16) blocks = 148 * 16;
     if (vec) row_prep_vec_kernel<<<(unsigned)blocks, 256, 0, st>>>(X, n, d, norms, xlo, max_norm_bits);
     else row_prep_any_kernel<<<(unsigned)blocks, 256, 0, st>>>(X, n, d, norms, xlo, max_norm_bits);
+    count_launch();
+    B2K_CUDA(cudaGetLastError());
+    return B2K_OK;
+}
+
+// ---- bf16 copies for the bf16 screening mode of K3 ---------------------------------------------
+// xb = x rounded to bf16 (round to nearest even), err2 = |x - xb|^2 per row.  The screening slack
+// is built from these measured rounding errors (Cauchy-Schwarz), not from the worst case 2^-8.
+// 8 lanes per row, 4 rows per warp; needs d % 8 == 0 (16-byte bf16 row pitch for TMA).
+__global__ void __launch_bounds__(256)
+row_bf16_kernel(const float* __restrict__ X, int64_t n, int d, __nv_bfloat16* __restrict__ xb,
+                float* __restrict__ err2, unsigned int* __restrict__ max_err_bits) {
+    const int lane = threadIdx.x & 31;
+    float vmax = 0.f;
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const int g = lane >> 3, cl = (lane & 7) * 4;
+    for (int64_t r0 = warp * 4; r0 < n; r0 += nwarps * 4) {
+        const int64_t row = r0 + g;
+        float acc = 0.f;
+        if (row < n) {
+            const float* xr = X + row * (int64_t)d;
+            for (int c = cl; c < d; c += 32) {
+                float4 v = ldg_stream(reinterpret_cast<const float4*>(xr + c));
+                __nv_bfloat162 b01 = __floats2bfloat162_rn(v.x, v.y), b23 = __floats2bfloat162_rn(v.z, v.w);
+                const float e0 = v.x - __low2float(b01), e1 = v.y - __high2float(b01);
+                const float e2 = v.z - __low2float(b23), e3 = v.w - __high2float(b23);
+                acc = fmaf(e0, e0, acc); acc = fmaf(e1, e1, acc); acc = fmaf(e2, e2, acc); acc = fmaf(e3, e3, acc);
+                uint2 o;
+                o.x = *reinterpret_cast<unsigned int*>(&b01);
+                o.y = *reinterpret_cast<unsigned int*>(&b23);
+                *reinterpret_cast<uint2*>(xb + row * (int64_t)d + c) = o;
+            }
+        }
+        acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+        acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+        acc += __shfl_xor_sync(0xffffffffu, acc, 4);
+        if (row < n && err2 && (lane & 7) == 0) err2[row] = acc;
+        if (row < n && acc <= FLT_MAX) vmax = fmaxf(vmax, acc);  // rows with non-finite values never match anyway
+    }
+    publish_max(vmax, max_err_bits, lane);
+}
+
+int launch_row_bf16(const float* X, int64_t n, int d, void* xb, float* err2, unsigned int* max_err_bits, cudaStream_t st) {
+    if (n <= 0) return B2K_OK;
+    if (d % 8 != 0 || (reinterpret_cast<uintptr_t>(X) & 15) || (reinterpret_cast<uintptr_t>(xb) & 7)) {
+        set_error("bf16 row copies need d %% 8 == 0 and aligned rows");
+        return B2K_EINVAL;
+    }
+    int64_t blocks = (n + 31) / 32;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    row_bf16_kernel<<<(unsigned)blocks, 256, 0, st>>>(X, n, d, static_cast<__nv_bfloat16*>(xb), err2, max_err_bits);
     count_launch();
     B2K_CUDA(cudaGetLastError());
     return B2K_OK;

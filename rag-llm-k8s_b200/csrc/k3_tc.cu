@@ -77,7 +77,7 @@ template <int CG, int NS, int MODE>
 struct K3Smem {
     static constexpr int B_ROWS = K3_BN / CG;
     static constexpr int B_BYTES = B_ROWS * K3_BK * 4;
-    static constexpr int NPART = MODE == 2 ? 1 : 2;  // hi only (screening), or hi + lo (3xTF32)
+    static constexpr int NPART = (MODE == 2 || MODE == 3) ? 1 : 2;  // one operand pair (screening), or hi + lo (3xTF32)
     static constexpr int OFF_B = NPART * K3_A_BYTES;  // stage = [Q_hi][Q_lo?][X_hi][X_lo?]
     static constexpr int STAGE_BYTES = NPART * (K3_A_BYTES + B_BYTES);
     static constexpr int OFF_XN = NS * STAGE_BYTES;            // float[2][256]
@@ -128,39 +128,53 @@ __device__ __forceinline__ float reg_select32(const float (&v)[32], int c) {
     }
 }
 
-// One thread, 32 consecutive accumulator columns of its query row: branch-free filter, then the
-// (rare) survivors.  v = main accumulator, w = cross-term accumulator (SEP only).
+// One thread, 32 consecutive accumulator columns of its query row.  The dense part is two
+// instructions per element or fewer: s = ||x||^2 - 2 ip (one FFMA) and "any s <= t" over four
+// independent chains (nvcc turns the OR of compares into 3-input FMNMX: 1.5 per element).  With
+// the bound refreshed between segments of the pass a warp meets a survivor in about one chunk
+// out of ten; only then are the columns located (second, mask-building walk).
+// v = main accumulator, w = cross-term accumulator (SEP only).
 template <bool SEP>
 __device__ __forceinline__ void k3_filter_chunk(const uint32_t (&v)[32], const uint32_t (&w)[32], const float* xn,
                                                 float t_cmp, float qn, float tau_eff, u64 kth, uint32_t row0,
                                                 u64* list, int& cnt) {
-    uint32_t mask = 0;
-    float ip[32];
+    bool any[4] = {false, false, false, false};
 #pragma unroll
     for (int c = 0; c < 32; c += 4) {
         const float4 x4 = *reinterpret_cast<const float4*>(xn + c);
         const float xs[4] = {x4.x, x4.y, x4.z, x4.w};
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            ip[c + j] = SEP ? __uint_as_float(v[c + j]) + __uint_as_float(w[c + j]) : __uint_as_float(v[c + j]);
-            const float s = fmaf(-2.f, ip[c + j], xs[j]);
-            mask |= (s <= t_cmp) ? (1u << (c + j)) : 0u;
+            const float ip = SEP ? __uint_as_float(v[c + j]) + __uint_as_float(w[c + j]) : __uint_as_float(v[c + j]);
+            any[j] |= fmaf(-2.f, ip, xs[j]) <= t_cmp;
         }
     }
-    // Survivors.  With warm-started thresholds a THREAD sees one every few tiles, but a WARP (32
-    // threads x 32 columns) sees one in most chunks, so this path must be cheap at warp level: a
-    // loop over the set bits (usually one trip for the whole warp), the value picked out of the
-    // registers by a 5-level select tree -- not 32 predicated copies of the body.
-    while (mask) {
-        const int c = __ffs(mask) - 1;
-        mask &= mask - 1;
-        const float ipc = reg_select32<0, 32>(ip, c);
-        const float xv = xn[c];
-        float dist = (qn + xv) - 2.f * ipc;  // oracle rule (2), then clamp
-        dist = dist < 0.f ? 0.f : dist;
-        if (dist <= tau_eff) {
-            const u64 key = make_key(dist, row0 + c);
-            if (key < kth) { list[cnt] = key; ++cnt; }
+    if (any[0] | any[1] | any[2] | any[3]) {
+        // which columns: a bit mask built without branches, then a loop over its set bits (usually
+        // one), the value picked out of the registers by a 5-level select tree
+        uint32_t mask = 0;
+        float ip[32];
+#pragma unroll
+        for (int c = 0; c < 32; c += 4) {
+            const float4 x4 = *reinterpret_cast<const float4*>(xn + c);
+            const float xs[4] = {x4.x, x4.y, x4.z, x4.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                ip[c + j] = SEP ? __uint_as_float(v[c + j]) + __uint_as_float(w[c + j]) : __uint_as_float(v[c + j]);
+                mask |= (fmaf(-2.f, ip[c + j], xs[j]) <= t_cmp) ? (1u << (c + j)) : 0u;
+            }
+        }
+        while (mask) {
+            const int c = __ffs(mask) - 1;
+            mask &= mask - 1;
+            const float ipc = reg_select32<0, 32>(ip, c);
+            const float xv = xn[c];
+            float dist = (qn + xv) - 2.f * ipc;  // oracle rule (2), then clamp
+            dist = dist < 0.f ? 0.f : dist;
+            if (dist <= tau_eff) {
+                const u64 key = make_key(dist, row0 + c);
+                if (key < kth) { list[cnt] = key; ++cnt; }
+            }
         }
     }
 }
@@ -179,7 +193,9 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
                       const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_xl,
                       const K3Params p) {
     constexpr bool SEP = (MODE == 1);  // separate accumulator for the cross terms
-    constexpr bool SCREEN = (MODE == 2);  // one TF32 product + error slack; exact distances come from the re-rank kernel
+    constexpr bool SCREEN = (MODE == 2 || MODE == 3);  // one product + error slack; exact distances come from the re-rank kernel
+    constexpr bool BF16 = (MODE == 3);                  // the screening product runs on bf16 copies of the rows (kind::f16)
+    constexpr int BKE = BF16 ? 64 : 32;                 // elements per k-chunk: one 128-byte swizzle row either way
     using L = K3Smem<CG, NS, MODE>;
     // No integer round-trip on this pointer: the compiler must keep seeing shared memory here, or
     // every access through it becomes a generic LD/ST (that cost 2k cycles per 32 accumulator
@@ -201,7 +217,7 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t rank = (CG == 2) ? ptx::cluster_ctarank() : 0u;
-    const int nkc = (p.d + K3_BK - 1) / K3_BK;
+    const int nkc = (p.d + BKE - 1) / BKE;
 
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tmap(&tm_q); ptx::prefetch_tmap(&tm_ql); ptx::prefetch_tmap(&tm_x); ptx::prefetch_tmap(&tm_xl);
@@ -244,7 +260,14 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
                     } else {
                         u = (long long)atomicAdd(p.next_unit, 1ull);
                     }
-                    if (u >= p.nunits) u = -1;
+                    // consumers get the unit already split into (tile, query block): a 64-bit division
+                    // per unit in each epilogue warp was ~350 cycles of dependent instructions, four times
+                    if (u < 0 || u >= p.nunits) {
+                        u = -1;
+                    } else {
+                        const uint32_t tt = (uint32_t)u / (uint32_t)p.nqb;  // nunits < 2^31 (2^24 tiles x 32 query blocks)
+                        u = ((long long)tt << 8) | (long long)((uint32_t)u - tt * (uint32_t)p.nqb);
+                    }
                     sched_u[ss] = u;
                     if (CG == 2) ptx::st_cluster_b64(&sched_u[ss], 1, (uint64_t)u);
                     ptx::mbar_arrive(&sfull[ss]);
@@ -256,8 +279,8 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
                 }
                 if (++ss == K3_NSCHED) { ss = 0; sph ^= 1; }
                 if (u < 0) break;
-                const int64_t t = u / p.nqb;
-                const int qb = (int)(u - t * p.nqb);
+                const int64_t t = u >> 8;
+                const int qb = (int)(u & 255);
                 const int qrow0 = qb * (K3_BM * CG) + (int)rank * K3_BM;
                 const int64_t xrow0 = t * K3_BN + (int64_t)rank * L::B_ROWS;
                 for (int kc = 0; kc < nkc; ++kc) {
@@ -265,17 +288,17 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
                     unsigned char* sb = smem + stage * L::STAGE_BYTES;
                     if (CG == 1) {
                         ptx::mbar_arrive_expect_tx(&full[stage], L::STAGE_BYTES);
-                        ptx::tma_load_2d(sb, &tm_q, &full[stage], kc * K3_BK, qrow0);
-                        if (!SCREEN) ptx::tma_load_2d(sb + K3_A_BYTES, &tm_ql, &full[stage], kc * K3_BK, qrow0);
-                        ptx::tma_load_2d(sb + L::OFF_B, &tm_x, &full[stage], kc * K3_BK, (int)xrow0);
-                        if (!SCREEN) ptx::tma_load_2d(sb + L::OFF_B + L::B_BYTES, &tm_xl, &full[stage], kc * K3_BK, (int)xrow0);
+                        ptx::tma_load_2d(sb, &tm_q, &full[stage], kc * BKE, qrow0);
+                        if (!SCREEN) ptx::tma_load_2d(sb + K3_A_BYTES, &tm_ql, &full[stage], kc * BKE, qrow0);
+                        ptx::tma_load_2d(sb + L::OFF_B, &tm_x, &full[stage], kc * BKE, (int)xrow0);
+                        if (!SCREEN) ptx::tma_load_2d(sb + L::OFF_B + L::B_BYTES, &tm_xl, &full[stage], kc * BKE, (int)xrow0);
                     } else {
                         if (rank == 0) ptx::mbar_arrive_expect_tx(&full[stage], 2 * L::STAGE_BYTES);
                         else ptx::mbar_arrive_cluster(&full[stage], 0);
-                        ptx::tma_load_2d_pair(sb, &tm_q, &full[stage], kc * K3_BK, qrow0);
-                        if (!SCREEN) ptx::tma_load_2d_pair(sb + K3_A_BYTES, &tm_ql, &full[stage], kc * K3_BK, qrow0);
-                        ptx::tma_load_2d_pair(sb + L::OFF_B, &tm_x, &full[stage], kc * K3_BK, (int)xrow0);
-                        if (!SCREEN) ptx::tma_load_2d_pair(sb + L::OFF_B + L::B_BYTES, &tm_xl, &full[stage], kc * K3_BK, (int)xrow0);
+                        ptx::tma_load_2d_pair(sb, &tm_q, &full[stage], kc * BKE, qrow0);
+                        if (!SCREEN) ptx::tma_load_2d_pair(sb + K3_A_BYTES, &tm_ql, &full[stage], kc * BKE, qrow0);
+                        ptx::tma_load_2d_pair(sb + L::OFF_B, &tm_x, &full[stage], kc * BKE, (int)xrow0);
+                        if (!SCREEN) ptx::tma_load_2d_pair(sb + L::OFF_B + L::B_BYTES, &tm_xl, &full[stage], kc * BKE, (int)xrow0);
                     }
                     if (++stage == NS) { stage = 0; phase ^= 1; }
                 }
@@ -284,7 +307,7 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
     } else if (warp == 1) {
         // ===================== MMA issuer (leader CTA only) =====================
         if (rank == 0) {
-            constexpr uint32_t idesc = ptx::umma_idesc_tf32(K3_BM * CG, K3_BN);
+            constexpr uint32_t idesc = BF16 ? ptx::umma_idesc_bf16(K3_BM * CG, K3_BN) : ptx::umma_idesc_tf32(K3_BM * CG, K3_BN);
             int stage = 0, as = 0, ss = 0;
             uint32_t phase = 0, aphase = 0, sph = 0;
             for (;;) {
@@ -307,7 +330,9 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
 #pragma unroll
                         for (int ks = 0; ks < K3_BK / 8; ++ks) {
                             const uint64_t off = (uint64_t)(ks * 32 >> 4);  // 8 fp32 = 32 bytes along K
-                            if constexpr (SCREEN) {
+                            if constexpr (BF16) {
+                                ptx::mma_bf16<CG>(d_tmem, a_hi + off, b_hi + off, idesc, (kc | ks) != 0);  // 16 bf16 = 32 bytes along K
+                            } else if constexpr (SCREEN) {
                                 ptx::mma_tf32<CG>(d_tmem, a_hi + off, b_hi + off, idesc, (kc | ks) != 0);
                             } else {
                                 ptx::mma_tf32<CG>(d_corr, a_lo + off, b_hi + off, idesc, (kc | ks) != 0);  // small terms first
@@ -349,7 +374,7 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
             return CG == 1 ? ptx::mbar_try_wait(&sfull[ss], sph) : ptx::mbar_try_wait_cluster(&sfull[ss], sph);
         };
         auto issue_norms = [&](long long u, float* dst) {
-            const int64_t t = u / p.nqb;
+            const int64_t t = u >> 8;
             for (int j = epi_tid; j < K3_BN; j += K3_EPI_THREADS) {
                 const int64_t r = t * K3_BN + j;
                 if (r < p.n && j < p.tile_cols) ptx::cp_async_4(dst + j, p.norms + r);
@@ -373,11 +398,11 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
         QState S;
         if (cur >= 0) {
             issue_norms(cur, xn_s);
-            load_state((int)(cur % p.nqb), S);
+            load_state((int)(cur & 255), S);
         }
         while (cur >= 0) {
-            const int64_t t = cur / p.nqb;
-            const int qb = (int)(cur - t * p.nqb);
+            const int64_t t = cur >> 8;  // units arrive as (tile << 8) | query block
+            const int qb = (int)(cur & 255);
             const int64_t qi = qi_of(qb);
             const bool valid = qi < p.nq;
             const int64_t sidx = sidx_of(qb);
@@ -404,7 +429,7 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
                 nxt = take();
                 if (nxt >= 0) {
                     issue_norms(nxt, xn_s + (xb ^ 1) * K3_BN);
-                    if ((int)(nxt % p.nqb) != qb) { load_state((int)(nxt % p.nqb), N); n_loaded = true; }
+                    if ((int)(nxt & 255) != qb) { load_state((int)(nxt & 255), N); n_loaded = true; }
                 }
             }
 
@@ -489,7 +514,7 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
                 nxt = take();
                 if (nxt >= 0) issue_norms(nxt, xn_s + (xb ^ 1) * K3_BN);
             }
-            const int nqb_next = nxt >= 0 ? (int)(nxt % p.nqb) : -1;
+            const int nqb_next = nxt >= 0 ? (int)(nxt & 255) : -1;
             if (nqb_next == qb) {
                 // same query block again: the list state stays in registers, only the shared bound is refreshed
                 S.cnt = cnt; S.tau = tau; S.kth = kth;
@@ -529,6 +554,8 @@ __global__ void k3_init_kernel(int64_t nslots, int* cnt, float* tau, u64* kth, i
     if (i < nslots) { cnt[i] = 0; tau[i] = FLT_MAX; kth[i] = (u64)FLT_MAX_BITS << 32; }
     if (gts && i < nq) gts[i] = FLT_MAX_BITS;
 }
+
+__global__ void k3_set_counter_kernel(u64* next_unit, u64 value) { *next_unit = value; }
 
 // ---- K4: per query, merge the lists of every CTA that saw it ---------------------------------
 // One CTA per query.  The lists hold every key under the warm-started shared bound: a few
@@ -720,6 +747,22 @@ __global__ void k3_slack_kernel(int64_t nq, const float* __restrict__ qn, const 
     if (i < nq) slack2[i] = coef * sqrtf(qn[i]) * sqrtf(__uint_as_float(*max_norm_bits));
 }
 
+// bf16 screening: q~, x~ are the bf16 roundings.  q.x - q~.x~ = (q - q~).x + q~.(x - x~), so by
+// Cauchy-Schwarz |q.x - q~.x~| <= |q - q~| max|x| + |q~| max|x - x~|, with the rounding-error norms
+// MEASURED (K1 bf16 pass: per query here, running maximum over the rows at add time) instead of the
+// worst case 2^-8: typically 0.3 * 2^-8.  |q~| <= |q| (1 + 2^-8).  Products of two bf16 values are
+// exact in the fp32 accumulator; the accumulation error term is the same as in the TF32 mode.
+// On entry slack2[i] holds |q_i - q~_i|^2; on exit 2 * sigma_i.
+__global__ void k3_slack_bf16_kernel(int64_t nq, const float* __restrict__ qn, const unsigned int* __restrict__ max_norm_bits,
+                                     const unsigned int* __restrict__ max_err_bits, float acc_coef, float* __restrict__ slack2) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nq) return;
+    const float nqv = sqrtf(qn[i]), eq = sqrtf(slack2[i]);
+    const float mx = sqrtf(__uint_as_float(*max_norm_bits)), ex = sqrtf(__uint_as_float(*max_err_bits));
+    const float sigma = 2.f * 1.02f * (eq * mx + 1.004f * nqv * ex) + acc_coef * nqv * mx;
+    slack2[i] = 2.f * sigma;
+}
+
 __global__ void __launch_bounds__(K4_THREADS)
 k6_rerank_kernel(const K3Params p, int cg, int ncta, const float* __restrict__ X, const float* __restrict__ Q,
                  float* __restrict__ D, int64_t* __restrict__ I) {
@@ -786,9 +829,10 @@ struct K3State {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     unsigned int* flag_host = nullptr;  // pinned: overflow flag of the screening mode
     bool timing = false;
-    int last_mode = 0;  // 1 = 3xTF32, 2 = screening + re-rank (what the last search ran)
+    int last_mode = 0;  // 1 = 3xTF32, 2 = TF32 screening + re-rank, 3 = bf16 screening + re-rank (what the last search ran)
     int sep_mode = 0;  // long-row accuracy: 0 auto (d >= 512: separate accumulator), 1 separate accumulator, 2 off
     bool timed = false;
+    int segments = 1;  // cut the main pass into segments with a bound refresh in between (0 = one launch)
 };
 
 static int k3_P(int k) { return next_pow2(k + K3_BN); }
@@ -880,6 +924,7 @@ void k3_invalidate_maps(K3State*) {}  // maps are re-encoded on every search (ho
 void k3_set_timing(K3State* s, bool on) { s->timing = on; }
 void k3_set_cta_group(K3State* s, int cg) { s->cg = (cg == 1 || cg == 2) ? cg : 0; }
 void k3_set_sep_mode(K3State* s, int m) { s->sep_mode = m; }
+void k3_set_segments(K3State* s, int on) { s->segments = on; }
 int k3_last_mode(const K3State* s) { return s->last_mode; }
 
 int k3_last_kernel_ms(K3State* s, float* ms) {
@@ -889,12 +934,12 @@ int k3_last_kernel_ms(K3State* s, float* ms) {
     return B2K_OK;
 }
 
-static int make_map(K3State* s, CUtensorMap* m, const float* base, int64_t rows, int d, int box_rows) {
+static int make_map(K3State* s, CUtensorMap* m, const void* base, int64_t rows, int d, int box_rows, bool bf16 = false) {
     cuuint64_t gdim[2] = {(cuuint64_t)d, (cuuint64_t)rows};
-    cuuint64_t gstr[1] = {(cuuint64_t)d * 4};
-    cuuint32_t box[2] = {(cuuint32_t)K3_BK, (cuuint32_t)box_rows};
+    cuuint64_t gstr[1] = {(cuuint64_t)d * (bf16 ? 2 : 4)};
+    cuuint32_t box[2] = {(cuuint32_t)(bf16 ? 64 : K3_BK), (cuuint32_t)box_rows};  // 128 bytes wide either way
     cuuint32_t estr[2] = {1, 1};
-    CUresult r = s->encode(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), gdim, gstr, box, estr,
+    CUresult r = s->encode(m, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), gdim, gstr, box, estr,
                            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
@@ -938,6 +983,10 @@ static int launch_k3_any(int cg, int P, int mode, const CUtensorMap& mq, const C
         B2K_K3_CASE(1)
     }
 #undef B2K_K3_CASE
+    if (mode == 3) {  // bf16 screening (one CTA per tile)
+        if (P <= 512) return launch_k3<1, 4, 3>(mq, mql, mx, mxl, p, ncta, st);
+        return launch_k3<1, 2, 3>(mq, mql, mx, mxl, p, ncta, st);
+    }
     if (mode == 2) {  // screening: one operand pair per stage (48 KB / 32 KB), deeper rings
         if (cg == 1) {
             if (P <= 512) return launch_k3<1, 4, 2>(mq, mql, mx, mxl, p, ncta, st);
@@ -950,15 +999,17 @@ static int launch_k3_any(int cg, int P, int mode, const CUtensorMap& mq, const C
     return B2K_EINVAL;
 }
 
-int k3_search(K3State* s, const float* x, const float* xlo, const float* norms, const unsigned int* max_norm_bits,
-              int64_t n, int64_t capacity, int d, const float* q, int64_t nq, int k, float* D, int64_t* I,
-              unsigned char* scratch, cudaStream_t st, int exact, int* overflowed) {
-    (void)capacity;
-    const bool screen = !exact;
+int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, const float* norms,
+              const unsigned int* max_norm_bits, const unsigned int* max_err_bits, int64_t n, int d, const float* q,
+              int64_t nq, int k, float* D, int64_t* I, unsigned char* scratch, cudaStream_t st, int mode,
+              int* overflowed) {
+    const bool screen = mode != 1;
+    const bool bf16 = mode == 3;
+    if (bf16 && (d % 8 != 0 || !xbf || !max_err_bits)) { set_error("tensor kernel: bf16 screening needs d %% 8 == 0 and the bf16 rows"); return B2K_EINVAL; }
     if (overflowed) *overflowed = 0;
-    s->last_mode = screen ? 2 : 1;
-    K3Layout L = k3_layout(s->sm_count, d, nq, k, s->cg, !exact);
-    float* qlo = reinterpret_cast<float*>(scratch + L.off_qlo);
+    s->last_mode = mode;
+    K3Layout L = k3_layout(s->sm_count, d, nq, k, s->cg, screen);
+    float* qlo = reinterpret_cast<float*>(scratch + L.off_qlo);  // 3xTF32: residual rows; bf16 screening: bf16 queries
     K3Params p;
     p.n = n; p.d = d; p.nq = nq; p.k = k; p.P = L.P; p.nqb = L.nqb; p.qpc = L.qpc;
     const int64_t ntiles = (n + K3_BN - 1) / K3_BN;
@@ -982,7 +1033,15 @@ int k3_search(K3State* s, const float* x, const float* xlo, const float* norms, 
     // queries: norms (+ TF32 residual rows for the exact mode; K1 reused), screening slack, list state reset
     int rc = launch_row_prep(q, nq, d, const_cast<float*>(p.qn), screen ? nullptr : qlo, nullptr, st);
     if (rc) return rc;
-    if (screen) {
+    if (bf16) {
+        rc = launch_row_bf16(q, nq, d, qlo, const_cast<float*>(p.slack2), nullptr, st);
+        if (rc) return rc;
+        const float acc_coef = 8e-6f * (float)d / 256.f;
+        k3_slack_bf16_kernel<<<(unsigned)((nq + 255) / 256), 256, 0, st>>>(nq, p.qn, max_norm_bits, max_err_bits, acc_coef,
+                                                                           const_cast<float*>(p.slack2));
+        count_launch();
+        B2K_CUDA(cudaGetLastError());
+    } else if (screen) {
         const float coef = 2.f * (1.02f + 8e-6f * (float)d) / 256.f;  // 2 * sigma_q / (|q| * max|x|), see k3_slack_kernel
         k3_slack_kernel<<<(unsigned)((nq + 255) / 256), 256, 0, st>>>(nq, p.qn, max_norm_bits, coef, const_cast<float*>(p.slack2));
         count_launch();
@@ -996,10 +1055,17 @@ int k3_search(K3State* s, const float* x, const float* xlo, const float* norms, 
 
     B2K_CUDA(cudaFuncSetAttribute(k4_merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(K4Smem)));
     CUtensorMap mq, mql, mx, mxl;
-    if ((rc = make_map(s, &mq, q, nq, d, K3_BM))) return rc;
-    if ((rc = make_map(s, &mql, screen ? q : qlo, nq, d, K3_BM))) return rc;
-    if ((rc = make_map(s, &mx, x, n, d, K3_BN / L.cg))) return rc;
-    if ((rc = make_map(s, &mxl, screen ? x : xlo, n, d, K3_BN / L.cg))) return rc;
+    if (bf16) {
+        if ((rc = make_map(s, &mq, qlo, nq, d, K3_BM, true))) return rc;
+        if ((rc = make_map(s, &mx, xbf, n, d, K3_BN / L.cg, true))) return rc;
+        mql = mq;
+        mxl = mx;
+    } else {
+        if ((rc = make_map(s, &mq, q, nq, d, K3_BM))) return rc;
+        if ((rc = make_map(s, &mql, screen ? q : qlo, nq, d, K3_BM))) return rc;
+        if ((rc = make_map(s, &mx, x, n, d, K3_BN / L.cg))) return rc;
+        if ((rc = make_map(s, &mxl, screen ? x : xlo, n, d, K3_BN / L.cg))) return rc;
+    }
 
     // Warm start.  Round A: the first 64 rows of one tile per CTA (pair) with open thresholds --
     // every key is kept, so the pass is kept small; per query the k-th smallest distance of that
@@ -1010,8 +1076,9 @@ int k3_search(K3State* s, const float* x, const float* xlo, const float* norms, 
     const int nclusters = L.ncta / L.cg;
     // kernel mode: 0 3xTF32 in one accumulator (double-buffered), 1 3xTF32 with a separate cross-term
     // accumulator, 2 screening (one product; exact distances from the re-rank kernel)
-    const int sep = screen ? 2 : (s->sep_mode == 1 || (s->sep_mode == 0 && d >= 512)) ? 1 : 0;
+    const int sep = bf16 ? 3 : screen ? 2 : (s->sep_mode == 1 || (s->sep_mode == 0 && d >= 512)) ? 1 : 0;
     const int cols_a = 64;
+    int64_t warm_rows = 0;  // rows behind the bound the main pass starts with
     if (ntiles >= 2 * (int64_t)nclusters && (int64_t)nclusters * cols_a >= 2 * (int64_t)k) {
         K3Params pre = p;
         pre.static_mode = 1;
@@ -1031,6 +1098,7 @@ int k3_search(K3State* s, const float* x, const float* xlo, const float* norms, 
         k3_init_kernel<<<(unsigned)((nslots + 255) / 256), 256, 0, st>>>(nslots, p.cnt, p.tau, p.kth, nq, nullptr, p.next_unit, nullptr);
         count_launch(2);
         B2K_CUDA(cudaGetLastError());
+        warm_rows = (int64_t)nclusters * cols_a / G;
         // rows the second round should cover so that the full pass leaves ~<= 64 keys per list
         const double want_rows = (double)n * k / ((double)nclusters * 64.0);
         int tpc = (int)(want_rows / ((double)nclusters * K3_BN) + 0.999);
@@ -1049,12 +1117,46 @@ int k3_search(K3State* s, const float* x, const float* xlo, const float* norms, 
             k3_init_kernel<<<(unsigned)((nslots + 255) / 256), 256, 0, st>>>(nslots, p.cnt, p.tau, p.kth, nq, nullptr, p.next_unit, nullptr);
             count_launch(2);
             B2K_CUDA(cudaGetLastError());
+            warm_rows = (int64_t)nclusters * tpc * K3_BN;
         }
     }
 
+    // Main pass, in segments.  The warm start bounds the k-th distance by the k-th of a sample of
+    // `warm_rows` rows, under which about k * n / warm_rows rows of the whole database fall (~9.5k per
+    // query whatever k is) -- and inside one launch the bound barely moves, because a list only
+    // learns a better one when it compacts.  So the pass is cut where the scanned fraction has grown
+    // by a factor r, and between two segments K4 (threshold mode, ~50 us) turns everything kept so far
+    // into the exact k-th distance of the rows scanned so far.  Each segment then keeps about
+    // k * (r - 1) keys per query instead of thousands, which is what the epilogue's survivor path
+    // and the final merge pay for.
+    long long seg_end[8];
+    int nseg = 0;
+    if (warm_rows > 0 && s->segments) {
+        const double r = 1.0 + (double)(3 * k > 400 ? 3 * k : 400) / (double)k;
+        const long long upc = p.nunits / nclusters;
+        int maxb = (int)(upc / 128);
+        if (maxb > 6) maxb = 6;
+        double g = (double)warm_rows / (double)n * r;
+        while (g < 0.6 && nseg < maxb) {
+            const long long tiles = (long long)(g * (double)ntiles);
+            if (tiles > 0 && (nseg == 0 || tiles * L.nqb > seg_end[nseg - 1])) seg_end[nseg++] = tiles * L.nqb;
+            g *= r;
+        }
+    }
+    seg_end[nseg++] = p.nunits;
     if (s->timing) B2K_CUDA(cudaEventRecord(s->ev0, st));
-    rc = launch_k3_any(L.cg, L.P, sep, mq, mql, mx, mxl, p, L.ncta, st);
-    if (rc) return rc;
+    for (int sg = 0; sg < nseg; ++sg) {
+        K3Params ps = p;
+        ps.nunits = seg_end[sg];
+        if (sg > 0) {
+            k4_merge_kernel<<<(unsigned)nq, K4_THREADS, sizeof(K4Smem), st>>>(p, L.cg, L.ncta, 1, 1, nullptr, nullptr);
+            k3_set_counter_kernel<<<1, 1, 0, st>>>(p.next_unit, (u64)seg_end[sg - 1]);
+            count_launch(2);
+            B2K_CUDA(cudaGetLastError());
+        }
+        rc = launch_k3_any(L.cg, L.P, sep, mq, mql, mx, mxl, ps, L.ncta, st);
+        if (rc) return rc;
+    }
     if (s->timing) { B2K_CUDA(cudaEventRecord(s->ev1, st)); s->timed = true; }
 
     if (!screen) {

@@ -8,6 +8,9 @@ namespace b2k {
 // max_norm_bits (nullable): float bits of the largest finite squared norm, updated with atomicMax.
 int launch_row_prep(const float* X, int64_t n, int d, float* norms, float* xlo, unsigned int* max_norm_bits,
                     cudaStream_t st);
+// bf16 (round-to-nearest) copies of rows [0,n) of X into xb, with the squared rounding-error norm per row
+// (err2, nullable) and its running maximum (max_err_bits, nullable, float bits).  Needs d % 8 == 0.
+int launch_row_bf16(const float* X, int64_t n, int d, void* xb, float* err2, unsigned int* max_err_bits, cudaStream_t st);
 int launch_synth(uint64_t seed, int64_t row0, int64_t nrows, int d, float* out, cudaStream_t st);
 
 // K2 (k2_scan.cu)

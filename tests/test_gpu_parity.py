@@ -295,10 +295,11 @@ def test_one_million_rows_nq1_k10(faiss):
 
 
 @pytest.mark.parametrize("mode,cg,sep,k", [(1, 1, 2, 10), (1, 1, 1, 10), (1, 2, 2, 100), (1, 2, 1, 100), (1, 2, 2, 700),
-                                           (1, 2, 1, 1024), (2, 1, 0, 10), (2, 1, 0, 700), (2, 2, 0, 100), (2, 2, 0, 1024)])
+                                           (1, 2, 1, 1024), (2, 1, 0, 10), (2, 1, 0, 700), (2, 2, 0, 100), (2, 2, 0, 1024),
+                                           (3, 1, 0, 10), (3, 1, 0, 100), (3, 1, 0, 700), (3, 1, 0, 1024)])
 def test_tensor_kernel_variants(faiss, mode, cg, sep, k):
     """Every instantiation of the tcgen05 kernel -- 3xTF32 (one CTA / CTA pair, shared / separate
-    cross-term accumulator, short / long lists) and TF32 screening + exact re-rank -- against the
+    cross-term accumulator, short / long lists) and TF32 / bf16 screening + exact re-rank -- against the
     oracle's expansion numerics, on N(0,1) rows and on unit-norm rows with planted duplicates (the
     rag.py distribution)."""
     rng = np.random.default_rng(cg * 10 + sep)
@@ -315,9 +316,9 @@ def test_tensor_kernel_variants(faiss, mode, cg, sep, k):
         idx.set_option("tensor_sep_accum", sep)
         D, I = idx.search(q, k)
         st = idx.stats()
-        assert st["path"] == "tensor" and st["tensor_mode"] == {1: "3xtf32", 2: "screen+rerank"}[mode]
+        assert st["path"] == "tensor" and st["tensor_mode"] == {1: "3xtf32", 2: "screen+rerank", 3: "bf16screen+rerank"}[mode]
         assert np.all(D >= 0.0)
-        if mode == 2 and unit:
+        if mode >= 2 and unit:
             assert np.all(D[:8, 0] == 0.0)                # exact re-rank: a stored query is at distance exactly 0
         assert_knn_matches(D, I, x, q, k, expanded=True, what="mode=%d cg=%d sep=%d k=%d unit=%s" % (mode, cg, sep, k, unit))
 
@@ -526,6 +527,53 @@ def test_tensor_path_small_and_ragged(faiss, n, d):
     assert_knn_matches(D, I, x, q, 10, Dr, Ir, expanded=True, what="n=%d d=%d" % (n, d))
 
 
+def test_bf16_screening_incremental_adds_and_fallbacks(faiss):
+    """bf16 screening keeps bf16 copies of the rows: rows added AFTER the first bf16 search (and
+    after a capacity growth) must be searchable, a reset must drop the copies, d % 8 != 0 is served
+    by the TF32 screening, and an overflowing slack zone still ends in the 3xTF32 rerun."""
+    x = O.synth(61, 0, 30000, 128)
+    q = O.synth(62, 0, 40, 128)
+    idx = faiss.IndexFlatL2(128)
+    idx.set_option("tensor_mode", 3)
+    idx.add(x[:5000])
+    D, I = idx.search(q, 20)
+    assert idx.stats()["tensor_mode"] == "bf16screen+rerank"
+    assert_knn_matches(D, I, x[:5000], q, 20, expanded=True, what="bf16 first")
+    idx.add(x[5000:])                                     # grows the row storage and the bf16 copies
+    x2 = x.copy()
+    D, I = idx.search(q, 20)
+    assert_knn_matches(D, I, x2, q, 20, expanded=True, what="bf16 after growth")
+    big = (x[:64] * 300.0).astype(np.float32)             # larger norms and rounding errors arrive later
+    idx.add(big)
+    D, I = idx.search(q, 20)
+    assert_knn_matches(D, I, np.concatenate([x2, big]), q, 20, expanded=True, what="bf16 after large rows")
+    idx.reset()
+    idx.add(x[:3000])
+    D, I = idx.search(q, 20)
+    assert idx.stats()["tensor_mode"] == "bf16screen+rerank"
+    assert_knn_matches(D, I, x[:3000], q, 20, expanded=True, what="bf16 after reset")
+
+    y = O.synth(63, 0, 4000, 36)                          # 36 % 8 != 0: no 16-byte bf16 pitch
+    idx = _build(faiss, y)
+    idx.set_option("tensor_mode", 3)
+    qy = O.synth(64, 0, 32, 36)
+    D, I = idx.search(qy, 5)
+    assert idx.stats()["tensor_mode"] == "screen+rerank"
+    assert_knn_matches(D, I, y, qy, 5, expanded=True, what="bf16 -> tf32 screening")
+
+    rng = np.random.default_rng(0)
+    base = rng.standard_normal((1, 64)).astype(np.float32)
+    z = np.repeat(base, 20000, 0) + rng.standard_normal((20000, 64)).astype(np.float32) * 1e-6
+    z[::1000] = rng.standard_normal((20, 64)).astype(np.float32)
+    qz = rng.standard_normal((30, 64)).astype(np.float32)
+    idx = _build(faiss, z)
+    idx.set_option("tensor_mode", 3)
+    D, I = idx.search(qz, 10)
+    st = idx.stats()
+    assert st["screen_fallbacks"] >= 1 and st["tensor_mode"] == "3xtf32"
+    assert_knn_matches(D, I, z, qz, 10, expanded=True, what="bf16 overflow fallback")
+
+
 def test_nonfinite_rows_and_queries_on_the_tensor_path(faiss):
     """inf / NaN rows are never selected and do not disturb their neighbours in the tile; a NaN
     query gets all padding (no distance is < FLT_MAX), the other queries are unaffected."""
@@ -535,7 +583,7 @@ def test_nonfinite_rows_and_queries_on_the_tensor_path(faiss):
     x[300] = np.inf
     q = O.synth(52, 0, 24, 64)
     q[7, 1] = np.nan
-    for mode in (2, 1):
+    for mode in (2, 1, 3):
         idx = _build(faiss, x)
         idx.set_option("tensor_mode", mode)
         D, I = idx.search(q, 8)
