@@ -133,11 +133,12 @@ B2K_API int b2k_search_rows_noalloc(int device, const float* x_dev, int64_t n, i
 
 /* Tuning / test hooks.  Keys: "path" (0 auto, 1 force the scan kernel, 2 force the
  * tensor-core kernel), "scan_ctas_per_sm", "timing" (0/1), "tensor_cta_group" (0 auto, 1, 2),
- * "tensor_sep_accum" (0 auto, 1 on, 2 off), "tensor_mode" (0 auto = 2, 1 = 3xTF32 products,
+ * "tensor_sep_accum" (0 auto, 1 on, 2 off), "tensor_mode" (0 auto = 3 where it applies, else 2; 1 = 3xTF32 products,
  * 2 = one TF32 product as a screen + exact fp32 re-rank of the rows inside its error slack,
  * 3 = the same screen on bf16 copies of the rows (kept next to the fp32 rows, +50% memory;
  * needs d % 8 == 0, else 2 serves)), "tensor_segments" (1 default: the main pass runs in
- * segments with the k-th-distance bound refreshed in between; 0: one launch).
+ * segments with the k-th-distance bound refreshed in between; 0: one launch),
+ * "tensor_epilogue_warps" (0 auto, 4, 8: warps filtering the accumulators in the screening modes).
  * Unknown key -> B2K_EINVAL. */
 B2K_API int b2k_set_option(b2k_index* h, const char* key, int64_t value);
 

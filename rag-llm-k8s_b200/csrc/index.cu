@@ -49,6 +49,7 @@ struct b2k_index {
     bool lo_enabled = false;
     void* xbf = nullptr;  // bf16 copies of the rows (bf16 screening mode), allocated on first use
     bool bf_enabled = false;
+    bool bf_nomem = false;  // the bf16 copies did not fit next to the rows: TF32 screening serves from then on
     cudaStream_t stream = nullptr;
     mutable std::mutex mu;
     void* ws = nullptr;
@@ -62,7 +63,8 @@ struct b2k_index {
     int opt_cta_group = 0;  // 0 = library default
     int opt_sep = 0;
     int opt_segments = 1;
-    int opt_tensor_mode = 0;  // 0 auto (TF32 screening + exact re-rank), 1 3xTF32, 2 TF32 screening, 3 bf16 screening
+    int opt_epi = 0;
+    int opt_tensor_mode = 0;  // 0 auto (bf16 screening + exact re-rank where d % 8 == 0 and memory allows, else TF32 screening), 1 3xTF32, 2 TF32 screening, 3 bf16 screening
     int64_t stat_screen_fallbacks = 0;
     int last_path = 0;
     int sticky = 0;
@@ -163,7 +165,13 @@ int grow(b2k_index* h, int64_t need_rows) {
     }
     if (e == cudaSuccess) e = cudaMalloc(&nn, (size_t)cap * sizeof(float));
     if (e == cudaSuccess && h->lo_enabled) e = cudaMalloc(&nl, (size_t)cap * row_bytes);
-    if (e == cudaSuccess && h->bf_enabled) e = cudaMalloc(&nb, (size_t)cap * row_bytes / 2);
+    if (e == cudaSuccess && h->bf_enabled && cudaMalloc(&nb, (size_t)cap * row_bytes / 2) != cudaSuccess) {
+        // no room for the bf16 copies next to the grown rows: drop them, TF32 screening needs none
+        cudaGetLastError();
+        nb = nullptr;
+        h->bf_enabled = false;
+        h->bf_nomem = true;
+    }
     if (e != cudaSuccess) {
         cudaGetLastError();
         cudaFree(nx); cudaFree(nn); cudaFree(nl); cudaFree(nb);
@@ -210,7 +218,7 @@ int enable_bf(b2k_index* h, cudaStream_t st) {
     if (h->bf_enabled) return B2K_OK;
     if (h->capacity > 0) {
         cudaError_t e = cudaMalloc(&h->xbf, (size_t)h->capacity * h->d * 2);
-        if (e != cudaSuccess) { cudaGetLastError(); set_error("cudaMalloc for bf16 rows failed: %s", cudaGetErrorString(e)); return B2K_ENOMEM; }
+        if (e != cudaSuccess) { cudaGetLastError(); h->bf_nomem = true; set_error("cudaMalloc for bf16 rows failed: %s", cudaGetErrorString(e)); return B2K_ENOMEM; }
     }
     h->bf_enabled = true;
     if (h->ntotal > 0) return launch_row_bf16(h->x, h->ntotal, h->d, h->xbf, nullptr, h->done + MAX_ERR_SLOT, st);
@@ -317,9 +325,13 @@ int b2k_set_option(b2k_index* h, const char* key, int64_t value) {
         if (value < 0 || value > 3) { set_error("option tensor_mode must be 0 (auto), 1 (3xTF32), 2 (TF32 screening + exact re-rank) or 3 (bf16 screening + exact re-rank)"); return B2K_EINVAL; }
         h->opt_tensor_mode = (int)value;
     } else if (!strcmp(key, "tensor_segments")) {
-        if (value < 0 || value > 1) { set_error("option tensor_segments must be 0 (one launch) or 1 (segments with bound refreshes)"); return B2K_EINVAL; }
+        if (value < 0 || value > 100000) { set_error("option tensor_segments must be 0 (one launch), 1 (segments with bound refreshes) or a target number of keys per query and segment"); return B2K_EINVAL; }
         h->opt_segments = (int)value;
         if (h->k3) k3_set_segments(h->k3, h->opt_segments);
+    } else if (!strcmp(key, "tensor_epilogue_warps")) {
+        if (value != 0 && value != 4 && value != 8) { set_error("option tensor_epilogue_warps must be 0 (auto), 4 or 8"); return B2K_EINVAL; }
+        h->opt_epi = (int)value / 4;
+        if (h->k3) k3_set_epi_halves(h->k3, h->opt_epi);
     } else if (!strcmp(key, "timing")) {
         h->opt_timing = value != 0;
         if (h->k3) k3_set_timing(h->k3, h->opt_timing != 0);
@@ -371,6 +383,7 @@ int b2k_reset(b2k_index* h) {
     cudaFree(h->x); cudaFree(h->norms); cudaFree(h->xlo); cudaFree(h->xbf);
     h->x = h->norms = h->xlo = nullptr;
     h->xbf = nullptr;
+    h->bf_nomem = false;
     h->ntotal = h->capacity = 0;
     if (h->k3) k3_invalidate_maps(h->k3);
     B2K_CUDA(cudaMemset(h->done, 0, 256));
@@ -489,8 +502,8 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
     } else if (want_tc) {
         // 1 = 3xTF32, 2 = TF32 screening, 3 = bf16 screening (rows need a 16-byte bf16 pitch; if the bf16
         // copies do not fit in memory the TF32 screening serves instead)
-        int mode = h->opt_tensor_mode == 0 ? 2 : h->opt_tensor_mode;
-        if (mode == 3 && h->d % 8 != 0) mode = 2;
+        int mode = h->opt_tensor_mode == 0 ? 3 : h->opt_tensor_mode;
+        if (mode == 3 && (h->d % 8 != 0 || h->bf_nomem)) mode = 2;
         if (mode == 3 && enable_bf(h, st) != B2K_OK) mode = 2;
         if (mode == 1) rc = enable_lo(h, st);
         if (!rc && !h->k3) {
@@ -499,6 +512,7 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
             if (!rc) k3_set_cta_group(h->k3, h->opt_cta_group);
             if (!rc) k3_set_sep_mode(h->k3, h->opt_sep);
             if (!rc) k3_set_segments(h->k3, h->opt_segments);
+            if (!rc) k3_set_epi_halves(h->k3, h->opt_epi);
         }
         if (!rc) h->last_path = 2;
         // like faiss (query blocks of 4096), long batches go through in chunks: the candidate-list

@@ -41,8 +41,10 @@ namespace b2k {
 static constexpr int K3_BM = 128;       // query rows per CTA = TMEM lanes
 static constexpr int K3_BN = 256;       // database rows per tile = TMEM columns per accumulator
 static constexpr int K3_BK = 32;        // fp32 per k-chunk: one 128-byte swizzle row
-static constexpr int K3_THREADS = 192;  // warp 0 TMA, warp 1 MMA, warps 2..5 epilogue
-static constexpr int K3_EPI_THREADS = 128;
+// threads per CTA: warp 0 TMA, warp 1 MMA, then NH groups of four epilogue warps (NH = 1: warps
+// 2..5 take all 256 columns of their 32 query rows; NH = 2: warps 2..5 take columns 0..127 and
+// warps 6..9 columns 128..255 of the same rows, two warps per scheduler to hide each other's latencies)
+static constexpr int k3_threads(int nh) { return 64 + 128 * nh; }
 static constexpr int K3_A_BYTES = K3_BM * K3_BK * 4;  // 16 KB
 
 struct K3Params {
@@ -85,7 +87,8 @@ struct K3Smem {
     static constexpr int NBAR = 2 * NS + 4 + 2 * K3_NSCHED;
     static constexpr int OFF_SCHED = OFF_BAR + NBAR * 8;       // long long[K3_NSCHED]
     static constexpr int OFF_TMEM = OFF_SCHED + K3_NSCHED * 8;
-    static constexpr int OFF_SCRATCH = (OFF_TMEM + 16 + 15) & ~15;  // 4 warps x P keys
+    static constexpr int OFF_CNT = (OFF_TMEM + 16 + 15) & ~15;      // int[128]: list lengths of the unit in flight (NH = 2)
+    static constexpr int OFF_SCRATCH = OFF_CNT + K3_BM * 4;         // 4 warps x P keys
     static size_t bytes(int P) { return (size_t)OFF_SCRATCH + (size_t)4 * P * 8; }
 };
 
@@ -94,11 +97,11 @@ struct K3Smem {
 template <int CG>
 __device__ __forceinline__ long long sched_take_warp(uint64_t* sfull, uint64_t* sempty, const long long* sched_u,
                                                      int ss, uint32_t sph, uint32_t rank, int lane) {
-    if (CG == 1) ptx::mbar_wait(&sfull[ss], sph);
-    else ptx::mbar_wait_cluster(&sfull[ss], sph);
+    ptx::mbar_wait(&sfull[ss], sph);  // the peer CTA's copy arrives by st.async on its own barrier: no cluster-scope acquire
     const long long u = *reinterpret_cast<const volatile long long*>(&sched_u[ss]);
     __syncwarp();
-    if (lane == 0) {
+    // (u >= -1 always holds: the test makes the relaxed arrive wait for the value just read)
+    if (lane == 0 && u >= -1) {
         if (CG == 1 || rank == 0) ptx::mbar_arrive(&sempty[ss]);
         else ptx::mbar_arrive_cluster(&sempty[ss], 0);
     }
@@ -134,10 +137,12 @@ __device__ __forceinline__ float reg_select32(const float (&v)[32], int c) {
 // the bound refreshed between segments of the pass a warp meets a survivor in about one chunk
 // out of ten; only then are the columns located (second, mask-building walk).
 // v = main accumulator, w = cross-term accumulator (SEP only).
-template <bool SEP>
+// SHCNT: the list length lives in shared memory (*cnt_s) and is bumped atomically, because two
+// threads (the two column halves of the row) append to the same list.
+template <bool SEP, bool SHCNT>
 __device__ __forceinline__ void k3_filter_chunk(const uint32_t (&v)[32], const uint32_t (&w)[32], const float* xn,
                                                 float t_cmp, float qn, float tau_eff, u64 kth, uint32_t row0,
-                                                u64* list, int& cnt) {
+                                                u64* list, int& cnt, int* cnt_s) {
     bool any[4] = {false, false, false, false};
 #pragma unroll
     for (int c = 0; c < 32; c += 4) {
@@ -173,7 +178,10 @@ __device__ __forceinline__ void k3_filter_chunk(const uint32_t (&v)[32], const u
             dist = dist < 0.f ? 0.f : dist;
             if (dist <= tau_eff) {
                 const u64 key = make_key(dist, row0 + c);
-                if (key < kth) { list[cnt] = key; ++cnt; }
+                if (key < kth) {
+                    if constexpr (SHCNT) { list[atomicAdd(cnt_s, 1)] = key; }
+                    else { list[cnt] = key; ++cnt; }
+                }
             }
         }
     }
@@ -187,8 +195,8 @@ __device__ __forceinline__ void k3_filter_chunk(const uint32_t (&v)[32], const u
 // double buffering (the MMAs of the next tile wait for the epilogue), so it is used for long
 // rows (d >= 512) where the relative cost is a few percent and the error would otherwise
 // exceed 1e-5 of ||q||^2 + ||x||^2 on near-duplicate unit-norm vectors.
-template <int CG, int NS, int MODE>
-__global__ void __launch_bounds__(K3_THREADS, 1)
+template <int CG, int NS, int MODE, int NH>
+__global__ void __launch_bounds__(k3_threads(NH), 1)
 k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_ql,
                       const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_xl,
                       const K3Params p) {
@@ -214,6 +222,7 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
     long long* sched_u = reinterpret_cast<long long*>(smem + L::OFF_SCHED);
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + L::OFF_TMEM);
     u64* scratch = reinterpret_cast<u64*>(smem + L::OFF_SCRATCH);
+    int* cnt_s = reinterpret_cast<int*>(smem + L::OFF_CNT);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t rank = (CG == 2) ? ptx::cluster_ctarank() : 0u;
@@ -222,8 +231,8 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tmap(&tm_q); ptx::prefetch_tmap(&tm_ql); ptx::prefetch_tmap(&tm_x); ptx::prefetch_tmap(&tm_xl);
         for (int s = 0; s < NS; ++s) { ptx::mbar_init(&full[s], CG); ptx::mbar_init(&empty[s], 1); }
-        for (int s = 0; s < 2; ++s) { ptx::mbar_init(&tfull[s], 1); ptx::mbar_init(&tempty[s], 4 * CG); }
-        for (int s = 0; s < K3_NSCHED; ++s) { ptx::mbar_init(&sfull[s], 1); ptx::mbar_init(&sempty[s], 5 * CG); }
+        for (int s = 0; s < 2; ++s) { ptx::mbar_init(&tfull[s], 1); ptx::mbar_init(&tempty[s], 4 * NH * CG); }
+        for (int s = 0; s < K3_NSCHED; ++s) { ptx::mbar_init(&sfull[s], 1); ptx::mbar_init(&sempty[s], (1 + 4 * NH) * CG); }
         ptx::fence_barrier_init();
     }
     if (warp == 1) {
@@ -269,13 +278,12 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
                         u = ((long long)tt << 8) | (long long)((uint32_t)u - tt * (uint32_t)p.nqb);
                     }
                     sched_u[ss] = u;
-                    if (CG == 2) ptx::st_cluster_b64(&sched_u[ss], 1, (uint64_t)u);
                     ptx::mbar_arrive(&sfull[ss]);
-                    if (CG == 2) ptx::mbar_arrive_cluster(&sfull[ss], 1);
+                    if (CG == 2) ptx::st_async_b64_cluster(&sched_u[ss], &sfull[ss], 1, (uint64_t)u);
                 } else {
-                    ptx::mbar_wait_cluster(&sfull[ss], sph);
+                    ptx::mbar_wait(&sfull[ss], sph);
                     u = *reinterpret_cast<const volatile long long*>(&sched_u[ss]);
-                    ptx::mbar_arrive_cluster(&sempty[ss], 0);
+                    if (u >= -1) ptx::mbar_arrive_cluster(&sempty[ss], 0);
                 }
                 if (++ss == K3_NSCHED) { ss = 0; sph ^= 1; }
                 if (u < 0) break;
@@ -353,9 +361,12 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
     } else {
         // ===================== epilogue: fused top-k selection =====================
         const int e = warp & 3;                 // TMEM lane quarter this warp may access
+        const int h = (warp - 2) >> 2;          // column half this warp filters (always 0 when NH = 1)
         const int row = e * 32 + lane;          // query row inside the CTA's 128
         const int epi_tid = (warp - 2) * 32 + lane;
-        u64* scr = scratch + (size_t)(warp - 2) * p.P;
+        constexpr int EPI_THREADS = 128 * NH;
+        constexpr int HCOLS = K3_BN / NH;       // columns per thread and unit
+        u64* scr = scratch + (size_t)e * p.P;   // compaction scratch (half 0 only)
         int as = 0, ss = 0, xb = 0;
         uint32_t aphase = 0, sph = 0;
         const float INF = __int_as_float(0x7f800000);
@@ -364,6 +375,9 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
         // other half of xn_s with cp.async while this tile is filtered, and the list state of the
         // next query block is loaded early (or simply kept in registers when the block repeats).
         // Without this the epilogue paid two global-memory round trips (~1.9k cycles) per unit.
+        // With NH = 2 the thread of column half 0 owns the list state (length, bound, write-back,
+        // compaction); the thread of half 1 only appends (through the shared length) and prunes with
+        // the bound it last loaded -- possibly a unit or two old, which keeps a few more keys, never fewer.
         struct QState { int cnt; float tau; u64 kth; float qn, slack; unsigned int gts; };
         auto take = [&]() -> long long {
             const long long u = sched_take_warp<CG>(sfull, sempty, sched_u, ss, sph, rank, lane);
@@ -371,11 +385,11 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
             return u;
         };
         auto next_is_ready = [&]() -> bool {
-            return CG == 1 ? ptx::mbar_try_wait(&sfull[ss], sph) : ptx::mbar_try_wait_cluster(&sfull[ss], sph);
+            return ptx::mbar_try_wait(&sfull[ss], sph);
         };
         auto issue_norms = [&](long long u, float* dst) {
             const int64_t t = u >> 8;
-            for (int j = epi_tid; j < K3_BN; j += K3_EPI_THREADS) {
+            for (int j = epi_tid; j < K3_BN; j += EPI_THREADS) {
                 const int64_t r = t * K3_BN + j;
                 if (r < p.n && j < p.tile_cols) ptx::cp_async_4(dst + j, p.norms + r);
                 else dst[j] = INF;
@@ -386,9 +400,9 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
         auto load_state = [&](int qb, QState& S) {
             const int64_t sidx = sidx_of(qb), qi = qi_of(qb);
             const bool valid = qi < p.nq;
-            S.cnt = p.cnt[sidx];
-            S.tau = p.tau[sidx];
-            S.kth = p.kth[sidx];
+            S.cnt = __ldcg(p.cnt + sidx);
+            S.tau = __ldcg(p.tau + sidx);
+            S.kth = __ldcg(p.kth + sidx);
             S.qn = valid ? p.qn[qi] : 0.f;
             S.slack = (SCREEN && valid) ? p.slack2[qi] : 0.f;
             S.gts = valid ? __ldcg(p.gts + qi) : 0u;
@@ -418,8 +432,10 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
             // candidate the exact test below would accept
             const float t_cmp = valid ? (tau_eff - qn) + 2e-6f * (fabsf(tau_eff) + qn) : -INF;
             float* xn = xn_s + xb * K3_BN;
+            if (NH > 1 && h == 0) cnt_s[row] = cnt;
             ptx::cp_async_wait_all();
-            asm volatile("bar.sync 1, 128;" ::: "memory");  // this tile's norms are in place for all four warps
+            // this tile's norms (and list lengths) are in place for all epilogue warps
+            asm volatile("bar.sync 1, %0;" ::"n"(EPI_THREADS) : "memory");
 
             // look one unit ahead if the scheduler has already published it
             long long nxt = -2;
@@ -429,37 +445,37 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
                 nxt = take();
                 if (nxt >= 0) {
                     issue_norms(nxt, xn_s + (xb ^ 1) * K3_BN);
-                    if ((int)(nxt & 255) != qb) { load_state((int)(nxt & 255), N); n_loaded = true; }
+                    if ((int)(nxt & 255) != qb || h != 0) { load_state((int)(nxt & 255), N); n_loaded = true; }
                 }
             }
 
             ptx::mbar_wait(&tfull[as], aphase);
             ptx::tc_fence_after();
-            const uint32_t taddr = tmem_base + ((uint32_t)(e * 32) << 16) + (uint32_t)(as * K3_BN);
+            const uint32_t taddr = tmem_base + ((uint32_t)(e * 32) << 16) + (uint32_t)(as * K3_BN + h * HCOLS);
             u64* list = p.cand + sidx * p.P;
+            const float* xnh = xn + h * HCOLS;
             // Two register buffers: the tcgen05.ld of the next 32 columns is in flight while this
-            // chunk is filtered.  Filtering is branch-free (one FFMA + one compare per element folded
-            // into a bit mask); the rare survivors are handled after the chunk.
+            // chunk is filtered.
             uint32_t va[32], vb[32], wa[32], wb[32];
             ptx::tmem_ld_32x32(taddr, va);
             if (SEP) ptx::tmem_ld_32x32(taddr + K3_BN, wa);
-            const uint32_t row_base = (uint32_t)(t * K3_BN);
+            const uint32_t row_base = (uint32_t)(t * K3_BN) + (uint32_t)(h * HCOLS);
 #pragma unroll 1
-            for (int c0 = 0; c0 < K3_BN; c0 += 64) {
+            for (int c0 = 0; c0 < HCOLS; c0 += 64) {
                 ptx::tmem_ld_wait();
                 ptx::tmem_ld_32x32(taddr + c0 + 32, vb);
                 if (SEP) ptx::tmem_ld_32x32(taddr + K3_BN + c0 + 32, wb);
                 reg_fence32(va);
                 if (SEP) reg_fence32(wa);
-                k3_filter_chunk<SEP>(va, wa, xn + c0, t_cmp, qn, tau_eff, kth_eff, row_base + c0, list, cnt);
+                k3_filter_chunk<SEP, (NH > 1)>(va, wa, xnh + c0, t_cmp, qn, tau_eff, kth_eff, row_base + c0, list, cnt, cnt_s + row);
                 ptx::tmem_ld_wait();
-                if (c0 + 64 < K3_BN) {
+                if (c0 + 64 < HCOLS) {
                     ptx::tmem_ld_32x32(taddr + c0 + 64, va);
                     if (SEP) ptx::tmem_ld_32x32(taddr + K3_BN + c0 + 64, wa);
                 }
                 reg_fence32(vb);
                 if (SEP) reg_fence32(wb);
-                k3_filter_chunk<SEP>(vb, wb, xn + c0 + 32, t_cmp, qn, tau_eff, kth_eff, row_base + c0 + 32, list, cnt);
+                k3_filter_chunk<SEP, (NH > 1)>(vb, wb, xnh + c0 + 32, t_cmp, qn, tau_eff, kth_eff, row_base + c0 + 32, list, cnt, cnt_s + row);
             }
             // accumulator drained: hand it back to the MMA warp (of the leader CTA)
             ptx::tc_fence_before();
@@ -468,9 +484,17 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
                 if (CG == 1 || rank == 0) ptx::mbar_arrive(&tempty[as]);
                 else ptx::mbar_arrive_cluster(&tempty[as], 0);
             }
+            if (NH > 1) {
+                // both column halves of this lane quarter have finished appending (their keys are
+                // visible to each other: bar.sync orders the participants' memory accesses)
+                asm volatile("bar.sync %0, 64;" ::"r"(2 + e) : "memory");
+                if (h == 0) cnt = cnt_s[row];
+            }
 
-            // compaction of lists that could overflow on the next tile (warp-cooperative)
-            unsigned need = __ballot_sync(0xffffffffu, valid && cnt > p.P - K3_BN);
+            // compaction of lists that could overflow on the next tile (warp-cooperative, half 0).
+            // Half 1 cannot touch these lists meanwhile: its next append comes after the next bar.sync 1,
+            // where half 0 only arrives once it is done here.
+            unsigned need = h == 0 ? __ballot_sync(0xffffffffu, valid && cnt > p.P - K3_BN) : 0u;
             while (need) {
                 const int Lq = __ffs(need) - 1;
                 need &= need - 1;
@@ -515,10 +539,17 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
                 if (nxt >= 0) issue_norms(nxt, xn_s + (xb ^ 1) * K3_BN);
             }
             const int nqb_next = nxt >= 0 ? (int)(nxt & 255) : -1;
-            if (nqb_next == qb) {
+            if (h != 0) {
+                // appending half: no state to write back; the next unit's bounds were (or are now) loaded
+                if (nxt >= 0) {
+                    if (n_loaded) S = N;
+                    else load_state(nqb_next, S);
+                }
+            } else if (nqb_next == qb) {
                 // same query block again: the list state stays in registers, only the shared bound is refreshed
                 S.cnt = cnt; S.tau = tau; S.kth = kth;
                 S.gts = valid ? __ldcg(p.gts + qi) : 0u;
+                if (NH > 1) { p.tau[sidx] = tau; p.kth[sidx] = kth; }  // for the other half's next look
             } else {
                 p.cnt[sidx] = cnt;
                 p.tau[sidx] = tau;
@@ -832,15 +863,23 @@ struct K3State {
     int last_mode = 0;  // 1 = 3xTF32, 2 = TF32 screening + re-rank, 3 = bf16 screening + re-rank (what the last search ran)
     int sep_mode = 0;  // long-row accuracy: 0 auto (d >= 512: separate accumulator), 1 separate accumulator, 2 off
     bool timed = false;
+    int epi_halves = 0;  // 0 auto (2 where available), 1 four epilogue warps, 2 eight
     int segments = 1;  // cut the main pass into segments with a bound refresh in between (0 = one launch)
 };
 
 static int k3_P(int k) { return next_pow2(k + K3_BN); }
 // CG = 1 has shared memory for compaction scratch up to 512 keys per warp; CG = 2 up to 2048.
-// Auto: CTA pairs for long rows (measured faster at d = 1024: 815 vs 782 TFLOP/s) and for long lists.
-static int k3_cg_for(int k, int want, int d, bool screen) {
+// 3xTF32: CTA pairs for long rows (measured faster at d = 1024: 815 vs 782 TFLOP/s) and for long
+// lists.  Screening: the kernel is bound by the operand stream from L2 (~15 TB/s chip-wide at
+// either precision), of which a pair needs a third less (each CTA loads half of the database
+// tile), so pairs win once there is enough work to fill them: 6.15 vs 6.67 ms at C3 (bf16),
+// 1.69 vs 2.21 ms at k = 1000, but 48 vs 35 us on 200k rows x 64 queries.
+static int k3_cg_for(int k, int want, int d, bool screen, int64_t n, int64_t nq, int sm_count) {
     if (want == 1 || want == 2) return (want == 1 && !screen && k3_P(k) > 512) ? 2 : want;
-    if (screen) return 1;  // measured: 8.9 vs 15.9 ms at d = 1024, 13.2 vs 20.8 ms at d = 384 (pairs)
+    if (screen) {
+        const int64_t units2 = ((n + K3_BN - 1) / K3_BN) * ((nq + 2 * K3_BM - 1) / (2 * K3_BM));
+        return units2 >= 64LL * (sm_count / 2) ? 2 : 1;
+    }
     if (k3_P(k) > 512) return 2;
     return d >= 512 ? 2 : 1;
 }
@@ -857,9 +896,9 @@ struct K3Layout {
     size_t off_qlo, off_qn, off_gts, off_slack, off_next, off_cnt, off_tau, off_kth, off_cand, total;
 };
 
-static K3Layout k3_layout(int sm_count, int d, int64_t nq, int k, int want_cg, bool screen) {
+static K3Layout k3_layout(int sm_count, int d, int64_t nq, int k, int want_cg, bool screen, int64_t n) {
     K3Layout L;
-    L.cg = k3_cg_for(k, want_cg, d, screen);
+    L.cg = k3_cg_for(k, want_cg, d, screen, n, nq, sm_count);
     L.ncta = (sm_count / L.cg) * L.cg;
     L.nqb = (int)((nq + K3_BM * L.cg - 1) / (K3_BM * L.cg));
     L.qpc = L.nqb * K3_BM;
@@ -882,7 +921,7 @@ static K3Layout k3_layout(int sm_count, int d, int64_t nq, int k, int want_cg, b
 
 size_t k3_scratch_bytes(int sm_count, int d, int64_t nq, int k) {
     // sized for either CTA-group configuration
-    size_t a = k3_layout(sm_count, d, nq, k, 1, true).total, b = k3_layout(sm_count, d, nq, k, 2, false).total;
+    size_t a = k3_layout(sm_count, d, nq, k, 1, true, 0).total, b = k3_layout(sm_count, d, nq, k, 2, false, 0).total;
     return a > b ? a : b;
 }
 
@@ -925,6 +964,7 @@ void k3_set_timing(K3State* s, bool on) { s->timing = on; }
 void k3_set_cta_group(K3State* s, int cg) { s->cg = (cg == 1 || cg == 2) ? cg : 0; }
 void k3_set_sep_mode(K3State* s, int m) { s->sep_mode = m; }
 void k3_set_segments(K3State* s, int on) { s->segments = on; }
+void k3_set_epi_halves(K3State* s, int nh) { s->epi_halves = nh; }
 int k3_last_mode(const K3State* s) { return s->last_mode; }
 
 int k3_last_kernel_ms(K3State* s, float* ms) {
@@ -949,14 +989,14 @@ static int make_map(K3State* s, CUtensorMap* m, const void* base, int64_t rows, 
     return B2K_OK;
 }
 
-template <int CG, int NS, int MODE>
+template <int CG, int NS, int MODE, int NH>
 static int launch_k3(const CUtensorMap& mq, const CUtensorMap& mql, const CUtensorMap& mx, const CUtensorMap& mxl,
                      const K3Params& p, int ncta, cudaStream_t st) {
     size_t smem = K3Smem<CG, NS, MODE>::bytes(p.P);
-    B2K_CUDA(cudaFuncSetAttribute(k3_tf32x3_topk_kernel<CG, NS, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    B2K_CUDA(cudaFuncSetAttribute(k3_tf32x3_topk_kernel<CG, NS, MODE, NH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(ncta);
-    cfg.blockDim = dim3(K3_THREADS);
+    cfg.blockDim = dim3(k3_threads(NH));
     cfg.dynamicSmemBytes = smem;
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
@@ -966,35 +1006,40 @@ static int launch_k3(const CUtensorMap& mq, const CUtensorMap& mql, const CUtens
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    B2K_CUDA(cudaLaunchKernelEx(&cfg, k3_tf32x3_topk_kernel<CG, NS, MODE>, mq, mql, mx, mxl, p));
+    B2K_CUDA(cudaLaunchKernelEx(&cfg, k3_tf32x3_topk_kernel<CG, NS, MODE, NH>, mq, mql, mx, mxl, p));
     count_launch();
     return B2K_OK;
 }
 
-static int launch_k3_any(int cg, int P, int mode, const CUtensorMap& mq, const CUtensorMap& mql, const CUtensorMap& mx,
+// nh: 1 = four epilogue warps, 2 = eight (two per scheduler; screening modes with one CTA per tile)
+static int launch_k3_any(int cg, int P, int mode, int nh, const CUtensorMap& mq, const CUtensorMap& mql, const CUtensorMap& mx,
                          const CUtensorMap& mxl, const K3Params& p, int ncta, cudaStream_t st) {
 #define B2K_K3_CASE(MODE_)                                                                        \
     case MODE_:                                                                                   \
-        if (cg == 1) return launch_k3<1, 2, MODE_>(mq, mql, mx, mxl, p, ncta, st);                \
-        if (P <= 512) return launch_k3<2, 3, MODE_>(mq, mql, mx, mxl, p, ncta, st);               \
-        return launch_k3<2, 2, MODE_>(mq, mql, mx, mxl, p, ncta, st);
+        if (cg == 1) return launch_k3<1, 2, MODE_, 1>(mq, mql, mx, mxl, p, ncta, st);             \
+        if (P <= 512) return launch_k3<2, 3, MODE_, 1>(mq, mql, mx, mxl, p, ncta, st);            \
+        return launch_k3<2, 2, MODE_, 1>(mq, mql, mx, mxl, p, ncta, st);
     switch (mode) {
         B2K_K3_CASE(0)
         B2K_K3_CASE(1)
     }
 #undef B2K_K3_CASE
-    if (mode == 3) {  // bf16 screening (one CTA per tile)
-        if (P <= 512) return launch_k3<1, 4, 3>(mq, mql, mx, mxl, p, ncta, st);
-        return launch_k3<1, 2, 3>(mq, mql, mx, mxl, p, ncta, st);
+    // screening (2 = TF32, 3 = bf16): one operand pair per stage (32 KB per CTA, or 48 KB without a
+    // partner), so the rings are deeper; the 2048-key compaction scratch of long lists needs the room
+#define B2K_K3_SCREEN(MODE_, NH_)                                                                  \
+    if (mode == MODE_ && nh == NH_) {                                                              \
+        if (cg == 1) {                                                                             \
+            if (P <= 512) return launch_k3<1, 4, MODE_, NH_>(mq, mql, mx, mxl, p, ncta, st);       \
+            return launch_k3<1, 2, MODE_, NH_>(mq, mql, mx, mxl, p, ncta, st);                     \
+        }                                                                                          \
+        if (P <= 512) return launch_k3<2, 6, MODE_, NH_>(mq, mql, mx, mxl, p, ncta, st);           \
+        return launch_k3<2, 4, MODE_, NH_>(mq, mql, mx, mxl, p, ncta, st);                         \
     }
-    if (mode == 2) {  // screening: one operand pair per stage (48 KB / 32 KB), deeper rings
-        if (cg == 1) {
-            if (P <= 512) return launch_k3<1, 4, 2>(mq, mql, mx, mxl, p, ncta, st);
-            return launch_k3<1, 2, 2>(mq, mql, mx, mxl, p, ncta, st);  // 2048-key compaction scratch needs the room
-        }
-        if (P <= 512) return launch_k3<2, 6, 2>(mq, mql, mx, mxl, p, ncta, st);
-        return launch_k3<2, 4, 2>(mq, mql, mx, mxl, p, ncta, st);
-    }
+    B2K_K3_SCREEN(2, 1)
+    B2K_K3_SCREEN(2, 2)
+    B2K_K3_SCREEN(3, 1)
+    B2K_K3_SCREEN(3, 2)
+#undef B2K_K3_SCREEN
     set_error("tensor kernel: bad accumulator mode %d", mode);
     return B2K_EINVAL;
 }
@@ -1008,7 +1053,7 @@ int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, con
     if (bf16 && (d % 8 != 0 || !xbf || !max_err_bits)) { set_error("tensor kernel: bf16 screening needs d %% 8 == 0 and the bf16 rows"); return B2K_EINVAL; }
     if (overflowed) *overflowed = 0;
     s->last_mode = mode;
-    K3Layout L = k3_layout(s->sm_count, d, nq, k, s->cg, screen);
+    K3Layout L = k3_layout(s->sm_count, d, nq, k, s->cg, screen, n);
     float* qlo = reinterpret_cast<float*>(scratch + L.off_qlo);  // 3xTF32: residual rows; bf16 screening: bf16 queries
     K3Params p;
     p.n = n; p.d = d; p.nq = nq; p.k = k; p.P = L.P; p.nqb = L.nqb; p.qpc = L.qpc;
@@ -1067,16 +1112,14 @@ int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, con
         if ((rc = make_map(s, &mxl, screen ? x : xlo, n, d, K3_BN / L.cg))) return rc;
     }
 
-    // Warm start.  Round A: the first 64 rows of one tile per CTA (pair) with open thresholds --
-    // every key is kept, so the pass is kept small; per query the k-th smallest distance of that
-    // sample becomes the shared threshold (an upper bound of the final k-th distance).  Round B:
-    // a few whole tiles per CTA under that threshold (few survivors), and the threshold is
-    // tightened again.  The full pass then prunes from its first tile: its lists stay far below
-    // capacity (no compaction sorts) and K4 has a few k keys per query to merge.
+    // Warm start: the first 64 rows of one tile per CTA (pair) with open thresholds -- every key is
+    // kept, so the pass is kept small; per query the k-th smallest distance of that sample becomes
+    // the shared threshold (an upper bound of the final k-th distance).
     const int nclusters = L.ncta / L.cg;
     // kernel mode: 0 3xTF32 in one accumulator (double-buffered), 1 3xTF32 with a separate cross-term
-    // accumulator, 2 screening (one product; exact distances from the re-rank kernel)
+    // accumulator, 2 TF32 screening, 3 bf16 screening (one product; exact distances from the re-rank kernel)
     const int sep = bf16 ? 3 : screen ? 2 : (s->sep_mode == 1 || (s->sep_mode == 0 && d >= 512)) ? 1 : 0;
+    const int nh = s->epi_halves == 1 ? 1 : 2;  // eight epilogue warps where instantiated (screening modes)
     const int cols_a = 64;
     int64_t warm_rows = 0;  // rows behind the bound the main pass starts with
     if (ntiles >= 2 * (int64_t)nclusters && (int64_t)nclusters * cols_a >= 2 * (int64_t)k) {
@@ -1085,61 +1128,39 @@ int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, con
         pre.static_tpc = 1;
         pre.static_tile0 = 0;
         pre.tile_cols = cols_a;
-        // every key of this pass is kept, so it is made as small as a usable bound allows: each CTA
-        // (pair) only serves every G-th query block, leaving nclusters / G lists of 64 keys per query
+        // each CTA (pair) only serves every G-th query block, leaving nclusters / G lists of 64 keys per query
         int G = (int)(((int64_t)nclusters * cols_a) / (12 * (int64_t)k));
         G = G < 1 ? 1 : (G > L.nqb ? L.nqb : G);
         pre.static_qb_mod = G;
         pre.nunits = (int64_t)nclusters * L.nqb;
         pre.n = (int64_t)nclusters * K3_BN;
-        rc = launch_k3_any(L.cg, L.P, sep, mq, mql, mx, mxl, pre, L.ncta, st);
+        rc = launch_k3_any(L.cg, L.P, sep, nh, mq, mql, mx, mxl, pre, L.ncta, st);
         if (rc) return rc;
         k4_merge_kernel<<<(unsigned)nq, K4_THREADS, sizeof(K4Smem), st>>>(pre, L.cg, L.ncta, 1, 1, nullptr, nullptr);
         k3_init_kernel<<<(unsigned)((nslots + 255) / 256), 256, 0, st>>>(nslots, p.cnt, p.tau, p.kth, nq, nullptr, p.next_unit, nullptr);
         count_launch(2);
         B2K_CUDA(cudaGetLastError());
         warm_rows = (int64_t)nclusters * cols_a / G;
-        // rows the second round should cover so that the full pass leaves ~<= 64 keys per list
-        const double want_rows = (double)n * k / ((double)nclusters * 64.0);
-        int tpc = (int)(want_rows / ((double)nclusters * K3_BN) + 0.999);
-        if (tpc < 1) tpc = 1;
-        if (tpc > 16) tpc = 16;
-        if (ntiles >= (int64_t)(tpc + 1) * nclusters * 2) {
-            pre.static_tpc = tpc;
-            pre.static_qb_mod = 1;
-            pre.static_tile0 = nclusters;
-            pre.tile_cols = K3_BN;
-            pre.n = (int64_t)nclusters * (tpc + 1) * K3_BN;
-            pre.nunits = (int64_t)nclusters * (tpc + 1) * L.nqb;
-            rc = launch_k3_any(L.cg, L.P, sep, mq, mql, mx, mxl, pre, L.ncta, st);
-            if (rc) return rc;
-            k4_merge_kernel<<<(unsigned)nq, K4_THREADS, sizeof(K4Smem), st>>>(pre, L.cg, L.ncta, 1, 1, nullptr, nullptr);
-            k3_init_kernel<<<(unsigned)((nslots + 255) / 256), 256, 0, st>>>(nslots, p.cnt, p.tau, p.kth, nq, nullptr, p.next_unit, nullptr);
-            count_launch(2);
-            B2K_CUDA(cudaGetLastError());
-            warm_rows = (int64_t)nclusters * tpc * K3_BN;
-        }
     }
 
-    // Main pass, in segments.  The warm start bounds the k-th distance by the k-th of a sample of
-    // `warm_rows` rows, under which about k * n / warm_rows rows of the whole database fall (~9.5k per
-    // query whatever k is) -- and inside one launch the bound barely moves, because a list only
-    // learns a better one when it compacts.  So the pass is cut where the scanned fraction has grown
-    // by a factor r, and between two segments K4 (threshold mode, ~50 us) turns everything kept so far
-    // into the exact k-th distance of the rows scanned so far.  Each segment then keeps about
-    // k * (r - 1) keys per query instead of thousands, which is what the epilogue's survivor path
-    // and the final merge pay for.
+    // Main pass, in segments.  A bound that is the k-th distance of a sample of m rows lets about
+    // k * n / m rows of the whole database through -- and inside one launch the bound barely moves,
+    // because a list only learns a better one when it compacts.  So the pass is cut where the
+    // scanned fraction has grown by a factor r, and between two segments K4 (threshold mode, ~50 us)
+    // turns everything kept so far into the exact k-th distance of the rows scanned so far.  Each
+    // segment then lets about k * (r - 1) keys per query through; r is chosen for max(400, 2k) keys
+    // (measured best among 200..3000 on four shapes; without any refresh C3 takes 55 ms instead of 6.7).  The kept
+    // keys stay in the lists across segments; the rows of every segment are scanned exactly once.
     long long seg_end[8];
     int nseg = 0;
     if (warm_rows > 0 && s->segments) {
-        const double r = 1.0 + (double)(3 * k > 400 ? 3 * k : 400) / (double)k;
-        const long long upc = p.nunits / nclusters;
-        int maxb = (int)(upc / 128);
-        if (maxb > 6) maxb = 6;
+        const double target = s->segments > 1 ? (double)s->segments : 400.0;
+        const double r = 1.0 + (target > 2.0 * k ? target : 2.0 * k) / (double)k;
+        const long long min_step = 4LL * nclusters;  // units
         double g = (double)warm_rows / (double)n * r;
-        while (g < 0.6 && nseg < maxb) {
-            const long long tiles = (long long)(g * (double)ntiles);
-            if (tiles > 0 && (nseg == 0 || tiles * L.nqb > seg_end[nseg - 1])) seg_end[nseg++] = tiles * L.nqb;
+        while (g < 0.6 && nseg < 6) {
+            const long long end = (long long)(g * (double)ntiles) * L.nqb;
+            if (end >= (nseg ? seg_end[nseg - 1] : 0) + min_step && end + min_step <= p.nunits) seg_end[nseg++] = end;
             g *= r;
         }
     }
@@ -1154,7 +1175,7 @@ int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, con
             count_launch(2);
             B2K_CUDA(cudaGetLastError());
         }
-        rc = launch_k3_any(L.cg, L.P, sep, mq, mql, mx, mxl, ps, L.ncta, st);
+        rc = launch_k3_any(L.cg, L.P, sep, nh, mq, mql, mx, mxl, ps, L.ncta, st);
         if (rc) return rc;
     }
     if (s->timing) { B2K_CUDA(cudaEventRecord(s->ev1, st)); s->timed = true; }

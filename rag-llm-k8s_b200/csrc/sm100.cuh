@@ -45,13 +45,30 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t by
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
-// arrive on the barrier at the same smem offset in CTA `cta` of the cluster
+// Arrive on the barrier at the same smem offset in CTA `cta` of the cluster.  Relaxed: the
+// arrivals made this way only count (a slot is free, an accumulator is drained); no data is
+// published through them.  (The release.cluster form costs a memory barrier per arrive, and
+// its partner, an acquire.cluster wait, invalidates the whole L1 -- CCTL.IVALL -- every time:
+// 30% of all stall samples of the CTA-pair kernel when the unit ring was built on them.)
 __device__ __forceinline__ void mbar_arrive_cluster(uint64_t* bar, uint32_t cta) {
     asm volatile(
         "{\n\t.reg .b32 ra;\n\t"
         "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
-        "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t}"
+        "mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [ra];\n\t}"
         ::"r"(smem_u32(bar)), "r"(cta) : "memory");
+}
+// Publish a 64-bit value into CTA `cta` of the cluster: the value goes to the same smem offset as
+// `local`, and completes (complete_tx, 8 bytes) on the barrier at the same offset as `bar` there,
+// on which this thread also makes the one expected arrival.  The receiver waits on its own
+// barrier with the ordinary CTA-scope wait, as for a TMA load.
+__device__ __forceinline__ void st_async_b64_cluster(void* local, uint64_t* bar, uint32_t cta, uint64_t v) {
+    asm volatile(
+        "{\n\t.reg .b32 ra, rb;\n\t"
+        "mapa.shared::cluster.u32 ra, %0, %2;\n\t"
+        "mapa.shared::cluster.u32 rb, %1, %2;\n\t"
+        "mbarrier.arrive.expect_tx.relaxed.cluster.shared::cluster.b64 _, [rb], 8;\n\t"
+        "st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b64 [ra], %3, [rb];\n\t}"
+        ::"r"(smem_u32(local)), "r"(smem_u32(bar)), "r"(cta), "l"(v) : "memory");
 }
 __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
     uint32_t ok;
@@ -65,40 +82,11 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     while (!mbar_try_wait(bar, parity)) {}
 }
-__device__ __forceinline__ bool mbar_try_wait_cluster(uint64_t* bar, uint32_t parity) {
-    uint32_t ok;
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
-    return ok != 0;
-}
 // 4-byte asynchronous copy global -> shared (LDGSTS); completion with cp_async_wait_all
 __device__ __forceinline__ void cp_async_4(void* smem_dst, const void* gmem_src) {
     asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(smem_dst)), "l"(gmem_src) : "memory");
 }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
-// wait with cluster-scope acquire: pairs with a remote (other CTA) release-arrive
-__device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity) {
-    uint32_t ok;
-    do {
-        asm volatile(
-            "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
-            "selp.u32 %0, 1, 0, p;\n\t}"
-            : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
-    } while (!ok);
-}
-// 64-bit store into the same smem offset of CTA `cta` of the cluster
-__device__ __forceinline__ void st_cluster_b64(void* local, uint32_t cta, uint64_t v) {
-    asm volatile(
-        "{\n\t.reg .b32 ra;\n\t"
-        "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
-        "st.shared::cluster.b64 [ra], %2;\n\t}"
-        ::"r"(smem_u32(local)), "r"(cta), "l"(v) : "memory");
-}
-
 // ---- TMA ------------------------------------------------------------------------------
 __device__ __forceinline__ void prefetch_tmap(const CUtensorMap* m) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(m)) : "memory");

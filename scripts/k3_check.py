@@ -14,6 +14,7 @@ unit = False
 sep = 0
 tmode = 0
 seg = 1
+ew = 0
 while args and "=" in args[0]:
     kx, v = args.pop(0).split("=")
     if kx == "cg": cg = int(v)
@@ -21,6 +22,7 @@ while args and "=" in args[0]:
     if kx == "sep": sep = int(v)
     if kx == "mode": tmode = int(v)
     if kx == "seg": seg = int(v)
+    if kx == "ew": ew = int(v)
 cases = [(1000, 64, 128, 10), (5000, 384, 40, 10), (100000, 384, 300, 100), (70000, 100, 1024, 5), (3001, 1024, 129, 37)]
 if args:
     cases = [tuple(int(v) for v in a.split(",")) for a in args]
@@ -32,7 +34,7 @@ for (n, d, nq, k) in cases:
     else:
         x = None; q = b200knn.synth(5678, 0, nq, d).cpu().numpy()
         idx = b200knn.IndexFlatL2(d); idx.reserve(n); idx.add_synthetic(n, 1234, 0)
-    idx.set_option("path", 2); idx.set_option("timing", 1); idx.set_option("tensor_cta_group", cg); idx.set_option("tensor_sep_accum", sep); idx.set_option("tensor_mode", tmode); idx.set_option("tensor_segments", seg)
+    idx.set_option("path", 2); idx.set_option("timing", 1); idx.set_option("tensor_cta_group", cg); idx.set_option("tensor_sep_accum", sep); idx.set_option("tensor_mode", tmode); idx.set_option("tensor_segments", seg); idx.set_option("tensor_epilogue_warps", ew)
     D, I = idx.search(q, k)
     t0 = time.time(); D, I = idx.search(q, k); t1 = time.time()
     st = idx.stats()
