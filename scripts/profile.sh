@@ -6,9 +6,9 @@ R=${1:-r01}
 C3="python bench.py --workload c3 --steps 2 --warmup 1 --no-cpu-baseline"
 Q1="python bench.py --workload c3q1 --steps 5 --warmup 3 --no-cpu-baseline"
 $C3 > gpurun_out/${R}_c3_plain.log 2>&1 && \
-ncu --metrics gpu__time_duration.sum --clock-control none -c 80 --csv --log-file gpurun_out/${R}_c3_launches.csv $C3 > gpurun_out/${R}_c3_ncu1.log 2>&1
+ncu --metrics gpu__time_duration.sum --clock-control none -c 120 --csv --log-file gpurun_out/${R}_c3_launches.csv $C3 > gpurun_out/${R}_c3_ncu1.log 2>&1
 $C3 > /dev/null 2>&1 && \
-ncu --set full --clock-control none --import-source on -k regex:k3_tf32 -s 2 -c 1 -o gpurun_out/${R}_k3_c3 $C3 > gpurun_out/${R}_c3_ncu2.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:k3_tf32 -s 0 -c 7 -o gpurun_out/${R}_k3_c3 $C3 > gpurun_out/${R}_c3_ncu2.log 2>&1
 $Q1 > gpurun_out/${R}_q1_plain.log 2>&1 && \
 ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --csv --log-file gpurun_out/${R}_q1_launches.csv $Q1 > gpurun_out/${R}_q1_ncu1.log 2>&1
 $Q1 > /dev/null 2>&1 && \
