@@ -248,6 +248,7 @@ def main():
     # kernel alone (events recorded inside the library around the launch)
     q1 = q_dev[:1].contiguous()
     lat, lat_k = [], []
+    nq1_rows = "fp32"
     for i in range(30):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
@@ -259,6 +260,7 @@ def main():
             st1 = index.stats()
             if st1.get("path") == "scan" and st1.get("main_kernel_ms"):
                 lat_k.append(st1["main_kernel_ms"])
+                nq1_rows = st1.get("scan_rows", "fp32")
     p50_nq1 = statistics.median(lat)
     p50_nq1_kernel = statistics.median(lat_k) if lat_k else None
     ms_step = ms_dev / args.steps
@@ -313,10 +315,14 @@ def main():
     else:
         per_launch_ms = (stats["main_kernel_ms"] / max(stats.get("launches", 1), 1)) if stats.get("main_kernel_ms") \
             else ms_dev / max(launches, 1)
-        gbs = n_local * d * 4 / (per_launch_ms * 1e-3) / 1e9
-        roof = {"bound": "hbm", "kernel": "scan_l2_topk_kernel", "achieved": gbs, "peak": pk["hbm"], "unit": "GB/s",
+        bpe = 2 if stats.get("scan_rows") == "bf16+rerank" else 4
+        gbs = n_local * d * bpe / (per_launch_ms * 1e-3) / 1e9
+        roof = {"bound": "hbm", "kernel": "scan_l2_topk_kernel", "scan_rows": stats.get("scan_rows", "fp32"),
+                "achieved": gbs, "peak": pk["hbm"], "unit": "GB/s",
                 "traffic": None, "launch_ms": per_launch_ms, "peak_source": "%s copy bandwidth" % pk["source"],
-                "algorithmic": "N*d*4 bytes per launch (one pass over the rows per group of <= 8 queries)"}
+                "algorithmic": "N*d*%d bytes per launch (one pass over the %s per group of queries%s)" % (
+                    bpe, "bf16 copies of the rows" if bpe == 2 else "fp32 rows",
+                    "; the k best come from an exact fp32 re-rank of 2k+32 candidates" if bpe == 2 else "")}
     tr = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tr):
         # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full capture
@@ -328,7 +334,10 @@ def main():
     roof["scope"] = "one GPU (rank 0's shard of %d rows)" % n_local if world > 1 else "the one GPU"
     # single-query scan (the HBM-bound path) on the same index
     t_nq1 = p50_nq1_kernel or p50_nq1
-    roof_nq1 = {"bound": "hbm", "kernel": "scan_l2_topk_kernel", "achieved": n_local * d * 4 / (t_nq1 * 1e-3) / 1e9,
+    bpe1 = 2 if nq1_rows == "bf16+rerank" else 4
+    roof_nq1 = {"bound": "hbm", "kernel": "scan_l2_topk_kernel", "scan_rows": nq1_rows,
+                "achieved": n_local * d * bpe1 / (t_nq1 * 1e-3) / 1e9,
+                "algorithmic": "N*d*%d bytes (one pass over the %s)" % (bpe1, "bf16 copies of the rows" if bpe1 == 2 else "fp32 rows"),
                 "peak": pk["hbm"], "unit": "GB/s", "launch_ms": t_nq1,
                 "timed": "kernel (in-library CUDA events)" if p50_nq1_kernel else "public call (CUDA events)"}
     roof_nq1["frac"] = roof_nq1["achieved"] / roof_nq1["peak"]

@@ -138,7 +138,9 @@ B2K_API int b2k_search_rows_noalloc(int device, const float* x_dev, int64_t n, i
  * 3 = the same screen on bf16 copies of the rows (kept next to the fp32 rows, +50% memory;
  * needs d % 8 == 0, else 2 serves)), "tensor_segments" (1 default: the main pass runs in
  * segments with the k-th-distance bound refreshed in between; 0: one launch),
- * "tensor_epilogue_warps" (0 auto, 4, 8: warps filtering the accumulators in the screening modes).
+ * "tensor_epilogue_warps" (0 auto, 4, 8: warps filtering the accumulators in the screening modes),
+ * "scan_rows" (what the nq < 20 scan reads: 0 auto = the bf16 copies + exact fp32 re-rank once the
+ * rows exceed 128 MB, d % 8 == 0 and k <= 496; 1 = always the fp32 rows; 2 = bf16 whenever possible).
  * Unknown key -> B2K_EINVAL. */
 B2K_API int b2k_set_option(b2k_index* h, const char* key, int64_t value);
 
@@ -147,7 +149,8 @@ B2K_API int b2k_set_option(b2k_index* h, const char* key, int64_t value);
  * tensor-core main kernel; needs option "timing" = 1; synchronises on that kernel),
  * "tensor_mode_used" (1 / 2 / 3), "screen_fallbacks" (searches repeated in 3xTF32 mode because the
  * slack zone overflowed), "scan_kernel_ms" / "scan_launches" (the same for the scan kernel launches of the last
- * scan-path search). */
+ * scan-path search), "scan_rows_used" (1 fp32 rows / 2 bf16 copies + re-rank), "scan_fallback"
+ * (1 if the last bf16 scan was redone on the fp32 rows; synchronises the device). */
 B2K_API int b2k_get_stat(b2k_index* h, const char* key, double* out);
 
 /* Number of kernels this library has launched in this process (bench `gpu_launches`). */

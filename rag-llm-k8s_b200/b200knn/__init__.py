@@ -175,6 +175,8 @@ class IndexFlatL2:
             out["main_kernel_ms"] = v.value
             L.b2k_get_stat(self._h, b"scan_launches", C.byref(v))
             out["launches"] = int(v.value)
+        if out["path"] == "scan" and L.b2k_get_stat(self._h, b"scan_rows_used", C.byref(v)) == 0:
+            out["scan_rows"] = {1: "fp32", 2: "bf16+rerank"}.get(int(v.value))
         return out
 
     def set_option(self, key, value):

@@ -51,6 +51,14 @@ __device__ __forceinline__ float4 ldg_stream(const float4* p) {
     return r;
 }
 
+__device__ __forceinline__ uint4 ldg_stream(const uint4* p) {
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(p));
+    return r;
+}
+
 // Block-wide bitonic sort (ascending) of P = 2^m keys in shared memory.
 // All threads of the block must call; ends with the data visible to all threads.
 __device__ __forceinline__ void block_bitonic_sort(u64* s, int P) {

@@ -63,6 +63,8 @@ struct b2k_index {
     int opt_cta_group = 0;  // 0 = library default
     int opt_sep = 0;
     int opt_segments = 1;
+    int opt_scan_rows = 0;  // nq < 20 scan: 0 auto (bf16 copies + exact re-rank for large indexes), 1 fp32 rows, 2 bf16 copies
+    bool last_scan_bf = false;
     int opt_epi = 0;
     int opt_tensor_mode = 0;  // 0 auto (bf16 screening + exact re-rank where d % 8 == 0 and memory allows, else TF32 screening), 1 3xTF32, 2 TF32 screening, 3 bf16 screening
     int64_t stat_screen_fallbacks = 0;
@@ -79,6 +81,7 @@ struct b2k_index {
 static constexpr int64_t MAX_ROWS = 0xFFFFFFFEll;  // row index lives in the low 32 bits of a key
 static constexpr size_t IO_CHUNK = (size_t)64 << 20;
 static constexpr int MAX_NORM_SLOT = 2;  // h->done[0] ticket, [1] scan work counter, [2] bits of the largest squared row norm
+static constexpr int SCAN_FLAG_SLOT = 4;  // [4] raised by the bf16 scan's re-rank when its candidates did not cover the slack zone
 static constexpr int MAX_ERR_SLOT = 3;   // [3] bits of the largest squared bf16 rounding-error norm of a row
 static constexpr int64_t TC_QUERY_CHUNK = 4096;  // queries per tensor-core pass (faiss: distance_compute_blas_query_bs)
 
@@ -225,8 +228,31 @@ int enable_bf(b2k_index* h, cudaStream_t st) {
     return B2K_OK;
 }
 
+size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
+
+// Candidates the bf16 scan selects for a request of k (0: the bf16 scan cannot serve this k).
+int scan_bf_candidates(int k) {
+    const int kp = 2 * k + 32;
+    return kp <= B2K_MAX_K ? kp : 0;
+}
+
+// The bf16 scan pays once the rows are large enough for HBM time to matter: below 128 MB of rows
+// the extra re-rank launch costs more than the halved row stream saves.
+bool scan_wants_bf(const b2k_index* h, int k) {
+    if (h->opt_scan_rows == 1 || h->bf_nomem || h->d % 8 != 0 || scan_bf_candidates(k) == 0) return false;
+    if (h->opt_scan_rows == 2) return true;
+    return (double)h->ntotal * h->d >= 32e6;
+}
+
+size_t scan_ws_bytes(const b2k_index* h, int64_t nq, int k, bool bf) {
+    const int grid = scan_grid(h->ntotal, h->sm_count, h->opt_scan_ctas_per_sm);
+    if (!bf) return scan_partial_bytes(grid, 8, k);
+    const int kp = scan_bf_candidates(k);
+    return align256(scan_partial_bytes(grid, 8, kp)) + align256((size_t)nq * kp * 4) + align256((size_t)nq * kp * 8);
+}
+
 int scan_search(b2k_index* h, int64_t nq, const float* qd, int k, float* Dd, int64_t* Id, unsigned char* ws_tail,
-                cudaStream_t st) {
+                cudaStream_t st, bool bf) {
     const int grid = scan_grid(h->ntotal, h->sm_count, h->opt_scan_ctas_per_sm);
     u64* partial = reinterpret_cast<u64*>(ws_tail);
     if (h->opt_timing) {
@@ -234,6 +260,37 @@ int scan_search(b2k_index* h, int64_t nq, const float* qd, int k, float* Dd, int
         B2K_CUDA(cudaEventRecord(h->ev_t0, st));
     }
     h->scan_launches = 0;
+    h->last_scan_bf = bf;
+    if (bf) {
+        // screening scan over the bf16 copies -> kp candidates per query -> exact re-rank; if the
+        // candidates did not cover the slack zone (flag), the fp32 scan behind it redoes the search
+        const int kp = scan_bf_candidates(k);
+        unsigned char* w = ws_tail + align256(scan_partial_bytes(grid, 8, kp));
+        float* Da = reinterpret_cast<float*>(w);
+        int64_t* Ia = reinterpret_cast<int64_t*>(w + align256((size_t)nq * kp * 4));
+        unsigned int* flag = h->done + SCAN_FLAG_SLOT;
+        B2K_CUDA(cudaMemsetAsync(flag, 0, sizeof(unsigned int), st));
+        for (int64_t q0 = 0; q0 < nq;) {
+            int qt = scan_pick_qt(nq - q0, kp);
+            if (qt > 4) qt = 4;  // 8 queries per pass would make the bf16 variant ALU-bound
+            int rc = launch_scan(h->xbf, qd + q0 * (int64_t)h->d, h->ntotal, h->d, qt, kp, grid, partial, h->done,
+                                 Da + q0 * kp, Ia + q0 * kp, st, true, nullptr);
+            if (rc) return rc;
+            q0 += qt;
+            ++h->scan_launches;
+        }
+        if (h->opt_timing) { B2K_CUDA(cudaEventRecord(h->ev_t1, st)); h->scan_timed = true; }
+        int rc = launch_scan_rerank(h->x, qd, nq, h->d, k, kp, Da, Ia, h->done + MAX_ERR_SLOT, Dd, Id, flag, st);
+        if (rc) return rc;
+        for (int64_t q0 = 0; q0 < nq;) {
+            int qt = scan_pick_qt(nq - q0, k);
+            rc = launch_scan(h->x, qd + q0 * (int64_t)h->d, h->ntotal, h->d, qt, k, grid, partial, h->done,
+                             Dd + q0 * k, Id + q0 * k, st, false, flag);
+            if (rc) return rc;
+            q0 += qt;
+        }
+        return B2K_OK;
+    }
     for (int64_t q0 = 0; q0 < nq;) {
         int qt = scan_pick_qt(nq - q0, k);
         int rc = launch_scan(h->x, qd + q0 * (int64_t)h->d, h->ntotal, h->d, qt, k, grid, partial, h->done,
@@ -246,7 +303,7 @@ int scan_search(b2k_index* h, int64_t nq, const float* qd, int k, float* Dd, int
     return B2K_OK;
 }
 
-size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
+
 
 }  // namespace
 
@@ -332,6 +389,9 @@ int b2k_set_option(b2k_index* h, const char* key, int64_t value) {
         if (value != 0 && value != 4 && value != 8) { set_error("option tensor_epilogue_warps must be 0 (auto), 4 or 8"); return B2K_EINVAL; }
         h->opt_epi = (int)value / 4;
         if (h->k3) k3_set_epi_halves(h->k3, h->opt_epi);
+    } else if (!strcmp(key, "scan_rows")) {
+        if (value < 0 || value > 2) { set_error("option scan_rows must be 0 (auto), 1 (fp32 rows) or 2 (bf16 copies + exact re-rank)"); return B2K_EINVAL; }
+        h->opt_scan_rows = (int)value;
     } else if (!strcmp(key, "timing")) {
         h->opt_timing = value != 0;
         if (h->k3) k3_set_timing(h->k3, h->opt_timing != 0);
@@ -348,6 +408,17 @@ int b2k_get_stat(b2k_index* h, const char* key, double* out) {
     if (!strcmp(key, "last_path")) { *out = h->last_path; return B2K_OK; }
     if (!strcmp(key, "tensor_mode_used")) { *out = h->k3 ? k3_last_mode(h->k3) : 0; return B2K_OK; }
     if (!strcmp(key, "screen_fallbacks")) { *out = (double)h->stat_screen_fallbacks; return B2K_OK; }
+    if (!strcmp(key, "scan_rows_used")) { *out = h->last_scan_bf ? 2 : 1; return B2K_OK; }
+    if (!strcmp(key, "scan_fallback")) {  // 1 if the last bf16 scan had to be redone on the fp32 rows (synchronises)
+        DeviceGuard g(h->device);
+        unsigned int f = 0;
+        if (h->last_scan_bf) {
+            B2K_CUDA(cudaDeviceSynchronize());
+            B2K_CUDA(cudaMemcpy(&f, h->done + SCAN_FLAG_SLOT, sizeof(f), cudaMemcpyDeviceToHost));
+        }
+        *out = f;
+        return B2K_OK;
+    }
     if (!strcmp(key, "tensor_kernel_ms")) {
         float ms = 0.f;
         if (!h->k3 || k3_last_kernel_ms(h->k3, &ms)) { set_error("no timed tensor-core kernel yet (set option timing=1)"); return B2K_EINVAL; }
@@ -466,7 +537,14 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
     const int kk = (int)k;
     cudaStream_t st = on_device ? (cudaStream_t)stream : h->stream;
 
-    const bool want_tc = h->ntotal > 0 && (h->opt_path == 2 || (h->opt_path == 0 && nq >= 20)) && k3_supported(h->d, kk);
+    // faiss switches from direct differences to the sgemm expansion at nq = 20; here both kernels end
+    // in direct fp32 differences (the tensor path re-ranks), so the switch is purely a matter of speed:
+    // the scan costs one pass over the rows per group of <= 4 (bf16) or 8 (fp32) queries, the tensor
+    // path ~0.3 ms of fixed work plus one cheap pass for any nq <= 128 (measured at 10M x 384: nq = 8
+    // scan 4.9 ms, tensor 1.9 ms; nq = 16: 9.8 vs 1.9; nq = 2: 1.8 vs 1.9; at 100k rows nq = 4: 0.12 vs 0.16 ms).
+    const double elems = (double)h->ntotal * h->d;
+    const bool tc_pays = nq >= 20 || (h->opt_tensor_mode != 1 && ((nq >= 5 && elems >= 16e6) || (nq >= 3 && elems >= 256e6)));
+    const bool want_tc = h->ntotal > 0 && (h->opt_path == 2 || (h->opt_path == 0 && tc_pays)) && k3_supported(h->d, kk);
 
     // workspace: [queries][D][I] for host callers, then the kernels' scratch
     size_t q_bytes = align256((size_t)nq * h->d * sizeof(float));
@@ -476,7 +554,7 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
     size_t scratch = 0;
     if (h->ntotal > 0) {
         if (want_tc) scratch = k3_scratch_bytes(h->sm_count, h->d, nq < TC_QUERY_CHUNK ? nq : TC_QUERY_CHUNK, kk);
-        else scratch = scan_partial_bytes(scan_grid(h->ntotal, h->sm_count, h->opt_scan_ctas_per_sm), 8, kk);
+        else scratch = scan_ws_bytes(h, nq, kk, scan_wants_bf(h, kk));
     }
     int rc = ensure_ws(h, io_bytes + align256(scratch));
     if (rc) return rc;
@@ -533,7 +611,9 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
         }
     } else {
         h->last_path = 1;
-        rc = scan_search(h, nq, qd, kk, Dd, Id, ws_tail, st);
+        bool bf = scan_wants_bf(h, kk);
+        if (bf && enable_bf(h, st) != B2K_OK) bf = false;  // no room for the copies: fp32 rows (the workspace is large enough for either)
+        rc = scan_search(h, nq, qd, kk, Dd, Id, ws_tail, st, bf);
     }
     if (rc) return rc;
     B2K_CUDA(cudaEventRecord(h->ev_ws, st));

@@ -14,6 +14,15 @@
 // k best keys, and the LAST CTA to finish (atomic ticket) merges all CTAs' lists and
 // writes D / I -- so the whole search is ONE launch per query group and no distance ever
 // reaches HBM.  Roofline: HBM; algorithmic bytes per launch = n * d * 4.
+//
+// BF variant (screening): the same kernel over the bf16 copies of the rows (half the bytes).
+// d~ = |q - x~|^2 is computed in fp32 from the fp32 query and the bf16 row x~; by the triangle
+// inequality | |q - x~| - |q - x| | <= |x - x~| <= E (E = largest rounding-error norm of a row,
+// tracked by K1), so every exact top-k row satisfies sqrt(d~) <= sqrt(T~) + 2E with T~ the k-th
+// smallest d~.  The scan therefore selects k' > k candidates by d~, and the re-rank kernel
+// (scan_rerank_kernel) checks that the k'-th d~ lies strictly beyond that zone (else it raises a
+// flag and the fp32 scan, launched right behind with "run only if flagged", redoes the search),
+// computes the exact fp32 distances of the k' rows and writes the k best.  Results are exact.
 #include "common.cuh"
 #include "kernels.h"
 
@@ -71,13 +80,30 @@ __device__ __forceinline__ void compact(u64* buf, int P, int* cnt, u64* kth, flo
     __syncthreads();
 }
 
-template <int QT, bool VEC>
+// 8 columns of a row as fp32: two float4 of an fp32 row, or one 16-byte group of 8 bf16
+// (bf16 -> fp32 is a 16-bit shift, exact).
+struct RowSeg8 { float v[8]; };
+__device__ __forceinline__ RowSeg8 unpack_bf16x8(const uint4& w) {
+    RowSeg8 r;
+    r.v[0] = __uint_as_float(w.x << 16); r.v[1] = __uint_as_float(w.x & 0xffff0000u);
+    r.v[2] = __uint_as_float(w.y << 16); r.v[3] = __uint_as_float(w.y & 0xffff0000u);
+    r.v[4] = __uint_as_float(w.z << 16); r.v[5] = __uint_as_float(w.z & 0xffff0000u);
+    r.v[6] = __uint_as_float(w.w << 16); r.v[7] = __uint_as_float(w.w & 0xffff0000u);
+    return r;
+}
+
+// BF: X points to bf16 rows (d % 8 == 0), see the file header.  run_if (nullable): the launch is a
+// conditional repeat and does nothing unless *run_if != 0.
+template <int QT, bool VEC, bool BF>
 __global__ void __launch_bounds__(SCAN_THREADS)
-scan_l2_topk_kernel(const float* __restrict__ X, const float* __restrict__ Q, int64_t n, int d,
+scan_l2_topk_kernel(const void* __restrict__ Xv, const float* __restrict__ Q, int64_t n, int d,
                     int k, int P, u64* __restrict__ partial,
-                    unsigned int* __restrict__ done, float* __restrict__ D, int64_t* __restrict__ I) {
+                    unsigned int* __restrict__ done, float* __restrict__ D, int64_t* __restrict__ I,
+                    const unsigned int* __restrict__ run_if) {
+    if (run_if && *run_if == 0u) return;
+    const float* __restrict__ X = static_cast<const float*>(Xv);
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    const int dq = (d + 3) & ~3;
+    const int dq = BF ? ((d + 7) & ~7) : ((d + 3) & ~3);
     ScanSmem s = carve(smem_raw, QT, dq, P);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     __shared__ int s_is_last;
@@ -112,7 +138,89 @@ scan_l2_topk_kernel(const float* __restrict__ X, const float* __restrict__ Q, in
         for (int q = 0; q < QT; ++q) tau_r[q] = s.tau[q];
         int flag = 0;
 
-        if (VEC) {
+        if (BF) {
+            // bf16 rows: 8 lanes per row, 16 bytes = 8 columns per lane and request, 64 columns per step
+            const unsigned short* Xb = static_cast<const unsigned short*>(Xv);
+            const int g = lane >> 3, cl = (lane & 7) * 8;
+            float acc[4][QT];
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+#pragma unroll
+                for (int q = 0; q < QT; ++q) acc[u][q] = 0.f;
+            int64_t rows[4];
+            const unsigned short* rp[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                rows[u] = base + warp * 16 + u * 4 + g;
+                int64_t rr = rows[u] < row_end ? rows[u] : row_begin;
+                rp[u] = Xb + rr * (int64_t)d + cl;
+            }
+            uint4 xv[4];
+            {
+                const bool cok0 = cl < d;
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                    xv[u] = cok0 ? ldg_stream(reinterpret_cast<const uint4*>(rp[u])) : make_uint4(0u, 0u, 0u, 0u);
+            }
+#pragma unroll 1
+            for (int c0 = 0; c0 < d; c0 += 64) {
+                const bool cok = (c0 + cl) < d;
+                const bool nok = (c0 + 64 + cl) < d;
+                uint4 xn[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                    xn[u] = nok ? ldg_stream(reinterpret_cast<const uint4*>(rp[u] + c0 + 64)) : make_uint4(0u, 0u, 0u, 0u);
+                RowSeg8 xs[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) xs[u] = unpack_bf16x8(xv[u]);
+#pragma unroll
+                for (int q = 0; q < QT; ++q) {
+                    // beyond d both the query (zero padding) and the row (zero bits) are 0
+                    const float4 qa = cok ? *reinterpret_cast<const float4*>(s.qs + q * dq + c0 + cl) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    const float4 qb = cok ? *reinterpret_cast<const float4*>(s.qs + q * dq + c0 + cl + 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    const float qv[8] = {qa.x, qa.y, qa.z, qa.w, qb.x, qb.y, qb.z, qb.w};
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+#pragma unroll
+                        for (int t = 0; t < 8; ++t) {
+                            const float a = qv[t] - xs[u].v[t];
+                            acc[u][q] = fmaf(a, a, acc[u][q]);
+                        }
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) xv[u] = xn[u];
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+#pragma unroll
+                for (int q = 0; q < QT; ++q) {
+                    float v = acc[u][q];
+                    v += __shfl_xor_sync(0xffffffffu, v, 1);
+                    v += __shfl_xor_sync(0xffffffffu, v, 2);
+                    v += __shfl_xor_sync(0xffffffffu, v, 4);
+                    acc[u][q] = v;
+                }
+            if ((lane & 7) == 0) {
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    if (rows[u] < row_end) {
+#pragma unroll
+                        for (int q = 0; q < QT; ++q) {
+                            float dv = acc[u][q];
+                            if (dv <= tau_r[q]) {
+                                u64 key = make_key(dv, (uint32_t)rows[u]);
+                                if (key < s.kth[q]) {
+                                    int pos = atomicAdd(&s.cnt[q], 1);
+                                    s.buf[q * P + pos] = key;
+                                    if (pos + 1 > P - SCAN_ROWS_PER_ITER) flag = 1;
+                                }
+                            }
+                        }
+                    }
+                }
+            }
+        } else if (VEC) {
             // 8 lanes per row, 4 rows per warp request, 4 requests (u) in flight.
             const int g = lane >> 3, cl = (lane & 7) * 4;
             float acc[4][QT];
@@ -363,38 +471,46 @@ int scan_grid(int64_t n, int sm_count, int ctas_per_sm) {
 
 size_t scan_partial_bytes(int grid, int qt, int k) { return (size_t)grid * qt * k * sizeof(u64); }
 
-template <int QT, bool VEC>
-static int launch_scan_t(const float* X, const float* Q, int64_t n, int d, int k, int P, int grid,
-                         u64* partial, unsigned int* done, float* D, int64_t* I, cudaStream_t st) {
+template <int QT, bool VEC, bool BF>
+static int launch_scan_t(const void* X, const float* Q, int64_t n, int d, int k, int P, int grid,
+                         u64* partial, unsigned int* done, float* D, int64_t* I, const unsigned int* run_if,
+                         cudaStream_t st) {
     size_t smem = scan_smem_bytes(QT, d, P);
     if (smem > 48 * 1024)  // per-device attribute: set on every large launch (a handle may live on any GPU)
-        B2K_CUDA(cudaFuncSetAttribute(scan_l2_topk_kernel<QT, VEC>,
+        B2K_CUDA(cudaFuncSetAttribute(scan_l2_topk_kernel<QT, VEC, BF>,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     // one wave: never launch more CTAs than are resident at once (register/smem limited per variant)
     int occ = 0, dev = 0, sms = 0;
-    B2K_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, scan_l2_topk_kernel<QT, VEC>, SCAN_THREADS, smem));
+    B2K_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, scan_l2_topk_kernel<QT, VEC, BF>, SCAN_THREADS, smem));
     B2K_CUDA(cudaGetDevice(&dev));
     B2K_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     if (occ > 0 && grid > occ * sms) grid = occ * sms;
-    scan_l2_topk_kernel<QT, VEC><<<grid, SCAN_THREADS, smem, st>>>(X, Q, n, d, k, P, partial, done, D, I);
+    scan_l2_topk_kernel<QT, VEC, BF><<<grid, SCAN_THREADS, smem, st>>>(X, Q, n, d, k, P, partial, done, D, I, run_if);
     count_launch();
     B2K_CUDA(cudaGetLastError());
     return B2K_OK;
 }
 
 // One launch: QT (1,2,4,8) queries against rows [0,n).  Q, D, I already offset to the group.
-int launch_scan(const float* X, const float* Q, int64_t n, int d, int qt, int k, int grid,
-                u64* partial, unsigned int* done, float* D, int64_t* I, cudaStream_t st) {
+// bf16: X holds bf16 rows (d % 8 == 0) and D receives the screening distances d~.
+int launch_scan(const void* X, const float* Q, int64_t n, int d, int qt, int k, int grid,
+                u64* partial, unsigned int* done, float* D, int64_t* I, cudaStream_t st, bool bf16,
+                const unsigned int* run_if) {
     const int P = scan_pick_P(k);
     const bool vec = (d % 4 == 0) && ((reinterpret_cast<uintptr_t>(X) & 15) == 0);
     if (scan_smem_bytes(qt, d, P) > 200 * 1024) {
         set_error("scan kernel: d=%d too large for shared memory", d);
         return B2K_ELIMIT;
     }
-#define B2K_SCAN_CASE(QT_)                                                                          \
-    case QT_:                                                                                       \
-        return vec ? launch_scan_t<QT_, true>(X, Q, n, d, k, P, grid, partial, done, D, I, st)      \
-                   : launch_scan_t<QT_, false>(X, Q, n, d, k, P, grid, partial, done, D, I, st);
+    if (bf16 && (d % 8 != 0 || !vec)) {
+        set_error("scan kernel: bf16 rows need d %% 8 == 0 and 16-byte alignment");
+        return B2K_EINVAL;
+    }
+#define B2K_SCAN_CASE(QT_)                                                                                        \
+    case QT_:                                                                                                     \
+        if (bf16) return launch_scan_t<QT_, true, true>(X, Q, n, d, k, P, grid, partial, done, D, I, run_if, st); \
+        return vec ? launch_scan_t<QT_, true, false>(X, Q, n, d, k, P, grid, partial, done, D, I, run_if, st)     \
+                   : launch_scan_t<QT_, false, false>(X, Q, n, d, k, P, grid, partial, done, D, I, run_if, st);
     switch (qt) {
         B2K_SCAN_CASE(1)
         B2K_SCAN_CASE(2)
@@ -404,6 +520,77 @@ int launch_scan(const float* X, const float* Q, int64_t n, int d, int qt, int k,
 #undef B2K_SCAN_CASE
     set_error("scan kernel: bad query-group size %d", qt);
     return B2K_EINVAL;
+}
+
+// ---- re-rank of the bf16 scan's candidates ---------------------------------------------------
+// One CTA per query: the kp candidates (ids Ia, screening distances Da, sorted by (d~, id)) ->
+// exact fp32 distances (direct differences, one warp per row, fixed summation order: the
+// arithmetic of the fp32 scan's rule (1)) -> the k best by (distance, id).  Coverage check first:
+// every row that could be in the exact top-k has sqrt(d~) <= sqrt(T~) + 2E (file header), T~ the
+// k-th candidate's d~; if the LAST candidate is not strictly beyond that zone, rows outside the
+// candidate list could belong to the answer and *flag is raised (the caller's conditional fp32
+// scan then overwrites D / I).  eta covers the fp32 rounding of the d~ sums themselves.
+static constexpr int RERANK_THREADS = 256;
+__global__ void __launch_bounds__(RERANK_THREADS)
+scan_rerank_kernel(const float* __restrict__ X, const float* __restrict__ Q, int d, int k, int kp,
+                   const float* __restrict__ Da, const int64_t* __restrict__ Ia,
+                   const unsigned int* __restrict__ max_err_bits, float* __restrict__ D, int64_t* __restrict__ I,
+                   unsigned int* __restrict__ flag) {
+    __shared__ u64 keys[1024];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int64_t qi = blockIdx.x;
+    const float* da = Da + qi * kp;
+    const int64_t* ia = Ia + qi * kp;
+    if (tid == 0 && ia[kp - 1] >= 0 && ia[k - 1] >= 0) {  // the list is full: rows exist beyond it
+        const float E = sqrtf(__uint_as_float(*max_err_bits)) * 1.001f;
+        const float eta = ((float)d * 0.125f + 8.f) * 5.97e-8f;
+        const float zr = (sqrtf(da[k - 1]) * (1.f + 2.f * eta) + 2.f * E) * (1.f + 2.f * eta);
+        const float zone = zr * zr * (1.f + 1e-6f);
+        if (!(da[kp - 1] > zone)) atomicExch(flag, 1u);
+    }
+    int Ps = 2;
+    while (Ps < kp) Ps <<= 1;
+    for (int c = tid; c < Ps; c += RERANK_THREADS) keys[c] = KEY_EMPTY;
+    __syncthreads();
+    const float* qv = Q + qi * (int64_t)d;
+    for (int c = warp; c < kp; c += RERANK_THREADS / 32) {
+        const int64_t id = ia[c];
+        if (id < 0) continue;  // warp-uniform
+        const float* xv = X + id * (int64_t)d;
+        float acc = 0.f;
+        for (int t = lane * 4; t < d; t += 128) {
+            const float4 a = __ldg(reinterpret_cast<const float4*>(qv + t));
+            const float4 b = ldg_stream(reinterpret_cast<const float4*>(xv + t));
+            const float e0 = a.x - b.x, e1 = a.y - b.y, e2 = a.z - b.z, e3 = a.w - b.w;
+            acc = fmaf(e0, e0, acc); acc = fmaf(e1, e1, acc); acc = fmaf(e2, e2, acc); acc = fmaf(e3, e3, acc);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        if (lane == 0 && acc < FLT_MAX) keys[c] = make_key(acc, (uint32_t)id);
+    }
+    __syncthreads();
+    block_bitonic_sort(keys, Ps);
+    for (int j = tid; j < k; j += RERANK_THREADS) {
+        const u64 key = j < Ps ? keys[j] : KEY_EMPTY;
+        if (key != KEY_EMPTY) {
+            D[qi * k + j] = key_dist(key);
+            I[qi * k + j] = (int64_t)key_row(key);
+        } else {
+            D[qi * k + j] = FLT_MAX;
+            I[qi * k + j] = -1;
+        }
+    }
+}
+
+int launch_scan_rerank(const float* X, const float* Q, int64_t nq, int d, int k, int kp, const float* Da,
+                       const int64_t* Ia, const unsigned int* max_err_bits, float* D, int64_t* I,
+                       unsigned int* flag, cudaStream_t st) {
+    if (nq <= 0) return B2K_OK;
+    if (kp > 1024 || kp < k || d % 4 != 0) { set_error("scan re-rank: bad candidate count %d for k=%d", kp, k); return B2K_EINVAL; }
+    scan_rerank_kernel<<<(unsigned)nq, RERANK_THREADS, 0, st>>>(X, Q, d, k, kp, Da, Ia, max_err_bits, D, I, flag);
+    count_launch();
+    B2K_CUDA(cudaGetLastError());
+    return B2K_OK;
 }
 
 }  // namespace b2k

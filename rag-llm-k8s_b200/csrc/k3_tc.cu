@@ -878,7 +878,8 @@ static int k3_cg_for(int k, int want, int d, bool screen, int64_t n, int64_t nq,
     if (want == 1 || want == 2) return (want == 1 && !screen && k3_P(k) > 512) ? 2 : want;
     if (screen) {
         const int64_t units2 = ((n + K3_BN - 1) / K3_BN) * ((nq + 2 * K3_BM - 1) / (2 * K3_BM));
-        return units2 >= 64LL * (sm_count / 2) ? 2 : 1;
+        // a pair serves 256 queries per unit: with <= 128 its second CTA would multiply padding
+        return (nq > K3_BM && units2 >= 64LL * (sm_count / 2)) ? 2 : 1;
     }
     if (k3_P(k) > 512) return 2;
     return d >= 512 ? 2 : 1;

@@ -18,8 +18,14 @@ int scan_pick_P(int k);
 int scan_pick_qt(int64_t nq_left, int k);
 int scan_grid(int64_t n, int sm_count, int ctas_per_sm);
 size_t scan_partial_bytes(int grid, int qt, int k);
-int launch_scan(const float* X, const float* Q, int64_t n, int d, int qt, int k, int grid,
-                u64* partial, unsigned int* done, float* D, int64_t* I, cudaStream_t st);
+// bf16 = true: X holds bf16 rows and D receives screening distances; run_if (nullable): do nothing unless *run_if != 0
+int launch_scan(const void* X, const float* Q, int64_t n, int d, int qt, int k, int grid,
+                u64* partial, unsigned int* done, float* D, int64_t* I, cudaStream_t st, bool bf16 = false,
+                const unsigned int* run_if = nullptr);
+// exact fp32 re-rank of the bf16 scan's kp candidates per query -> k best; raises *flag when kp did not cover the slack zone
+int launch_scan_rerank(const float* X, const float* Q, int64_t nq, int d, int k, int kp, const float* Da,
+                       const int64_t* Ia, const unsigned int* max_err_bits, float* D, int64_t* I,
+                       unsigned int* flag, cudaStream_t st);
 int launch_fill_empty(float* D, int64_t* I, int64_t count, cudaStream_t st);
 
 // K5 (k5_merge.cu): per query, k smallest (distance,id) of nlists*k candidates.

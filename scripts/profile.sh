@@ -12,5 +12,5 @@ ncu --set full --clock-control none --import-source on -k regex:k3_tf32 -s 0 -c 
 $Q1 > gpurun_out/${R}_q1_plain.log 2>&1 && \
 ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --csv --log-file gpurun_out/${R}_q1_launches.csv $Q1 > gpurun_out/${R}_q1_ncu1.log 2>&1
 $Q1 > /dev/null 2>&1 && \
-ncu --set full --clock-control none --import-source on -k regex:scan_l2 -s 4 -c 1 -o gpurun_out/${R}_k2_c3q1 $Q1 > gpurun_out/${R}_q1_ncu2.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:scan_l2 -s 4 -c 2 -o gpurun_out/${R}_k2_c3q1 $Q1 > gpurun_out/${R}_q1_ncu2.log 2>&1
 ls -la gpurun_out | tail -12

@@ -1,4 +1,4 @@
-"""Per-phase timing of the sharded nq=1 search (run under torchrun)."""
+"""Per-phase timing of the sharded search (run under torchrun):  shard_lat.py [N] [nq] [k] [d]"""
 import os, sys, statistics, time
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "rag-llm-k8s_b200"))
@@ -7,18 +7,53 @@ import b200knn
 from b200knn.sharded import ShardedIndexFlatL2
 lr = int(os.environ.get("LOCAL_RANK", "0")); torch.cuda.set_device(lr)
 dist.init_process_group("nccl", device_id=torch.device("cuda", lr))
-N, d, k = 10_000_000, 384, 100
+a = [int(v) for v in sys.argv[1:]]
+N = a[0] if len(a) > 0 else 10_000_000
+nq = a[1] if len(a) > 1 else 1024
+k = a[2] if len(a) > 2 else 100
+d = a[3] if len(a) > 3 else 384
 idx = ShardedIndexFlatL2(d, device=lr); idx.add_synthetic_global(N, 1234); idx.set_option("timing", 1)
-q = b200knn.synth(5678, 0, 1, d, device=lr)
-for nq in (1, 1024):
-    qq = b200knn.synth(5678, 0, nq, d, device=lr)
-    ev, wall, kern = [], [], []
-    for i in range(25):
-        torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        t0 = time.perf_counter(); e0.record(); idx.search(qq, k); e1.record(); torch.cuda.synchronize(); t1 = time.perf_counter()
-        if i >= 5:
-            ev.append(e0.elapsed_time(e1)); wall.append((t1 - t0) * 1e3); kern.append(idx.stats()["main_kernel_ms"])
-    if dist.get_rank() == 0:
-        print("nq=%d world=%d: events %.3f ms, wall %.3f ms, local kernel %.3f ms" % (nq, dist.get_world_size(), statistics.median(ev), statistics.median(wall), statistics.median(kern)), flush=True)
+qq = b200knn.synth(5678, 0, nq, d, device=lr)
+W = dist.get_world_size()
+
+
+def ev():
+    e = torch.cuda.Event(enable_timing=True); e.record(); return e
+
+
+rows = []
+for i in range(25):
+    torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    e0 = ev()
+    D, I = idx.local.search(qq, k)
+    e1 = ev()
+    nk = nq * k
+    words = nk + (nk + 1) // 2
+    send = torch.empty(words, dtype=torch.int64, device=qq.device)
+    send[:nk].view(nq, k).copy_(idx._to_global(torch.as_tensor(I)))
+    send[nk:].view(torch.float32)[:nk].view(nq, k).copy_(torch.as_tensor(D))
+    e2 = ev()
+    recv = torch.empty(W * words, dtype=torch.int64, device=qq.device)
+    dist.all_gather_into_tensor(recv, send)
+    e3 = ev()
+    recv = recv.view(W, words)
+    Icat = recv[:, :nk].reshape(W, nq, k)
+    Dcat = recv[:, nk:].contiguous().view(torch.float32)[:, :nk].reshape(W, nq, k)
+    Dm, Im = b200knn.merge_topk(Dcat, Icat)
+    e4 = ev()
+    torch.cuda.synchronize(); t1 = time.perf_counter()
+    if i >= 5:
+        rows.append((e0.elapsed_time(e1), e1.elapsed_time(e2), e2.elapsed_time(e3), e3.elapsed_time(e4), (t1 - t0) * 1e3,
+                     idx.local.stats().get("main_kernel_ms", 0.0)))
+    # whole call through the public method, for comparison
+tot = []
+for i in range(15):
+    torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
+    e0 = ev(); idx.search(qq, k); e1 = ev(); torch.cuda.synchronize()
+    if i >= 5: tot.append(e0.elapsed_time(e1))
+if dist.get_rank() == 0:
+    med = [statistics.median(c) for c in zip(*rows)]
+    print("N=%d nq=%d k=%d d=%d world=%d: local search %.3f (main pass %.3f) | pack %.3f | all_gather %.3f | merge %.3f | wall %.3f ms ; public search() %.3f ms"
+          % (N, nq, k, d, W, med[0], med[5], med[1], med[2], med[3], med[4], statistics.median(tot)), flush=True)
 dist.destroy_process_group()

@@ -102,11 +102,14 @@ if os.path.exists(k3_rep):
     md.append("\nDRAM traffic of the main pass (read + write, all segments) = **%.2f GB**; the rows are 15.36 GB as fp32, 7.68 GB as the bf16 copies the screening reads.\n" % (tot / 1e9))
 
 for tag, rep, wl, kern, note in [
-        ("K2 scan, C3 nq=1 (10M x 384, k=100)", "%s_k2_c3q1.ncu-rep" % R, "c3q1", "scan_l2_topk_kernel", "one scan launch")]:
+        ("K2 scan, C3 nq=1 (10M x 384, k=100; bf16 copies, 232 candidates, exact fp32 re-rank behind it)", "%s_k2_c3q1.ncu-rep" % R, "c3q1", "scan_l2_topk_kernel", "one scan launch")]:
     rep_path = os.path.join(G, rep)
     if not os.path.exists(rep_path):
         continue
-    m = raw_metrics(rep_path, WANTED)
+    # two consecutive launches are captured: the scan over the bf16 copies and, right behind it, the
+    # conditional fp32 repeat, which exits at once unless the re-rank raised its flag -- keep the real one
+    cands = raw_metrics_all(rep_path, WANTED)
+    m = max(cands, key=lambda mm: to_ms(*mm["gpu__time_duration.sum"]))
     md.append("## %s\n\n`ncu --set full --clock-control none --import-source on` (%s). Cold-ish caches, serialised: compare shares, not absolutes.\n" % (tag, note))
     md.append("| metric | value |\n|---|---|")
     for k, (v, u) in m.items():

@@ -574,6 +574,89 @@ def test_bf16_screening_incremental_adds_and_fallbacks(faiss):
     assert_knn_matches(D, I, z, qz, 10, expanded=True, what="bf16 overflow fallback")
 
 
+def _scan_fallback(idx):
+    import ctypes as C
+    from b200knn import _lib
+    v = C.c_double()
+    assert _lib.lib().b2k_get_stat(idx._h, b"scan_fallback", C.byref(v)) == 0
+    return int(v.value)
+
+
+@pytest.mark.parametrize("n,d,nq,k", [(30000, 64, 1, 5), (50000, 384, 1, 100), (20011, 128, 3, 10), (40000, 256, 19, 37),
+                                      (9000, 1024, 2, 496), (300, 64, 1, 10), (5, 8, 4, 3)])
+def test_scan_over_bf16_copies_is_exact(faiss, n, d, nq, k):
+    """nq < 20 on the bf16 copies of the rows (`scan_rows` = 2): candidates by |q - bf16(x)|^2, exact
+    fp32 re-rank -- the same (D, I) as the oracle and as the fp32-row scan (both end in a direct fp32
+    sum; only the summation order differs), on N(0,1) rows and on unit-norm rows with self matches."""
+    rng = np.random.default_rng(n + k)
+    for unit in (False, True):
+        x = O.synth(71, 0, n, d)
+        q = O.synth(72, 0, nq, d)
+        if unit:
+            x, q = unit_rows(x), unit_rows(q)
+            q[0] = x[rng.integers(0, n)]
+        idx = _build(faiss, x)
+        idx.set_option("path", 1)
+        idx.set_option("scan_rows", 2)
+        D, I = idx.search(q, k)
+        st = idx.stats()
+        assert st["path"] == "scan" and st["scan_rows"] == "bf16+rerank"
+        assert _scan_fallback(idx) == 0
+        if unit:
+            assert D[0, 0] == 0.0
+        assert_knn_matches(D, I, x, q, k, what="bf16 scan n=%d d=%d nq=%d k=%d unit=%s" % (n, d, nq, k, unit))
+        ref = _build(faiss, x)
+        ref.set_option("path", 1)
+        ref.set_option("scan_rows", 1)
+        Dr, Ir = ref.search(q, k)
+        assert ref.stats()["scan_rows"] == "fp32"
+        assert_knn_matches(D, I, x, q, k, Dr, Ir, what="bf16 scan vs fp32 scan")
+
+
+def test_scan_over_bf16_copies_falls_back_and_follows_adds(faiss):
+    """Thousands of rows at (almost) the k-th distance do not fit the candidate list: the
+    conditional fp32 scan behind the re-rank must redo the search (flag raised, results still
+    exact).  Rows added after the bf16 copies exist are found; d % 8 != 0 and k > 496 use fp32."""
+    rng = np.random.default_rng(3)
+    base = rng.standard_normal((1, 64)).astype(np.float32)
+    z = np.repeat(base, 20000, 0) + rng.standard_normal((20000, 64)).astype(np.float32) * 1e-6
+    z[::1000] = rng.standard_normal((20, 64)).astype(np.float32)
+    qz = rng.standard_normal((2, 64)).astype(np.float32)
+    idx = _build(faiss, z)
+    idx.set_option("scan_rows", 2)
+    D, I = idx.search(qz, 30)                              # only 20 rows lie outside the cluster: the 30th is inside
+    assert idx.stats()["scan_rows"] == "bf16+rerank" and _scan_fallback(idx) == 1
+    assert_knn_matches(D, I, z, qz, 30, what="bf16 scan fallback")
+    D, I = idx.search(qz, 3)                               # far from the cluster: no fallback needed
+    assert _scan_fallback(idx) == 0
+    assert_knn_matches(D, I, z, qz, 3, what="bf16 scan, same data, small k")
+
+    x = O.synth(73, 0, 20000, 128)
+    q = O.synth(74, 0, 2, 128)
+    idx = faiss.IndexFlatL2(128)
+    idx.set_option("scan_rows", 2)
+    idx.add(x[:6000])
+    D, I = idx.search(q, 8)
+    assert_knn_matches(D, I, x[:6000], q, 8, what="bf16 scan first")
+    idx.add(x[6000:])
+    near = (q[:1] + 1e-3).astype(np.float32)               # a new nearest neighbour arrives last
+    idx.add(near)
+    D, I = idx.search(q, 8)
+    assert I[0, 0] == 20000 and _scan_fallback(idx) == 0
+    assert_knn_matches(D, I, np.concatenate([x, near]), q, 8, what="bf16 scan after adds")
+    D, I = idx.search(q, 600)                              # 2k + 32 > 1024: fp32 rows
+    assert idx.stats()["scan_rows"] == "fp32"
+    assert_knn_matches(D, I, np.concatenate([x, near]), q, 600, what="large k on fp32 rows")
+
+    y = O.synth(75, 0, 3000, 36)
+    idx = _build(faiss, y)
+    idx.set_option("scan_rows", 2)
+    qy = O.synth(76, 0, 1, 36)
+    D, I = idx.search(qy, 5)
+    assert idx.stats()["scan_rows"] == "fp32"
+    assert_knn_matches(D, I, y, qy, 5, what="d % 8 != 0 on fp32 rows")
+
+
 def test_nonfinite_rows_and_queries_on_the_tensor_path(faiss):
     """inf / NaN rows are never selected and do not disturb their neighbours in the tile; a NaN
     query gets all padding (no distance is < FLT_MAX), the other queries are unaffected."""

@@ -39,7 +39,8 @@ def test_noalloc_entry_point_matches_regular_search():
     x = b200knn.synth(1234, 0, 300_000, 384, device=dev)
     ref = b200knn.IndexFlatL2(384, device=dev)
     ref.add(x)
-    ref.set_option("path", 1)            # the scan kernel: what the no-alloc entry point runs
+    ref.set_option("path", 1)            # the scan kernel: what the no-alloc entry point runs ...
+    ref.set_option("scan_rows", 1)       # ... on the fp32 rows (the handle would otherwise scan its bf16 copies and re-rank)
 
     # first call: also resolves the static array's address on this device (before any capture)
     q1 = b200knn.synth(5678, 0, 1, 384, device=dev)
