@@ -140,7 +140,11 @@ B2K_API int b2k_search_rows_noalloc(int device, const float* x_dev, int64_t n, i
  * segments with the k-th-distance bound refreshed in between; 0: one launch),
  * "tensor_epilogue_warps" (0 auto, 4, 8: warps filtering the accumulators in the screening modes),
  * "scan_rows" (what the nq < 20 scan reads: 0 auto = the bf16 copies + exact fp32 re-rank once the
- * rows exceed 128 MB, d % 8 == 0 and k <= 496; 1 = always the fp32 rows; 2 = bf16 whenever possible).
+ * rows exceed 128 MB, d % 8 == 0 and k <= 496; 1 = always the fp32 rows; 2 = bf16 whenever possible),
+ * "screen_flag_ptr" (device address of a caller-owned 32-bit word, 0 = off: batched searches then
+ * do not synchronise; they raise the word if the screening lists could not hold every candidate,
+ * and the caller must check it after its own synchronisation and repeat that search with
+ * "tensor_mode" = 1 -- the row-sharded index ships the word with its all-gather).
  * Unknown key -> B2K_EINVAL. */
 B2K_API int b2k_set_option(b2k_index* h, const char* key, int64_t value);
 

@@ -40,11 +40,16 @@ class ShardedIndexFlatL2:
             self.device = default_device() if device is None else int(device)
             self.local = IndexFlatL2(d, device=self.device)
             self._tdev = torch.device("cuda", self.device)
+            # screening-overflow word owned by this object (see b2k_set_option "screen_flag_ptr")
+            self._flag = torch.zeros(2, dtype=torch.int32, device=self._tdev)
+            self.local.set_option("screen_flag_ptr", self._flag.data_ptr())
         else:
             self.device = None
             self.local = _local
             self._tdev = torch.device("cpu")
+            self._flag = None
         self._merge = _merge
+        self._tensor_mode = 0
         self._ntotal = 0
         # segments of this rank's shard: local rows [ls, ls+cnt) are global rows [gs, gs+cnt)
         self._seg_local = []
@@ -94,6 +99,8 @@ class ShardedIndexFlatL2:
         self._seg_local, self._seg_global = [], []
 
     def set_option(self, key, value):
+        if key == "tensor_mode":
+            self._tensor_mode = int(value)
         self.local.set_option(key, value)
 
     def stats(self):
@@ -119,26 +126,47 @@ class ShardedIndexFlatL2:
         xq = torch.as_tensor(np.ascontiguousarray(x, dtype=np.float32)) if as_numpy else x
         xq = xq.to(self._tdev, torch.float32).contiguous()
         assert xq.dim() == 2 and xq.shape[1] == self._d, "search: dimension mismatch"
+        Dm, Im, redo = self._search_once(xq, k)
+        if redo:
+            # some rank's screening lists could not hold every candidate (masses of near-duplicates at
+            # the k-th distance): every rank saw the same flags, so every rank repeats with 3xTF32
+            self.local.set_option("tensor_mode", 1)
+            try:
+                Dm, Im, _ = self._search_once(xq, k)
+            finally:
+                self.local.set_option("tensor_mode", self._tensor_mode)
+        if as_numpy:
+            return torch.as_tensor(Dm).cpu().numpy(), torch.as_tensor(Im).cpu().numpy()
+        return Dm, Im
+
+    def _search_once(self, xq, k):
         nq = xq.shape[0]
         nk = nq * k
-        # packed send buffer: nk int64 ids followed by nk float32 distances (8-byte aligned)
+        # packed send buffer: nk int64 ids, nk float32 distances (8-byte aligned), one flag word
         words = nk + (nk + 1) // 2
-        send = torch.empty(words, dtype=torch.int64, device=self._tdev)
+        send = torch.empty(words + 1, dtype=torch.int64, device=self._tdev)
         I_loc = send[:nk].view(nq, k)
-        D_loc = send[nk:].view(torch.float32)[:nk].view(nq, k)
+        D_loc = send[nk:words].view(torch.float32)[:nk].view(nq, k)
+        if self._flag is not None:
+            self._flag.zero_()
+        # with the flag word installed the shard search does not synchronise: the exchange and the merge
+        # are queued behind it while it runs, and the screening check travels with the all-gather
         D, I = self.local.search(xq, k)
         D_loc.copy_(torch.as_tensor(D))
         I_loc.copy_(self._to_global(torch.as_tensor(I).to(self._tdev)))
-        recv = torch.empty(self.world * words, dtype=torch.int64, device=self._tdev)
+        if self._flag is not None:
+            send[words:].copy_(self._flag.view(torch.int64))
+        else:
+            send[words:].zero_()
+        recv = torch.empty(self.world * (words + 1), dtype=torch.int64, device=self._tdev)
         dist.all_gather_into_tensor(recv, send, group=self.group)     # the one collective of the path
-        recv = recv.view(self.world, words)
+        recv = recv.view(self.world, words + 1)
         Icat = recv[:, :nk].reshape(self.world, nq, k)
-        Dcat = recv[:, nk:].contiguous().view(torch.float32)[:, :nk].reshape(self.world, nq, k)
+        Dcat = recv[:, nk:words].contiguous().view(torch.float32)[:, :nk].reshape(self.world, nq, k)
         if self._merge is not None:
             Dm, Im = self._merge(Dcat, Icat)
         else:
             from . import merge_topk
             Dm, Im = merge_topk(Dcat, Icat)
-        if as_numpy:
-            return torch.as_tensor(Dm).cpu().numpy(), torch.as_tensor(Im).cpu().numpy()
-        return Dm, Im
+        redo = self._flag is not None and bool((recv[:, words] != 0).any().item())
+        return Dm, Im, redo

@@ -63,6 +63,7 @@ struct b2k_index {
     int opt_cta_group = 0;  // 0 = library default
     int opt_sep = 0;
     int opt_segments = 1;
+    unsigned int* opt_flag_ptr = nullptr;
     int opt_scan_rows = 0;  // nq < 20 scan: 0 auto (bf16 copies + exact re-rank for large indexes), 1 fp32 rows, 2 bf16 copies
     bool last_scan_bf = false;
     int opt_epi = 0;
@@ -389,6 +390,13 @@ int b2k_set_option(b2k_index* h, const char* key, int64_t value) {
         if (value != 0 && value != 4 && value != 8) { set_error("option tensor_epilogue_warps must be 0 (auto), 4 or 8"); return B2K_EINVAL; }
         h->opt_epi = (int)value / 4;
         if (h->k3) k3_set_epi_halves(h->k3, h->opt_epi);
+    } else if (!strcmp(key, "screen_flag_ptr")) {
+        // device address of a caller-owned 32-bit word (0 = off): batched searches then do not
+        // synchronise; they raise the word when the screening lists could not hold every candidate,
+        // and the caller must check it (after its own synchronisation) and repeat that search with
+        // tensor_mode = 1.  Used by the sharded index, which ships the word with its all-gather.
+        h->opt_flag_ptr = reinterpret_cast<unsigned int*>(static_cast<uintptr_t>(value));
+        if (h->k3) k3_set_ext_flag(h->k3, h->opt_flag_ptr);
     } else if (!strcmp(key, "scan_rows")) {
         if (value < 0 || value > 2) { set_error("option scan_rows must be 0 (auto), 1 (fp32 rows) or 2 (bf16 copies + exact re-rank)"); return B2K_EINVAL; }
         h->opt_scan_rows = (int)value;
@@ -591,6 +599,7 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
             if (!rc) k3_set_sep_mode(h->k3, h->opt_sep);
             if (!rc) k3_set_segments(h->k3, h->opt_segments);
             if (!rc) k3_set_epi_halves(h->k3, h->opt_epi);
+            if (!rc) k3_set_ext_flag(h->k3, h->opt_flag_ptr);
         }
         if (!rc) h->last_path = 2;
         // like faiss (query blocks of 4096), long batches go through in chunks: the candidate-list

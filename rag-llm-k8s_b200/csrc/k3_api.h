@@ -29,6 +29,9 @@ void k3_set_cta_group(K3State* s, int cg);
 void k3_set_sep_mode(K3State* s, int m);     // separate accumulator for the small cross terms: 0 auto, 1 on, 2 off  // 1 = one CTA per tile, 2 = CTA pairs (cta_group::2)
 void k3_set_segments(K3State* s, int on);   // main pass in segments with bound refreshes in between (default on)
 void k3_set_epi_halves(K3State* s, int nh); // epilogue warps: 0 auto, 1 four (one per scheduler), 2 eight
+// flag != null: the screening modes raise *flag (device word, never reset by the library) instead of
+// synchronising and reporting through *overflowed; the caller checks it and repeats the search with mode 1
+void k3_set_ext_flag(K3State* s, unsigned int* flag);
 int k3_last_kernel_ms(K3State* s, float* ms);
 int k3_last_mode(const K3State* s);  // 1 = 3xTF32, 2 = TF32 screening + exact re-rank, 3 = bf16 screening + exact re-rank
 

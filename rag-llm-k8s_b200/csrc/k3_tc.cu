@@ -863,6 +863,7 @@ struct K3State {
     int last_mode = 0;  // 1 = 3xTF32, 2 = TF32 screening + re-rank, 3 = bf16 screening + re-rank (what the last search ran)
     int sep_mode = 0;  // long-row accuracy: 0 auto (d >= 512: separate accumulator), 1 separate accumulator, 2 off
     bool timed = false;
+    unsigned int* ext_flag = nullptr;  // caller-owned overflow word (deferred screening check)
     int epi_halves = 0;  // 0 auto (2 where available), 1 four epilogue warps, 2 eight
     int segments = 1;  // cut the main pass into segments with a bound refresh in between (0 = one launch)
 };
@@ -966,6 +967,7 @@ void k3_set_cta_group(K3State* s, int cg) { s->cg = (cg == 1 || cg == 2) ? cg : 
 void k3_set_sep_mode(K3State* s, int m) { s->sep_mode = m; }
 void k3_set_segments(K3State* s, int on) { s->segments = on; }
 void k3_set_epi_halves(K3State* s, int nh) { s->epi_halves = nh; }
+void k3_set_ext_flag(K3State* s, unsigned int* flag) { s->ext_flag = flag; }
 int k3_last_mode(const K3State* s) { return s->last_mode; }
 
 int k3_last_kernel_ms(K3State* s, float* ms) {
@@ -1068,7 +1070,8 @@ int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, con
     p.kth = reinterpret_cast<u64*>(scratch + L.off_kth);
     p.cand = reinterpret_cast<u64*>(scratch + L.off_cand);
     p.next_unit = reinterpret_cast<u64*>(scratch + L.off_next);
-    p.overflow = reinterpret_cast<unsigned int*>(scratch + L.off_next + 16);
+    // ext_flag (caller-owned device word, never reset here): the screening check is left to the caller and the call does not synchronise
+    p.overflow = s->ext_flag ? s->ext_flag : reinterpret_cast<unsigned int*>(scratch + L.off_next + 16);
     p.slack2 = reinterpret_cast<float*>(scratch + L.off_slack);
     p.static_mode = 0;
     p.static_tpc = 1;
@@ -1095,7 +1098,8 @@ int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, con
     }
     const int64_t nslots = (int64_t)L.ncta * L.qpc;
     const int64_t ninit = nslots > nq ? nslots : nq;
-    k3_init_kernel<<<(unsigned)((ninit + 255) / 256), 256, 0, st>>>(nslots, p.cnt, p.tau, p.kth, nq, p.gts, p.next_unit, p.overflow);
+    k3_init_kernel<<<(unsigned)((ninit + 255) / 256), 256, 0, st>>>(nslots, p.cnt, p.tau, p.kth, nq, p.gts, p.next_unit,
+                                                                    s->ext_flag ? nullptr : p.overflow);
     count_launch();
     B2K_CUDA(cudaGetLastError());
 
@@ -1196,6 +1200,7 @@ int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, con
     B2K_CUDA(cudaGetLastError());
     // a list or the re-rank buffer could not hold every row inside the slack (masses of near-
     // duplicates around the k-th neighbour): the caller repeats the search in the exact mode
+    if (s->ext_flag) return B2K_OK;
     B2K_CUDA(cudaMemcpyAsync(s->flag_host, p.overflow, sizeof(unsigned int), cudaMemcpyDeviceToHost, st));
     B2K_CUDA(cudaStreamSynchronize(st));
     if (overflowed) *overflowed = (int)*s->flag_host;

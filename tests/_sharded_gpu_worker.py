@@ -37,6 +37,27 @@ def main():
     q = O.synth(5678, 0, 40, d)
     D, I = idx.search(q, 10)
     assert_knn_matches(D, I, xs, q, 10, expanded=True, what="sharded synthetic")
+    # screening overflow on ONE shard only (near-duplicates all land on the last rank): the flag
+    # travels with the all-gather, every rank repeats the search in 3xTF32 mode, results stay exact
+    idx.reset()
+    rng = np.random.default_rng(0)
+    base = rng.standard_normal((1, 64)).astype(np.float32)
+    per = 20000
+    z = rng.standard_normal((per * world, 64)).astype(np.float32)
+    z[per * (world - 1):] = base + rng.standard_normal((per, 64)).astype(np.float32) * 1e-6
+    z[per * (world - 1)::1000] = rng.standard_normal((20, 64)).astype(np.float32)
+    idx2 = ShardedIndexFlatL2(64, device=lr)
+    idx2.add(z)
+    qz = (base + rng.standard_normal((30, 64)).astype(np.float32) * 0.05).astype(np.float32)
+    D, I = idx2.search(qz, 10)
+    assert_knn_matches(D, I, z, qz, 10, expanded=True, what="sharded overflow redo rank=%d" % rank)
+    st = idx2.stats()
+    if rank == world - 1:
+        assert st["tensor_mode"] == "3xtf32", st
+    idx.add_synthetic_global(200000, 1234)               # the first index again: screening mode, no redo
+    D2, I2 = idx.search(q, 10)
+    assert idx.stats()["tensor_mode"] == "bf16screen+rerank"
+    assert_knn_matches(D2, I2, xs, q, 10, expanded=True, what="sharded synthetic again")
     dist.barrier()
     if rank == 0:
         print("SHARDED-GPU-OK world=%d" % world)
