@@ -136,7 +136,8 @@ B2K_API int b2k_search_rows_noalloc(int device, const float* x_dev, int64_t n, i
  * "tensor_sep_accum" (0 auto, 1 on, 2 off), "tensor_mode" (0 auto = 3 where it applies, else 2; 1 = 3xTF32 products,
  * 2 = one TF32 product as a screen + exact fp32 re-rank of the rows inside its error slack,
  * 3 = the same screen on bf16 copies of the rows (kept next to the fp32 rows, +50% memory;
- * needs d % 8 == 0, else 2 serves)), "tensor_segments" (1 default: the main pass runs in
+ * needs d % 8 == 0, else 2 serves), 4 = the 3xTF32 product used as the screen (what 2 and 3 fall
+ * back to when their slack zone overflows; if that overflows too, the exact scan kernel answers)), "tensor_segments" (1 default: the main pass runs in
  * segments with the k-th-distance bound refreshed in between; 0: one launch),
  * "tensor_epilogue_warps" (0 auto, 4, 8: warps filtering the accumulators in the screening modes),
  * "scan_rows" (what the nq < 20 scan reads: 0 auto = the bf16 copies + exact fp32 re-rank once the
@@ -151,8 +152,8 @@ B2K_API int b2k_set_option(b2k_index* h, const char* key, int64_t value);
 /* Read-back of measurements / state.  Keys: "last_path" (1 = scan kernel, 2 = tensor-core
  * kernel served the last search), "tensor_kernel_ms" (CUDA-event duration of the last
  * tensor-core main kernel; needs option "timing" = 1; synchronises on that kernel),
- * "tensor_mode_used" (1 / 2 / 3), "screen_fallbacks" (searches repeated in 3xTF32 mode because the
- * slack zone overflowed), "scan_kernel_ms" / "scan_launches" (the same for the scan kernel launches of the last
+ * "tensor_mode_used" (1 / 2 / 3 / 4), "screen_fallbacks" (query chunks repeated with a narrower screen, or by the scan kernel,
+ * because the slack zone overflowed), "scan_kernel_ms" / "scan_launches" (the same for the scan kernel launches of the last
  * scan-path search), "scan_rows_used" (1 fp32 rows / 2 bf16 copies + re-rank), "scan_fallback"
  * (1 if the last bf16 scan was redone on the fp32 rows; synchronises the device). */
 B2K_API int b2k_get_stat(b2k_index* h, const char* key, double* out);

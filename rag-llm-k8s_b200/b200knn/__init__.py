@@ -167,8 +167,10 @@ class IndexFlatL2:
             out["path"] = {1: "scan", 2: "tensor"}.get(int(v.value))
         if out["path"] == "tensor" and L.b2k_get_stat(self._h, b"tensor_kernel_ms", C.byref(v)) == 0:
             out["main_kernel_ms"] = v.value
+        if L.b2k_get_stat(self._h, b"screen_fallbacks", C.byref(v)) == 0:
+            out["screen_fallbacks"] = int(v.value)
         if out["path"] == "tensor" and L.b2k_get_stat(self._h, b"tensor_mode_used", C.byref(v)) == 0:
-            out["tensor_mode"] = {1: "3xtf32", 2: "screen+rerank", 3: "bf16screen+rerank"}.get(int(v.value))
+            out["tensor_mode"] = {1: "3xtf32", 2: "screen+rerank", 3: "bf16screen+rerank", 4: "3xtf32screen+rerank"}.get(int(v.value))
             L.b2k_get_stat(self._h, b"screen_fallbacks", C.byref(v))
             out["screen_fallbacks"] = int(v.value)
         if out["path"] == "scan" and L.b2k_get_stat(self._h, b"scan_kernel_ms", C.byref(v)) == 0:

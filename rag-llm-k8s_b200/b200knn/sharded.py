@@ -50,6 +50,7 @@ class ShardedIndexFlatL2:
             self._flag = None
         self._merge = _merge
         self._tensor_mode = 0
+        self._path = 0
         self._ntotal = 0
         # segments of this rank's shard: local rows [ls, ls+cnt) are global rows [gs, gs+cnt)
         self._seg_local = []
@@ -101,6 +102,8 @@ class ShardedIndexFlatL2:
     def set_option(self, key, value):
         if key == "tensor_mode":
             self._tensor_mode = int(value)
+        if key == "path":
+            self._path = int(value)
         self.local.set_option(key, value)
 
     def stats(self):
@@ -127,14 +130,17 @@ class ShardedIndexFlatL2:
         xq = xq.to(self._tdev, torch.float32).contiguous()
         assert xq.dim() == 2 and xq.shape[1] == self._d, "search: dimension mismatch"
         Dm, Im, redo = self._search_once(xq, k)
-        if redo:
-            # some rank's screening lists could not hold every candidate (masses of near-duplicates at
-            # the k-th distance): every rank saw the same flags, so every rank repeats with 3xTF32
-            self.local.set_option("tensor_mode", 1)
+        # some rank's screening lists could not hold every candidate (masses of near-duplicates at the
+        # k-th distance, norms that dwarf the distances): every rank saw the same flags, so every rank
+        # repeats -- first with the 3xTF32 product as the screen, then with the exact scan kernel
+        for key, val, back in (("tensor_mode", 4, self._tensor_mode), ("path", 1, self._path)):
+            if not redo:
+                break
+            self.local.set_option(key, val)
             try:
-                Dm, Im, _ = self._search_once(xq, k)
+                Dm, Im, redo = self._search_once(xq, k)
             finally:
-                self.local.set_option("tensor_mode", self._tensor_mode)
+                self.local.set_option(key, back)
         if as_numpy:
             return torch.as_tensor(Dm).cpu().numpy(), torch.as_tensor(Im).cpu().numpy()
         return Dm, Im

@@ -67,7 +67,7 @@ struct b2k_index {
     int opt_scan_rows = 0;  // nq < 20 scan: 0 auto (bf16 copies + exact re-rank for large indexes), 1 fp32 rows, 2 bf16 copies
     bool last_scan_bf = false;
     int opt_epi = 0;
-    int opt_tensor_mode = 0;  // 0 auto (bf16 screening + exact re-rank where d % 8 == 0 and memory allows, else TF32 screening), 1 3xTF32, 2 TF32 screening, 3 bf16 screening
+    int opt_tensor_mode = 0;  // 0 auto (bf16 screening + exact re-rank where d % 8 == 0 and memory allows, else TF32 screening), 1 3xTF32, 2 TF32 screening, 3 bf16 screening, 4 3xTF32 screening
     int64_t stat_screen_fallbacks = 0;
     int last_path = 0;
     int sticky = 0;
@@ -380,7 +380,7 @@ int b2k_set_option(b2k_index* h, const char* key, int64_t value) {
         h->opt_sep = (int)value;
         if (h->k3) k3_set_sep_mode(h->k3, h->opt_sep);
     } else if (!strcmp(key, "tensor_mode")) {
-        if (value < 0 || value > 3) { set_error("option tensor_mode must be 0 (auto), 1 (3xTF32), 2 (TF32 screening + exact re-rank) or 3 (bf16 screening + exact re-rank)"); return B2K_EINVAL; }
+        if (value < 0 || value > 4) { set_error("option tensor_mode must be 0 (auto), 1 (3xTF32), 2 (TF32 screening), 3 (bf16 screening) or 4 (3xTF32 screening); 2-4 end in the exact re-rank"); return B2K_EINVAL; }
         h->opt_tensor_mode = (int)value;
     } else if (!strcmp(key, "tensor_segments")) {
         if (value < 0 || value > 100000) { set_error("option tensor_segments must be 0 (one launch), 1 (segments with bound refreshes) or a target number of keys per query and segment"); return B2K_EINVAL; }
@@ -561,7 +561,11 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
     size_t io_bytes = on_device ? 0 : q_bytes + d_bytes + i_bytes;
     size_t scratch = 0;
     if (h->ntotal > 0) {
-        if (want_tc) scratch = k3_scratch_bytes(h->sm_count, h->d, nq < TC_QUERY_CHUNK ? nq : TC_QUERY_CHUNK, kk);
+        if (want_tc) {
+            scratch = k3_scratch_bytes(h->sm_count, h->d, nq < TC_QUERY_CHUNK ? nq : TC_QUERY_CHUNK, kk);
+            const size_t sb = scan_ws_bytes(h, nq, kk, false);  // last line of defence of the screening modes
+            if (sb > scratch) scratch = sb;
+        }
         else scratch = scan_ws_bytes(h, nq, kk, scan_wants_bf(h, kk));
     }
     int rc = ensure_ws(h, io_bytes + align256(scratch));
@@ -586,12 +590,13 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
     if (h->ntotal == 0) {
         rc = launch_fill_empty(Dd, Id, nq * kk, st);
     } else if (want_tc) {
-        // 1 = 3xTF32, 2 = TF32 screening, 3 = bf16 screening (rows need a 16-byte bf16 pitch; if the bf16
-        // copies do not fit in memory the TF32 screening serves instead)
+        // 1 = 3xTF32 (faiss-like expansion numerics), 2 = TF32 screening, 3 = bf16 screening (rows need a
+        // 16-byte bf16 pitch; if the bf16 copies do not fit in memory the TF32 screening serves
+        // instead), 4 = 3xTF32 as a screen.  2, 3 and 4 end in the exact fp32 re-rank.
         int mode = h->opt_tensor_mode == 0 ? 3 : h->opt_tensor_mode;
         if (mode == 3 && (h->d % 8 != 0 || h->bf_nomem)) mode = 2;
         if (mode == 3 && enable_bf(h, st) != B2K_OK) mode = 2;
-        if (mode == 1) rc = enable_lo(h, st);
+        if (mode == 1 || mode == 4) rc = enable_lo(h, st);
         if (!rc && !h->k3) {
             rc = k3_create(&h->k3, h->device, h->sm_count);
             if (!rc) k3_set_timing(h->k3, h->opt_timing != 0);
@@ -606,16 +611,24 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
         // scratch is sized per chunk and one pass over the rows per chunk is still compute-bound
         for (int64_t q0 = 0; q0 < nq && !rc; q0 += TC_QUERY_CHUNK) {
             const int64_t nqc = nq - q0 < TC_QUERY_CHUNK ? nq - q0 : TC_QUERY_CHUNK;
+            const float* qc = qd + q0 * (int64_t)h->d;
             int overflowed = 0;
             rc = k3_search(h->k3, h->x, h->xlo, h->xbf, h->norms, h->done + MAX_NORM_SLOT, h->done + MAX_ERR_SLOT, h->ntotal,
-                           h->d, qd + q0 * (int64_t)h->d, nqc, kk, Dd + q0 * kk, Id + q0 * kk, ws_tail, st, mode, &overflowed);
-            if (!rc && overflowed) {
-                // masses of near-duplicates around the k-th neighbour: repeat this chunk with 3xTF32
+                           h->d, qc, nqc, kk, Dd + q0 * kk, Id + q0 * kk, ws_tail, st, mode, &overflowed);
+            if (!rc && overflowed && mode != 4) {
+                // the slack zone of the cheap screen did not fit its lists (masses of near-duplicates around
+                // the k-th neighbour, or a distribution whose norms dwarf its distances): repeat this chunk
+                // with the 3xTF32 product as the screen, whose zone is ~10^4 times narrower
                 ++h->stat_screen_fallbacks;
                 rc = enable_lo(h, st);
                 if (!rc) rc = k3_search(h->k3, h->x, h->xlo, h->xbf, h->norms, h->done + MAX_NORM_SLOT, h->done + MAX_ERR_SLOT,
-                                        h->ntotal, h->d, qd + q0 * (int64_t)h->d, nqc, kk, Dd + q0 * kk, Id + q0 * kk, ws_tail,
-                                        st, 1, nullptr);
+                                        h->ntotal, h->d, qc, nqc, kk, Dd + q0 * kk, Id + q0 * kk, ws_tail, st, 4, &overflowed);
+            }
+            if (!rc && overflowed) {
+                // even that zone is crowded (exact duplicates by the thousand): the scan kernel is exact whatever the data
+                ++h->stat_screen_fallbacks;
+                h->last_path = 1;
+                rc = scan_search(h, nqc, qc, kk, Dd + q0 * kk, Id + q0 * kk, ws_tail, st, false);
             }
         }
     } else {

@@ -79,7 +79,7 @@ template <int CG, int NS, int MODE>
 struct K3Smem {
     static constexpr int B_ROWS = K3_BN / CG;
     static constexpr int B_BYTES = B_ROWS * K3_BK * 4;
-    static constexpr int NPART = (MODE == 2 || MODE == 3) ? 1 : 2;  // one operand pair (screening), or hi + lo (3xTF32)
+    static constexpr int NPART = (MODE == 2 || MODE == 3) ? 1 : 2;  // one operand pair (one-product screening), or hi + lo (3xTF32)
     static constexpr int OFF_B = NPART * K3_A_BYTES;  // stage = [Q_hi][Q_lo?][X_hi][X_lo?]
     static constexpr int STAGE_BYTES = NPART * (K3_A_BYTES + B_BYTES);
     static constexpr int OFF_XN = NS * STAGE_BYTES;            // float[2][256]
@@ -200,8 +200,12 @@ __global__ void __launch_bounds__(k3_threads(NH), 1)
 k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_ql,
                       const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_xl,
                       const K3Params p) {
-    constexpr bool SEP = (MODE == 1);  // separate accumulator for the cross terms
-    constexpr bool SCREEN = (MODE == 2 || MODE == 3);  // one product + error slack; exact distances come from the re-rank kernel
+    // MODE: 0 3xTF32, one accumulator | 1 3xTF32, separate cross-term accumulator | 2 one TF32 product, screening
+    //       3 one bf16 product, screening | 4 3xTF32 (as 1) used as a screen: second line of defence when the
+    //       slack zone of 2 / 3 overflows (its error is ~2^-21, so its slack zone is ~10^4 times narrower)
+    constexpr bool SEP = (MODE == 1 || MODE == 4);  // separate accumulator for the cross terms
+    constexpr bool ONEP = (MODE == 2 || MODE == 3);  // one product per k-step: no residual operands
+    constexpr bool SCREEN = (ONEP || MODE == 4);     // keep everything within the error slack; exact distances come from the re-rank kernel
     constexpr bool BF16 = (MODE == 3);                  // the screening product runs on bf16 copies of the rows (kind::f16)
     constexpr int BKE = BF16 ? 64 : 32;                 // elements per k-chunk: one 128-byte swizzle row either way
     using L = K3Smem<CG, NS, MODE>;
@@ -297,16 +301,16 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
                     if (CG == 1) {
                         ptx::mbar_arrive_expect_tx(&full[stage], L::STAGE_BYTES);
                         ptx::tma_load_2d(sb, &tm_q, &full[stage], kc * BKE, qrow0);
-                        if (!SCREEN) ptx::tma_load_2d(sb + K3_A_BYTES, &tm_ql, &full[stage], kc * BKE, qrow0);
+                        if (!ONEP) ptx::tma_load_2d(sb + K3_A_BYTES, &tm_ql, &full[stage], kc * BKE, qrow0);
                         ptx::tma_load_2d(sb + L::OFF_B, &tm_x, &full[stage], kc * BKE, (int)xrow0);
-                        if (!SCREEN) ptx::tma_load_2d(sb + L::OFF_B + L::B_BYTES, &tm_xl, &full[stage], kc * BKE, (int)xrow0);
+                        if (!ONEP) ptx::tma_load_2d(sb + L::OFF_B + L::B_BYTES, &tm_xl, &full[stage], kc * BKE, (int)xrow0);
                     } else {
                         if (rank == 0) ptx::mbar_arrive_expect_tx(&full[stage], 2 * L::STAGE_BYTES);
                         else ptx::mbar_arrive_cluster(&full[stage], 0);
                         ptx::tma_load_2d_pair(sb, &tm_q, &full[stage], kc * BKE, qrow0);
-                        if (!SCREEN) ptx::tma_load_2d_pair(sb + K3_A_BYTES, &tm_ql, &full[stage], kc * BKE, qrow0);
+                        if (!ONEP) ptx::tma_load_2d_pair(sb + K3_A_BYTES, &tm_ql, &full[stage], kc * BKE, qrow0);
                         ptx::tma_load_2d_pair(sb + L::OFF_B, &tm_x, &full[stage], kc * BKE, (int)xrow0);
-                        if (!SCREEN) ptx::tma_load_2d_pair(sb + L::OFF_B + L::B_BYTES, &tm_xl, &full[stage], kc * BKE, (int)xrow0);
+                        if (!ONEP) ptx::tma_load_2d_pair(sb + L::OFF_B + L::B_BYTES, &tm_xl, &full[stage], kc * BKE, (int)xrow0);
                     }
                     if (++stage == NS) { stage = 0; phase ^= 1; }
                 }
@@ -340,7 +344,7 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
                             const uint64_t off = (uint64_t)(ks * 32 >> 4);  // 8 fp32 = 32 bytes along K
                             if constexpr (BF16) {
                                 ptx::mma_bf16<CG>(d_tmem, a_hi + off, b_hi + off, idesc, (kc | ks) != 0);  // 16 bf16 = 32 bytes along K
-                            } else if constexpr (SCREEN) {
+                            } else if constexpr (ONEP) {
                                 ptx::mma_tf32<CG>(d_tmem, a_hi + off, b_hi + off, idesc, (kc | ks) != 0);
                             } else {
                                 ptx::mma_tf32<CG>(d_corr, a_lo + off, b_hi + off, idesc, (kc | ks) != 0);  // small terms first
@@ -1025,6 +1029,7 @@ static int launch_k3_any(int cg, int P, int mode, int nh, const CUtensorMap& mq,
     switch (mode) {
         B2K_K3_CASE(0)
         B2K_K3_CASE(1)
+        B2K_K3_CASE(4)
     }
 #undef B2K_K3_CASE
     // screening (2 = TF32, 3 = bf16): one operand pair per stage (32 KB per CTA, or 48 KB without a
@@ -1051,12 +1056,14 @@ int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, con
               const unsigned int* max_norm_bits, const unsigned int* max_err_bits, int64_t n, int d, const float* q,
               int64_t nq, int k, float* D, int64_t* I, unsigned char* scratch, cudaStream_t st, int mode,
               int* overflowed) {
-    const bool screen = mode != 1;
+    const bool screen = mode != 1;            // modes 2, 3, 4: slack lists + exact re-rank
+    const bool onep = mode == 2 || mode == 3;  // one product per k-step (no residual operands)
     const bool bf16 = mode == 3;
+    if (mode < 1 || mode > 4) { set_error("tensor kernel: bad mode %d", mode); return B2K_EINVAL; }
     if (bf16 && (d % 8 != 0 || !xbf || !max_err_bits)) { set_error("tensor kernel: bf16 screening needs d %% 8 == 0 and the bf16 rows"); return B2K_EINVAL; }
     if (overflowed) *overflowed = 0;
     s->last_mode = mode;
-    K3Layout L = k3_layout(s->sm_count, d, nq, k, s->cg, screen, n);
+    K3Layout L = k3_layout(s->sm_count, d, nq, k, s->cg, onep, n);
     float* qlo = reinterpret_cast<float*>(scratch + L.off_qlo);  // 3xTF32: residual rows; bf16 screening: bf16 queries
     K3Params p;
     p.n = n; p.d = d; p.nq = nq; p.k = k; p.P = L.P; p.nqb = L.nqb; p.qpc = L.qpc;
@@ -1080,7 +1087,7 @@ int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, con
     p.tile_cols = K3_BN;
 
     // queries: norms (+ TF32 residual rows for the exact mode; K1 reused), screening slack, list state reset
-    int rc = launch_row_prep(q, nq, d, const_cast<float*>(p.qn), screen ? nullptr : qlo, nullptr, st);
+    int rc = launch_row_prep(q, nq, d, const_cast<float*>(p.qn), onep ? nullptr : qlo, nullptr, st);
     if (rc) return rc;
     if (bf16) {
         rc = launch_row_bf16(q, nq, d, qlo, const_cast<float*>(p.slack2), nullptr, st);
@@ -1088,6 +1095,15 @@ int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, con
         const float acc_coef = 8e-6f * (float)d / 256.f;
         k3_slack_bf16_kernel<<<(unsigned)((nq + 255) / 256), 256, 0, st>>>(nq, p.qn, max_norm_bits, max_err_bits, acc_coef,
                                                                            const_cast<float*>(p.slack2));
+        count_launch();
+        B2K_CUDA(cudaGetLastError());
+    } else if (mode == 4) {
+        // 3xTF32 as a screen: the dropped lo*lo term is <= 2^-22 |q||x| and every accumulate truncates
+        // (<= 1 ulp of a partial sum <= |q||x|; d/8 accumulates into the main accumulator, 2d/8 small
+        // ones into the cross-term accumulator): |q.x - acc| <= (2^-22 + (3d/8 + 8) 2^-23) |q||x|, twice
+        // that on the distance, and the slack is twice sigma
+        const float coef = 2.f * 2.f * (2.4e-7f + ((float)d * 0.375f + 8.f) * 1.2e-7f);  // 3 ulp per accumulate for margin
+        k3_slack_kernel<<<(unsigned)((nq + 255) / 256), 256, 0, st>>>(nq, p.qn, max_norm_bits, coef, const_cast<float*>(p.slack2));
         count_launch();
         B2K_CUDA(cudaGetLastError());
     } else if (screen) {
@@ -1112,9 +1128,9 @@ int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, con
         mxl = mx;
     } else {
         if ((rc = make_map(s, &mq, q, nq, d, K3_BM))) return rc;
-        if ((rc = make_map(s, &mql, screen ? q : qlo, nq, d, K3_BM))) return rc;
+        if ((rc = make_map(s, &mql, onep ? q : qlo, nq, d, K3_BM))) return rc;
         if ((rc = make_map(s, &mx, x, n, d, K3_BN / L.cg))) return rc;
-        if ((rc = make_map(s, &mxl, screen ? x : xlo, n, d, K3_BN / L.cg))) return rc;
+        if ((rc = make_map(s, &mxl, onep ? x : xlo, n, d, K3_BN / L.cg))) return rc;
     }
 
     // Warm start: the first 64 rows of one tile per CTA (pair) with open thresholds -- every key is
@@ -1123,7 +1139,7 @@ int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, con
     const int nclusters = L.ncta / L.cg;
     // kernel mode: 0 3xTF32 in one accumulator (double-buffered), 1 3xTF32 with a separate cross-term
     // accumulator, 2 TF32 screening, 3 bf16 screening (one product; exact distances from the re-rank kernel)
-    const int sep = bf16 ? 3 : screen ? 2 : (s->sep_mode == 1 || (s->sep_mode == 0 && d >= 512)) ? 1 : 0;
+    const int sep = bf16 ? 3 : mode == 2 ? 2 : mode == 4 ? 4 : (s->sep_mode == 1 || (s->sep_mode == 0 && d >= 512)) ? 1 : 0;
     const int nh = s->epi_halves == 1 ? 1 : 2;  // eight epilogue warps where instantiated (screening modes)
     const int cols_a = 64;
     int64_t warm_rows = 0;  // rows behind the bound the main pass starts with

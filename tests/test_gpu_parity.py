@@ -296,10 +296,11 @@ def test_one_million_rows_nq1_k10(faiss):
 
 @pytest.mark.parametrize("mode,cg,sep,k", [(1, 1, 2, 10), (1, 1, 1, 10), (1, 2, 2, 100), (1, 2, 1, 100), (1, 2, 2, 700),
                                            (1, 2, 1, 1024), (2, 1, 0, 10), (2, 1, 0, 700), (2, 2, 0, 100), (2, 2, 0, 1024),
-                                           (3, 1, 0, 10), (3, 1, 0, 100), (3, 1, 0, 700), (3, 1, 0, 1024)])
+                                           (3, 1, 0, 10), (3, 1, 0, 100), (3, 1, 0, 700), (3, 1, 0, 1024),
+                                           (3, 2, 0, 100), (4, 1, 0, 10), (4, 2, 0, 100), (4, 2, 0, 700)])
 def test_tensor_kernel_variants(faiss, mode, cg, sep, k):
     """Every instantiation of the tcgen05 kernel -- 3xTF32 (one CTA / CTA pair, shared / separate
-    cross-term accumulator, short / long lists) and TF32 / bf16 screening + exact re-rank -- against the
+    cross-term accumulator, short / long lists) and TF32 / bf16 / 3xTF32 screening + exact re-rank -- against the
     oracle's expansion numerics, on N(0,1) rows and on unit-norm rows with planted duplicates (the
     rag.py distribution)."""
     rng = np.random.default_rng(cg * 10 + sep)
@@ -316,7 +317,7 @@ def test_tensor_kernel_variants(faiss, mode, cg, sep, k):
         idx.set_option("tensor_sep_accum", sep)
         D, I = idx.search(q, k)
         st = idx.stats()
-        assert st["path"] == "tensor" and st["tensor_mode"] == {1: "3xtf32", 2: "screen+rerank", 3: "bf16screen+rerank"}[mode]
+        assert st["path"] == "tensor" and st["tensor_mode"] == {1: "3xtf32", 2: "screen+rerank", 3: "bf16screen+rerank", 4: "3xtf32screen+rerank"}[mode]
         assert np.all(D >= 0.0)
         if mode >= 2 and unit:
             assert np.all(D[:8, 0] == 0.0)                # exact re-rank: a stored query is at distance exactly 0
@@ -326,7 +327,8 @@ def test_tensor_kernel_variants(faiss, mode, cg, sep, k):
 def test_screening_falls_back_when_the_slack_zone_overflows(faiss):
     """Screening keeps every row whose approximate distance is within the error slack of the k-th;
     thousands of rows at (almost) the same distance do not fit its lists, and the search must then
-    repeat itself in the 3xTF32 mode instead of dropping candidates."""
+    repeat itself with a narrower screen (3xTF32 + re-rank) and, if that zone is crowded too, with the
+    exact scan kernel, instead of dropping candidates."""
     rng = np.random.default_rng(0)
     base = rng.standard_normal((1, 64)).astype(np.float32)
     x = np.repeat(base, 20000, 0) + rng.standard_normal((20000, 64)).astype(np.float32) * 1e-6   # near-duplicates
@@ -335,7 +337,8 @@ def test_screening_falls_back_when_the_slack_zone_overflows(faiss):
     idx = _build(faiss, x)
     D, I = idx.search(q, 10)
     st = idx.stats()
-    assert st["path"] == "tensor" and st["screen_fallbacks"] >= 1 and st["tensor_mode"] == "3xtf32"
+    # 20000 rows within 1e-6 of each other crowd even the 3xTF32 screen's zone: the scan kernel answers
+    assert st["screen_fallbacks"] >= 1 and (st["path"] == "scan" or st.get("tensor_mode") == "3xtf32screen+rerank")
     assert_knn_matches(D, I, x, q, 10, expanded=True, what="overflow fallback")
 
 
@@ -570,7 +573,7 @@ def test_bf16_screening_incremental_adds_and_fallbacks(faiss):
     idx.set_option("tensor_mode", 3)
     D, I = idx.search(qz, 10)
     st = idx.stats()
-    assert st["screen_fallbacks"] >= 1 and st["tensor_mode"] == "3xtf32"
+    assert st["screen_fallbacks"] >= 1 and (st["path"] == "scan" or st.get("tensor_mode") == "3xtf32screen+rerank")
     assert_knn_matches(D, I, z, qz, 10, expanded=True, what="bf16 overflow fallback")
 
 
@@ -657,6 +660,32 @@ def test_scan_over_bf16_copies_falls_back_and_follows_adds(faiss):
     assert_knn_matches(D, I, y, qy, 5, what="d % 8 != 0 on fp32 rows")
 
 
+def test_screening_chain_stays_exact_when_norms_dwarf_distances(faiss):
+    """Rows 100 + N(0,1): squared norms ~1.3e6 against squared distances ~250.  The slack of the bf16
+    screen (proportional to |q||x|) swallows the whole database, so the search must climb down its
+    chain -- 3xTF32 as a screen with the exact re-rank, else the scan kernel -- and still return the
+    true neighbours with their direct-difference distances (the plain 3xTF32 expansion is off by
+    ~1 % here, as faiss's own sgemm path would be).  Checked against the float64 ground truth."""
+    rng = np.random.default_rng(11)
+    n, d, nq, k = 60000, 128, 32, 20
+    x = (rng.standard_normal((n, d)) + 100.0).astype(np.float32)
+    q = (rng.standard_normal((nq, d)) + 100.0).astype(np.float32)
+    idx = _build(faiss, x)
+    D, I = idx.search(q, k)
+    st = idx.stats()
+    assert st["screen_fallbacks"] >= 1
+    Dt, It = O.truth_f64(x, q, k)
+    dd = O.dist_f64(x, q, I)
+    assert np.all(dd <= Dt[:, k - 1:k] * (1 + 4e-6)), "a returned row is farther than the true k-th neighbour"
+    assert np.abs(D.astype(np.float64) - dd).max() <= 4e-6 * dd.max()
+    assert all(len(set(r.tolist())) == k for r in I)
+    idx.set_option("tensor_mode", 4)                       # the second link of the chain on its own
+    D4, I4 = idx.search(q, k)
+    assert idx.stats().get("tensor_mode") == "3xtf32screen+rerank" or idx.stats()["path"] == "scan"
+    dd4 = O.dist_f64(x, q, I4)
+    assert np.all(dd4 <= Dt[:, k - 1:k] * (1 + 4e-6))
+
+
 def test_nonfinite_rows_and_queries_on_the_tensor_path(faiss):
     """inf / NaN rows are never selected and do not disturb their neighbours in the tile; a NaN
     query gets all padding (no distance is < FLT_MAX), the other queries are unaffected."""
@@ -666,7 +695,7 @@ def test_nonfinite_rows_and_queries_on_the_tensor_path(faiss):
     x[300] = np.inf
     q = O.synth(52, 0, 24, 64)
     q[7, 1] = np.nan
-    for mode in (2, 1, 3):
+    for mode in (2, 1, 3, 4):
         idx = _build(faiss, x)
         idx.set_option("tensor_mode", mode)
         D, I = idx.search(q, 8)
