@@ -69,6 +69,8 @@ struct b2k_index {
     int opt_epi = 0;
     int opt_tensor_mode = 0;  // 0 auto (bf16 screening + exact re-rank where d % 8 == 0 and memory allows, else TF32 screening), 1 3xTF32, 2 TF32 screening, 3 bf16 screening, 4 3xTF32 screening
     int64_t stat_screen_fallbacks = 0;
+    int screen_fail_streak = 0;      // consecutive searches whose cheap screen overflowed
+    unsigned int screen_skipped = 0;  // searches that started at the 3xTF32 screen because of that
     int last_path = 0;
     int sticky = 0;
     K3State* k3 = nullptr;
@@ -463,6 +465,7 @@ int b2k_reset(b2k_index* h) {
     h->x = h->norms = h->xlo = nullptr;
     h->xbf = nullptr;
     h->bf_nomem = false;
+    h->screen_fail_streak = 0;
     h->ntotal = h->capacity = 0;
     if (h->k3) k3_invalidate_maps(h->k3);
     B2K_CUDA(cudaMemset(h->done, 0, 256));
@@ -595,8 +598,13 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
         // instead), 4 = 3xTF32 as a screen.  2, 3 and 4 end in the exact fp32 re-rank.
         int mode = h->opt_tensor_mode == 0 ? 3 : h->opt_tensor_mode;
         if (mode == 3 && (h->d % 8 != 0 || h->bf_nomem)) mode = 2;
+        // an index whose cheap screen keeps overflowing (outlier norms, offset data) starts at the
+        // 3xTF32 screen; every 64th search tries the cheap one again (rows may have changed)
+        if ((mode == 2 || mode == 3) && h->opt_tensor_mode == 0 && h->screen_fail_streak >= 2 && (++h->screen_skipped & 63) != 0) mode = 4;
         if (mode == 3 && enable_bf(h, st) != B2K_OK) mode = 2;
         if (mode == 1 || mode == 4) rc = enable_lo(h, st);
+        const bool cheap = mode == 2 || mode == 3;
+        bool cheap_failed = false;
         if (!rc && !h->k3) {
             rc = k3_create(&h->k3, h->device, h->sm_count);
             if (!rc) k3_set_timing(h->k3, h->opt_timing != 0);
@@ -616,6 +624,7 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
             rc = k3_search(h->k3, h->x, h->xlo, h->xbf, h->norms, h->done + MAX_NORM_SLOT, h->done + MAX_ERR_SLOT, h->ntotal,
                            h->d, qc, nqc, kk, Dd + q0 * kk, Id + q0 * kk, ws_tail, st, mode, &overflowed);
             if (!rc && overflowed && mode != 4) {
+                cheap_failed = true;
                 // the slack zone of the cheap screen did not fit its lists (masses of near-duplicates around
                 // the k-th neighbour, or a distribution whose norms dwarf its distances): repeat this chunk
                 // with the 3xTF32 product as the screen, whose zone is ~10^4 times narrower
@@ -631,6 +640,7 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
                 rc = scan_search(h, nqc, qc, kk, Dd + q0 * kk, Id + q0 * kk, ws_tail, st, false);
             }
         }
+        if (cheap) h->screen_fail_streak = cheap_failed ? h->screen_fail_streak + 1 : 0;
     } else {
         h->last_path = 1;
         bool bf = scan_wants_bf(h, kk);

@@ -679,6 +679,14 @@ def test_screening_chain_stays_exact_when_norms_dwarf_distances(faiss):
     assert np.all(dd <= Dt[:, k - 1:k] * (1 + 4e-6)), "a returned row is farther than the true k-th neighbour"
     assert np.abs(D.astype(np.float64) - dd).max() <= 4e-6 * dd.max()
     assert all(len(set(r.tolist())) == k for r in I)
+    # after two overflowing searches in a row the index starts at the 3xTF32 screen by itself
+    idx.search(q, k)
+    before = idx.stats()["screen_fallbacks"]
+    D3, I3 = idx.search(q, k)
+    st3 = idx.stats()
+    assert st3["screen_fallbacks"] == before and st3.get("tensor_mode") == "3xtf32screen+rerank"
+    assert np.array_equal(I3, I)
+    np.testing.assert_allclose(D3, D, rtol=1e-6)           # (the re-rank and the scan sum in different orders)
     idx.set_option("tensor_mode", 4)                       # the second link of the chain on its own
     D4, I4 = idx.search(q, k)
     assert idx.stats().get("tensor_mode") == "3xtf32screen+rerank" or idx.stats()["path"] == "scan"
