@@ -1,35 +1,46 @@
 // k3_tc.cu -- K3: batched exact search on the 5th-generation tensor cores, with the top-k
-// selection fused into the accumulator epilogue, and K4, the cross-CTA merge.
+// selection fused into the accumulator epilogue; K4, the cross-CTA merge / bound refresh; K6,
+// the exact fp32 re-rank behind the screening modes.
 //
 // Stands in for faiss `exhaustive_L2sqr_blas` (sgemm in 4096 x 1024 blocks, then
 // ||q||^2 + ||x||^2 - 2<q,x>, clamp at 0) + heap/reservoir result handlers behind
-// `index.search(xq, k)` (/root/reference/llm/rag.py:116) for nq >= 20 -- oracle rule (2).
+// `index.search(xq, k)` (/root/reference/llm/rag.py:116) -- oracle rule (2).
+//
+// Numerics (template parameter MODE; chosen per search by csrc/index.cu):
+//   3  one bf16 product (kind::f16) on bf16 copies of rows and queries       } screens: the lists keep
+//   2  one TF32 product (kind::tf32 reads fp32 and ignores 13 mantissa bits) } every key within a
+//   4  3xTF32 (as below) used as a screen                                    } rigorous error slack of
+//      the k-th approximate distance, and K6 computes the exact fp32 distances (direct differences)
+//      of those few hundred rows per query: the result is exact.  3 is the default, 2 serves when
+//      there are no bf16 copies, 4 when the slack zone of 3 / 2 overflows its lists.
+//   0 / 1  3xTF32: per 8 columns of K three products Q_lo*X_hi + Q_hi*X_lo + Q_hi*X_hi (hi = the fp32
+//      value as the tensor core reads it, lo = the exact fp32 remainder), in one accumulator (0) or
+//      with the two small terms in their own accumulator (1, long rows): faiss-like expansion
+//      numerics, distances straight from the accumulator (option tensor_mode = 1).
 //
 // What runs where (per CTA; CG = 1, or CG = 2 for a CTA pair issuing cta_group::2 MMAs):
-//   warp 0  TMA producer : cp.async.bulk.tensor 2-D boxes (32 fp32 = one 128-byte swizzle row
-//           wide) of Q_hi, Q_lo (128 query rows) and X_hi, X_lo (256/CG database rows) into an
-//           NS-stage shared-memory ring, completion on mbarriers.
-//   warp 1  MMA issuer   : one elected thread issues tcgen05.mma kind::tf32 (M = 128*CG,
-//           N = 256, K = 8): per 8 columns of K three products  Q_lo*X_hi + Q_hi*X_lo +
-//           Q_hi*X_hi  ("3xTF32": hi = the fp32 value as the tensor core reads it, i.e. with the
-//           low 13 mantissa bits ignored; lo = the exact fp32 remainder) accumulated in fp32 in
-//           TMEM.  Two 256-column accumulators (all 512 TMEM columns) so the MMAs of tile t+1
-//           overlap the epilogue of tile t.
-//   warps 2-5  epilogue  : tcgen05.ld 32 lanes x 32 columns at a time; one thread owns one
-//           query row, so its pruning threshold lives in a register:
-//                 s = ||x||^2 - 2*acc        (one FFMA; ||x||^2 staged in shared memory)
-//                 keep if s <= tau - ||q||^2 (one compare; taken ~k/N of the time)
-//           survivors are appended as 64-bit (distance,row) keys to that query's private list
-//           in global memory (L2-resident); a list that could overflow on the next tile is
-//           compacted by its warp with a bitonic sort in shared memory, which also lowers the
-//           threshold and publishes it (atomicMin) to the other CTAs.
-// No distance matrix is ever written: per tile the only global traffic is the operand
-// stream and the rare survivor keys.  K4 then merges, per query, the lists of all CTAs.
-//
-// Work split: unit = (database tile of 256 rows, block of 128*CG queries), units ordered tile-
-// major and dealt round-robin to the CTAs/pairs, so the CTAs running at any moment share a few
-// database tiles through L2 and every tile is fetched from HBM once per query batch.
-// Roofline: tensor (kind::tf32); executed flops = 3 * 2 * nq * N * d.
+//   warp 0  scheduler + TMA producer: takes units from a global atomic counter (tile-major, so the
+//           CTAs running at any moment share a few database tiles through L2 and every tile comes
+//           from HBM once per batch), publishes them through a 4-deep shared-memory ring, and
+//           issues cp.async.bulk.tensor 2-D boxes (one 128-byte swizzle row wide) of the 128 query
+//           rows and the 256/CG database rows of the unit into an NS-stage ring (mbarrier tx).
+//   warp 1  MMA issuer: one elected thread issues tcgen05.mma (M = 128*CG, N = 256), accumulators
+//           in TMEM; two 256-column accumulators (all 512 TMEM columns), so the MMAs of unit u+1
+//           overlap the epilogue of unit u; tcgen05.commit frees smem stages / publishes accumulators.
+//   warps 2..5 (NH = 1) or 2..9 (NH = 2)  epilogue: tcgen05.ld 32 lanes x 32 columns at a time, two
+//           register buffers.  M = queries, so a thread owns one query row (NH = 2: one column half
+//           of it) and its pruning threshold lives in a register:
+//                 s = ||x||^2 - 2*acc         (one FFMA; ||x||^2 staged in shared memory)
+//                 any s <= tau - ||q||^2 ?    (half a 3-input FMNMX per element)
+//           a thread that has a survivor in its 32 columns locates it (bit mask + register select
+//           tree) and appends a 64-bit (distance,row) key to that query's private list in global
+//           memory (L2-resident); a list that could overflow on the next tile is compacted by its
+//           warp with a bitonic sort in shared memory, which also lowers the threshold and
+//           publishes it (atomicMin) to the other CTAs.
+// No distance matrix is ever written: per unit the only global traffic is the operand stream and
+// the rare survivor keys.  The host (k3_search) runs one small warm-start launch, then the main
+// pass in a few segments with a K4 bound refresh in between, then K4 / K6.
+// Roofline: tensor; executed flops = (1 or 3) * 2 * nq * N * d.
 #include <cuda.h>
 
 #include "k3_api.h"
@@ -600,22 +611,25 @@ __global__ void k3_set_counter_kernel(u64* next_unit, u64 value) { *next_unit = 
 // under that value, and sort those.  The count is checked, so the result is exact: if the guess
 // leaves fewer than k keys (or too many), the kernel falls back to sorting everything.
 static constexpr int K4_THREADS = 256;
-static constexpr int K4_P = 4096;     // gathered keys kept in shared memory
+// K4_P (template parameter) = gathered keys kept in shared memory; 4096 is what runs.  A query
+// with more live keys takes the sample-and-regather path, which is exact for any buffer size.
 static constexpr int K4_SAMPLE = 512;
 static constexpr int K4_DIRECT = 1024; // up to this many gathered keys are simply sorted
-static constexpr int K4_OUT = 2048;   // keys under the refined bound (k <= 1024 plus the sampling margin)
 
+template <int K4_P>
 struct K4Smem {
+    static constexpr int OUT = K4_P / 2;  // keys under the refined bound (k <= 1024 plus the sampling margin)
     u64 buf[K4_P];
     u64 smp[K4_SAMPLE];
-    u64 out[K4_OUT];
+    u64 out[OUT];
     int cnt, cnt2;
     u64 kth;
 };
 
 // every list_step-th list of query (qb,row), all keys <= kbound -> sm.buf (first K4_P of them); returns the total
+template <int K4_P>
 __device__ __forceinline__ int k4_gather(const K3Params& p, int cg, int ncta, int lstep, int r, int qb, int row,
-                                         u64 kbound, K4Smem& sm) {
+                                         u64 kbound, K4Smem<K4_P>& sm) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     __syncthreads();
     if (tid == 0) sm.cnt = 0;
@@ -662,11 +676,12 @@ __device__ __forceinline__ void k4_sort(u64* a, int n, int cap) {
     block_bitonic_sort(a, Ps);
 }
 
+template <int K4_P>
 __global__ void __launch_bounds__(K4_THREADS)
 k4_merge_kernel(const K3Params p, int cg, int ncta, int threshold_only, int list_step, float* __restrict__ D,
                 int64_t* __restrict__ I) {
     extern __shared__ __align__(16) unsigned char k4_smem_raw[];
-    K4Smem& sm = *reinterpret_cast<K4Smem*>(k4_smem_raw);
+    K4Smem<K4_P>& sm = *reinterpret_cast<K4Smem<K4_P>*>(k4_smem_raw);
     const int tid = threadIdx.x;
     const int64_t qi = blockIdx.x;
     const int bq = K3_BM * cg;
@@ -703,13 +718,13 @@ k4_merge_kernel(const K3Params p, int cg, int ncta, int threshold_only, int list
             const u64 key = sm.buf[j];
             if (key <= b2) {
                 const int pos = atomicAdd(&sm.cnt2, 1);
-                if (pos < K4_OUT) sm.out[pos] = key;
+                if (pos < K4Smem<K4_P>::OUT) sm.out[pos] = key;
             }
         }
         __syncthreads();
         const int c2 = sm.cnt2;
-        if (c2 >= k && c2 <= K4_OUT) {
-            k4_sort(sm.out, c2, K4_OUT);
+        if (c2 >= k && c2 <= K4Smem<K4_P>::OUT) {
+            k4_sort(sm.out, c2, K4Smem<K4_P>::OUT);
             res = sm.out; nres = c2;
         }
         break;  // unlucky guess: fall through to the exhaustive path
@@ -798,11 +813,12 @@ __global__ void k3_slack_bf16_kernel(int64_t nq, const float* __restrict__ qn, c
     slack2[i] = 2.f * sigma;
 }
 
+template <int K4_P>
 __global__ void __launch_bounds__(K4_THREADS)
 k6_rerank_kernel(const K3Params p, int cg, int ncta, const float* __restrict__ X, const float* __restrict__ Q,
                  float* __restrict__ D, int64_t* __restrict__ I) {
     extern __shared__ __align__(16) unsigned char k4_smem_raw[];
-    K4Smem& sm = *reinterpret_cast<K4Smem*>(k4_smem_raw);
+    K4Smem<K4_P>& sm = *reinterpret_cast<K4Smem<K4_P>*>(k4_smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t qi = blockIdx.x;
     const int bq = K3_BM * cg;
@@ -819,22 +835,37 @@ k6_rerank_kernel(const K3Params p, int cg, int ncta, const float* __restrict__ X
         if (tid == 0) atomicExch(p.overflow, 1u);
         return;
     }
-    // exact distances: one warp per candidate, 128-bit loads, fixed summation order
+    // exact distances: one warp per candidate (two candidates in flight per warp), 128-bit loads,
+    // fixed summation order
     const float* qv = Q + qi * (int64_t)d;
-    for (int c = warp; c < total; c += K4_THREADS / 32) {
-        const uint32_t xr = key_row(sm.buf[c]);
-        const float* xv = X + (int64_t)xr * d;
-        float acc = 0.f;
+    constexpr int NW = K4_THREADS / 32;
+    for (int c = warp; c < total; c += 2 * NW) {
+        const int c2 = c + NW;
+        const bool has2 = c2 < total;
+        const uint32_t xr0 = key_row(sm.buf[c]);
+        const uint32_t xr1 = has2 ? key_row(sm.buf[c2]) : xr0;
+        const float* xv0 = X + (int64_t)xr0 * d;
+        const float* xv1 = X + (int64_t)xr1 * d;
+        float acc0 = 0.f, acc1 = 0.f;
         for (int t = lane * 4; t < d; t += 128) {
             const float4 a = __ldg(reinterpret_cast<const float4*>(qv + t));
-            const float4 b = ldg_stream(reinterpret_cast<const float4*>(xv + t));
-            const float e0 = a.x - b.x, e1 = a.y - b.y, e2 = a.z - b.z, e3 = a.w - b.w;
-            acc = fmaf(e0, e0, acc); acc = fmaf(e1, e1, acc); acc = fmaf(e2, e2, acc); acc = fmaf(e3, e3, acc);
+            const float4 b0 = ldg_stream(reinterpret_cast<const float4*>(xv0 + t));
+            const float4 b1 = ldg_stream(reinterpret_cast<const float4*>(xv1 + t));
+            float e0 = a.x - b0.x, e1 = a.y - b0.y, e2 = a.z - b0.z, e3 = a.w - b0.w;
+            acc0 = fmaf(e0, e0, acc0); acc0 = fmaf(e1, e1, acc0); acc0 = fmaf(e2, e2, acc0); acc0 = fmaf(e3, e3, acc0);
+            e0 = a.x - b1.x; e1 = a.y - b1.y; e2 = a.z - b1.z; e3 = a.w - b1.w;
+            acc1 = fmaf(e0, e0, acc1); acc1 = fmaf(e1, e1, acc1); acc1 = fmaf(e2, e2, acc1); acc1 = fmaf(e3, e3, acc1);
         }
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        for (int o = 16; o > 0; o >>= 1) {
+            acc0 += __shfl_xor_sync(0xffffffffu, acc0, o);
+            acc1 += __shfl_xor_sync(0xffffffffu, acc1, o);
+        }
         __syncwarp();
-        if (lane == 0) sm.buf[c] = acc < FLT_MAX ? make_key(acc, xr) : KEY_EMPTY;
+        if (lane == 0) {
+            sm.buf[c] = acc0 < FLT_MAX ? make_key(acc0, xr0) : KEY_EMPTY;
+            if (has2) sm.buf[c2] = acc1 < FLT_MAX ? make_key(acc1, xr1) : KEY_EMPTY;
+        }
     }
     __syncthreads();
     k4_sort(sm.buf, total, K4_P);
@@ -1052,6 +1083,12 @@ static int launch_k3_any(int cg, int P, int mode, int nh, const CUtensorMap& mq,
     return B2K_EINVAL;
 }
 
+static void launch_k4(bool small, int64_t nq, cudaStream_t st, const K3Params& p, int cg, int ncta, int threshold_only,
+                      int list_step, float* D, int64_t* I) {
+    if (small) k4_merge_kernel<1024><<<(unsigned)nq, K4_THREADS, sizeof(K4Smem<1024>), st>>>(p, cg, ncta, threshold_only, list_step, D, I);
+    else k4_merge_kernel<4096><<<(unsigned)nq, K4_THREADS, sizeof(K4Smem<4096>), st>>>(p, cg, ncta, threshold_only, list_step, D, I);
+}
+
 int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, const float* norms,
               const unsigned int* max_norm_bits, const unsigned int* max_err_bits, int64_t n, int d, const float* q,
               int64_t nq, int k, float* D, int64_t* I, unsigned char* scratch, cudaStream_t st, int mode,
@@ -1119,7 +1156,11 @@ int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, con
     count_launch();
     B2K_CUDA(cudaGetLastError());
 
-    B2K_CUDA(cudaFuncSetAttribute(k4_merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(K4Smem)));
+    // (1024-key buffers -- 16 KB per block, every query block resident at once -- were tried for k <= 256:
+    // K4 stayed at ~50 us, it is bound by the dependent loads inside a block, not by residency, and the
+    // smaller re-rank buffer made the 3xTF32 screen overflow on data it otherwise handles)
+    const bool k4_small = false;
+    B2K_CUDA(cudaFuncSetAttribute(k4_merge_kernel<4096>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(K4Smem<4096>)));
     CUtensorMap mq, mql, mx, mxl;
     if (bf16) {
         if ((rc = make_map(s, &mq, qlo, nq, d, K3_BM, true))) return rc;
@@ -1157,7 +1198,7 @@ int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, con
         pre.n = (int64_t)nclusters * K3_BN;
         rc = launch_k3_any(L.cg, L.P, sep, nh, mq, mql, mx, mxl, pre, L.ncta, st);
         if (rc) return rc;
-        k4_merge_kernel<<<(unsigned)nq, K4_THREADS, sizeof(K4Smem), st>>>(pre, L.cg, L.ncta, 1, 1, nullptr, nullptr);
+        launch_k4(k4_small, nq, st, pre, L.cg, L.ncta, 1, 1, nullptr, nullptr);
         k3_init_kernel<<<(unsigned)((nslots + 255) / 256), 256, 0, st>>>(nslots, p.cnt, p.tau, p.kth, nq, nullptr, p.next_unit, nullptr);
         count_launch(2);
         B2K_CUDA(cudaGetLastError());
@@ -1191,7 +1232,7 @@ int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, con
         K3Params ps = p;
         ps.nunits = seg_end[sg];
         if (sg > 0) {
-            k4_merge_kernel<<<(unsigned)nq, K4_THREADS, sizeof(K4Smem), st>>>(p, L.cg, L.ncta, 1, 1, nullptr, nullptr);
+            launch_k4(k4_small, nq, st, p, L.cg, L.ncta, 1, 1, nullptr, nullptr);
             k3_set_counter_kernel<<<1, 1, 0, st>>>(p.next_unit, (u64)seg_end[sg - 1]);
             count_launch(2);
             B2K_CUDA(cudaGetLastError());
@@ -1202,16 +1243,17 @@ int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, con
     if (s->timing) { B2K_CUDA(cudaEventRecord(s->ev1, st)); s->timed = true; }
 
     if (!screen) {
-        k4_merge_kernel<<<(unsigned)nq, K4_THREADS, sizeof(K4Smem), st>>>(p, L.cg, L.ncta, 0, 1, D, I);
+        launch_k4(k4_small, nq, st, p, L.cg, L.ncta, 0, 1, D, I);
         count_launch();
         B2K_CUDA(cudaGetLastError());
         return B2K_OK;
     }
     // screening: the exact k-th smallest approximate distance per query, then the exact re-rank of
     // everything within the slack of it
-    B2K_CUDA(cudaFuncSetAttribute(k6_rerank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(K4Smem)));
-    k4_merge_kernel<<<(unsigned)nq, K4_THREADS, sizeof(K4Smem), st>>>(p, L.cg, L.ncta, 1, 1, nullptr, nullptr);
-    k6_rerank_kernel<<<(unsigned)nq, K4_THREADS, sizeof(K4Smem), st>>>(p, L.cg, L.ncta, x, q, D, I);
+    B2K_CUDA(cudaFuncSetAttribute(k6_rerank_kernel<4096>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(K4Smem<4096>)));
+    launch_k4(k4_small, nq, st, p, L.cg, L.ncta, 1, 1, nullptr, nullptr);
+    if (k4_small) k6_rerank_kernel<1024><<<(unsigned)nq, K4_THREADS, sizeof(K4Smem<1024>), st>>>(p, L.cg, L.ncta, x, q, D, I);
+    else k6_rerank_kernel<4096><<<(unsigned)nq, K4_THREADS, sizeof(K4Smem<4096>), st>>>(p, L.cg, L.ncta, x, q, D, I);
     count_launch(2);
     B2K_CUDA(cudaGetLastError());
     // a list or the re-rank buffer could not hold every row inside the slack (masses of near-

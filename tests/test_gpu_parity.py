@@ -684,7 +684,9 @@ def test_screening_chain_stays_exact_when_norms_dwarf_distances(faiss):
     before = idx.stats()["screen_fallbacks"]
     D3, I3 = idx.search(q, k)
     st3 = idx.stats()
-    assert st3["screen_fallbacks"] == before and st3.get("tensor_mode") == "3xtf32screen+rerank"
+    # (no cheap attempt any more: at most the 3xTF32 screen itself overflows for a crowded query and the scan answers)
+    assert st3["screen_fallbacks"] - before <= 1
+    assert st3.get("tensor_mode") == "3xtf32screen+rerank" or st3["path"] == "scan"
     assert np.array_equal(I3, I)
     np.testing.assert_allclose(D3, D, rtol=1e-6)           # (the re-rank and the scan sum in different orders)
     idx.set_option("tensor_mode", 4)                       # the second link of the chain on its own
