@@ -115,17 +115,28 @@ class IndexFlatL2:
         x = _as_host_f32(x, self.d, "add")
         _lib.check(L.b2k_add(self._h, x.shape[0], x.ctypes.data_as(C.c_void_p), 0, None))
 
-    def search(self, x, k):
-        """(D, I) = k nearest stored rows of each query row (rag.py:116)."""
+    def search(self, x, k, params=None, D=None, I=None):
+        """(D, I) = k nearest stored rows of each query row (rag.py:116).
+
+        Same optional arguments as faiss: `D` / `I` are preallocated outputs (float32 / int64,
+        C-contiguous, shape (nq, k)) that are filled and returned; page-locked host arrays are
+        copied to / from directly, without the library's staging buffer.  `params` must be None."""
         L = _lib.lib()
         k = int(k)
         assert k > 0, "search: k must be positive"
+        assert params is None, "search: IndexFlatL2 takes no search parameters"
         if _is_torch(x) and x.is_cuda:
             import torch
             x = _as_dev_f32(x, self.d, self.device, "search")
             nq = x.shape[0]
-            D = torch.empty((nq, k), dtype=torch.float32, device=x.device)
-            I = torch.empty((nq, k), dtype=torch.int64, device=x.device)
+            if D is None:
+                D = torch.empty((nq, k), dtype=torch.float32, device=x.device)
+            if I is None:
+                I = torch.empty((nq, k), dtype=torch.int64, device=x.device)
+            assert _is_torch(D) and _is_torch(I) and D.is_cuda and I.is_cuda and D.device == x.device and I.device == x.device, \
+                "search: D / I must be CUDA tensors on the queries' device"
+            assert D.dtype == torch.float32 and I.dtype == torch.int64 and D.is_contiguous() and I.is_contiguous() \
+                and tuple(D.shape) == (nq, k) and tuple(I.shape) == (nq, k), "search: D / I must be contiguous (nq, k) float32 / int64"
             _lib.check(L.b2k_search(self._h, nq, C.c_void_p(x.data_ptr()), k, C.c_void_p(D.data_ptr()),
                                     C.c_void_p(I.data_ptr()), 1, self._stream()))
             return D, I
@@ -133,8 +144,13 @@ class IndexFlatL2:
             x = x.detach().cpu().numpy()
         x = _as_host_f32(x, self.d, "search")
         nq = x.shape[0]
-        D = np.empty((nq, k), dtype=np.float32)
-        I = np.empty((nq, k), dtype=np.int64)
+        if D is None:
+            D = np.empty((nq, k), dtype=np.float32)
+        if I is None:
+            I = np.empty((nq, k), dtype=np.int64)
+        assert isinstance(D, np.ndarray) and isinstance(I, np.ndarray) and D.dtype == np.float32 and I.dtype == np.int64 \
+            and D.flags["C_CONTIGUOUS"] and I.flags["C_CONTIGUOUS"] and D.shape == (nq, k) and I.shape == (nq, k), \
+            "search: D / I must be C-contiguous (nq, k) float32 / int64 arrays"
         _lib.check(L.b2k_search(self._h, nq, x.ctypes.data_as(C.c_void_p), k, D.ctypes.data_as(C.c_void_p),
                                 I.ctypes.data_as(C.c_void_p), 0, None))
         return D, I

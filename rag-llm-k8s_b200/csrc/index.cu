@@ -233,6 +233,13 @@ int enable_bf(b2k_index* h, cudaStream_t st) {
 
 size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
 
+// true if p is page-locked host memory known to CUDA (cudaMallocHost / cudaHostRegister / torch pin_memory)
+bool is_pinned_host(const void* p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return a.type == cudaMemoryTypeHost;
+}
+
 // Candidates the bf16 scan selects for a request of k (0: the bf16 scan cannot serve this k).
 int scan_bf_candidates(int k) {
     const int kp = 2 * k + 32;
@@ -579,11 +586,18 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
     const float* qd = xq;
     float* Dd = D;
     int64_t* Id = I;
+    bool q_pinned = false, out_pinned = false;
     if (!on_device) {
-        rc = ensure_pin(h, io_bytes);
-        if (rc) return rc;
-        memcpy(h->pin, xq, (size_t)nq * h->d * sizeof(float));
-        B2K_CUDA(cudaMemcpyAsync(wsb, h->pin, (size_t)nq * h->d * sizeof(float), cudaMemcpyHostToDevice, st));
+        // page-locked caller buffers are copied to / from directly; pageable ones go through the
+        // handle's own pinned staging buffer (an extra host memcpy each way)
+        q_pinned = is_pinned_host(xq);
+        out_pinned = is_pinned_host(D) && is_pinned_host(I);
+        if (!q_pinned || !out_pinned) {
+            rc = ensure_pin(h, io_bytes);
+            if (rc) return rc;
+        }
+        if (!q_pinned) memcpy(h->pin, xq, (size_t)nq * h->d * sizeof(float));
+        B2K_CUDA(cudaMemcpyAsync(wsb, q_pinned ? (const void*)xq : h->pin, (size_t)nq * h->d * sizeof(float), cudaMemcpyHostToDevice, st));
         qd = reinterpret_cast<const float*>(wsb);
         Dd = reinterpret_cast<float*>(wsb + q_bytes);
         Id = reinterpret_cast<int64_t*>(wsb + q_bytes + d_bytes);
@@ -652,12 +666,14 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
 
     if (!on_device) {
         unsigned char* pb = static_cast<unsigned char*>(h->pin);
-        B2K_CUDA(cudaMemcpyAsync(pb + q_bytes, Dd, (size_t)nq * kk * sizeof(float), cudaMemcpyDeviceToHost, st));
-        B2K_CUDA(cudaMemcpyAsync(pb + q_bytes + d_bytes, Id, (size_t)nq * kk * sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+        B2K_CUDA(cudaMemcpyAsync(out_pinned ? (void*)D : (void*)(pb + q_bytes), Dd, (size_t)nq * kk * sizeof(float), cudaMemcpyDeviceToHost, st));
+        B2K_CUDA(cudaMemcpyAsync(out_pinned ? (void*)I : (void*)(pb + q_bytes + d_bytes), Id, (size_t)nq * kk * sizeof(int64_t), cudaMemcpyDeviceToHost, st));
         cudaError_t e = cudaStreamSynchronize(st);
         if (e != cudaSuccess) { h->sticky = (int)e; set_error("b2k_search: %s", cudaGetErrorString(e)); return B2K_ECUDA; }
-        memcpy(D, pb + q_bytes, (size_t)nq * kk * sizeof(float));
-        memcpy(I, pb + q_bytes + d_bytes, (size_t)nq * kk * sizeof(int64_t));
+        if (!out_pinned) {
+            memcpy(D, pb + q_bytes, (size_t)nq * kk * sizeof(float));
+            memcpy(I, pb + q_bytes + d_bytes, (size_t)nq * kk * sizeof(int64_t));
+        }
     }
     return B2K_OK;
 }

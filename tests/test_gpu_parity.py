@@ -696,6 +696,31 @@ def test_screening_chain_stays_exact_when_norms_dwarf_distances(faiss):
     assert np.all(dd4 <= Dt[:, k - 1:k] * (1 + 4e-6))
 
 
+def test_preallocated_and_pinned_outputs(faiss):
+    """faiss's optional D / I output arguments, pageable and page-locked (the latter are copied to
+    directly, without the staging buffer): same answers as the plain call, outputs returned."""
+    import torch
+    x = O.synth(81, 0, 30000, 64)
+    idx = _build(faiss, x)
+    for nq, k in ((3, 7), (40, 10)):
+        q = O.synth(82, 0, nq, 64)
+        Dref, Iref = idx.search(q, k)
+        D = np.empty((nq, k), np.float32); I = np.empty((nq, k), np.int64)
+        D2, I2 = idx.search(q, k, D=D, I=I)
+        assert D2 is D and I2 is I and np.array_equal(D, Dref) and np.array_equal(I, Iref)
+        qp = torch.from_numpy(q).pin_memory().numpy()
+        Dp = torch.empty((nq, k), dtype=torch.float32, pin_memory=True).numpy()
+        Ip = torch.empty((nq, k), dtype=torch.int64, pin_memory=True).numpy()
+        idx.search(qp, k, D=Dp, I=Ip)
+        assert np.array_equal(Dp, Dref) and np.array_equal(Ip, Iref)
+        qd = torch.from_numpy(q).cuda()
+        Dd = torch.empty((nq, k), dtype=torch.float32, device="cuda"); Id = torch.empty((nq, k), dtype=torch.int64, device="cuda")
+        idx.search(qd, k, D=Dd, I=Id)
+        assert np.array_equal(Dd.cpu().numpy(), Dref) and np.array_equal(Id.cpu().numpy(), Iref)
+    with pytest.raises(AssertionError):
+        idx.search(O.synth(82, 0, 3, 64), 7, D=np.empty((3, 8), np.float32), I=np.empty((3, 7), np.int64))
+
+
 def test_nonfinite_rows_and_queries_on_the_tensor_path(faiss):
     """inf / NaN rows are never selected and do not disturb their neighbours in the tile; a NaN
     query gets all padding (no distance is < FLT_MAX), the other queries are unaffected."""
