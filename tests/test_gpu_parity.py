@@ -721,6 +721,44 @@ def test_preallocated_and_pinned_outputs(faiss):
         idx.search(O.synth(82, 0, 3, 64), 7, D=np.empty((3, 8), np.float32), I=np.empty((3, 7), np.int64))
 
 
+def _hard_cases(rng, n, d, nq):
+    g = rng.standard_normal((n, d)).astype(np.float32)
+    s = np.exp(rng.standard_normal((n, 1)) * 1.5).astype(np.float32)
+    yield "heavy-tailed row norms", g * s, rng.standard_normal((nq, d)).astype(np.float32)
+    c = rng.standard_normal((200, d)).astype(np.float32)
+    cl = (c[rng.integers(0, 200, n)] + rng.standard_normal((n, d)).astype(np.float32) * 1e-3).astype(np.float32)
+    yield "tight clusters", cl, (c[:nq] + rng.standard_normal((nq, d)).astype(np.float32) * 1e-3).astype(np.float32)
+    u = g / np.linalg.norm(g, axis=1, keepdims=True)
+    qs = u[rng.integers(0, n, nq)] + rng.standard_normal((nq, d)).astype(np.float32) * 0.01
+    yield "unit norm, queries next to stored rows", u.astype(np.float32), (qs / np.linalg.norm(qs, axis=1, keepdims=True)).astype(np.float32)
+    yield "tiny magnitudes", (g * 1e-18).astype(np.float32), (rng.standard_normal((nq, d)) * 1e-18).astype(np.float32)
+    lat = rng.integers(-3, 4, (n, d)).astype(np.float32)
+    yield "integer lattice, many exact ties", lat, rng.integers(-3, 4, (nq, d)).astype(np.float32)
+
+
+@pytest.mark.parametrize("opts", [{"path": 2, "tensor_mode": 3}, {"path": 2, "tensor_mode": 2}, {"path": 1, "scan_rows": 2}],
+                         ids=["tensor-bf16-screen", "tensor-tf32-screen", "scan-bf16"])
+def test_screens_are_exact_on_hard_distributions(faiss, opts):
+    """The reduced-precision screens against the float64 ground truth on distributions chosen to hurt
+    them (scripts/stress_exact.py has the long version): every returned row must be at least as close
+    as the true k-th neighbour, ids unique, distances = the direct fp32 sums."""
+    rng = np.random.default_rng(5)
+    n, d, k = 50000, 128, 20
+    nq = 3 if opts["path"] == 1 else 48
+    for name, x, q in _hard_cases(rng, n, d, nq):
+        idx = _build(faiss, x)
+        for kk, v in opts.items():
+            idx.set_option(kk, v)
+        D, I = idx.search(q, k)
+        Dt, It = O.truth_f64(x, q, k)
+        dd = O.dist_f64(x, q, I)
+        kth = Dt[:, k - 1:k]
+        assert np.all(dd <= kth * (1 + 4e-6) + 1e-37), name
+        rel = np.where(dd > 1e-37, np.abs(D.astype(np.float64) - dd) / np.maximum(dd, 1e-300), 0.0)
+        assert rel.max() < 4e-6, (name, rel.max())
+        assert all(len(set(r.tolist())) == k for r in I), name
+
+
 def test_nonfinite_rows_and_queries_on_the_tensor_path(faiss):
     """inf / NaN rows are never selected and do not disturb their neighbours in the tile; a NaN
     query gets all padding (no distance is < FLT_MAX), the other queries are unaffected."""
