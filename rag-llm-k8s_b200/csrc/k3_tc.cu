@@ -623,6 +623,7 @@ struct K4Smem {
     u64 smp[K4_SAMPLE];
     u64 out[OUT];
     int cnt, cnt2;
+    int sel[2];  // radix select: (bin, keys below it)
     u64 kth;
 };
 
@@ -676,6 +677,59 @@ __device__ __forceinline__ void k4_sort(u64* a, int n, int cap) {
     block_bitonic_sort(a, Ps);
 }
 
+// Float bits of the k-th smallest distance (1 <= k <= n) among the n keys of `a`: a 3-pass radix
+// select (11 + 11 + 10 bits) over the distance half of the keys, histogram in shared memory.  The
+// bound refreshes only need this number, and a full bitonic sort of the gathered keys was half of
+// their 57 us.  Distances are non-negative floats, so their bits order like unsigned integers.
+// hist: 2048 words of scratch.  Block-wide; every thread returns the result.
+__device__ __forceinline__ uint32_t k4_select_dist(const u64* a, int n, int k, uint32_t* hist, int* scratch2) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    __shared__ int s_wsum[K4_THREADS / 32];
+    uint32_t prefix = 0, mask = 0;
+    int remaining = k;
+#pragma unroll 1
+    for (int pass = 0; pass < 3; ++pass) {
+        const int shift = pass == 0 ? 21 : (pass == 1 ? 10 : 0);
+        const int nb = pass == 2 ? 1024 : 2048;
+        for (int b = tid; b < 2048; b += K4_THREADS) hist[b] = 0;
+        __syncthreads();
+        for (int i = tid; i < n; i += K4_THREADS) {
+            const uint32_t dbits = (uint32_t)(a[i] >> 32);
+            if ((dbits & mask) == prefix) atomicAdd(&hist[(dbits >> shift) & (uint32_t)(nb - 1)], 1u);
+        }
+        __syncthreads();
+        // each thread owns 8 consecutive bins; block-wide exclusive scan of the per-thread sums
+        int mine = 0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) mine += (int)hist[tid * 8 + j];
+        int incl = mine;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += v;
+        }
+        if (lane == 31) s_wsum[warp] = incl;
+        __syncthreads();
+        int before = incl - mine;
+        for (int w = 0; w < warp; ++w) before += s_wsum[w];
+        if (before < remaining && remaining <= before + mine) {  // exactly one thread: the k-th key is in its bins
+            int c = before;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const int hcount = (int)hist[tid * 8 + j];
+                if (c < remaining && remaining <= c + hcount) { scratch2[0] = tid * 8 + j; scratch2[1] = c; }
+                c += hcount;
+            }
+        }
+        __syncthreads();
+        prefix |= (uint32_t)scratch2[0] << shift;
+        mask |= (uint32_t)(nb - 1) << shift;
+        remaining -= scratch2[1];
+        __syncthreads();
+    }
+    return prefix;
+}
+
 template <int K4_P>
 __global__ void __launch_bounds__(K4_THREADS)
 k4_merge_kernel(const K3Params p, int cg, int ncta, int threshold_only, int list_step, float* __restrict__ D,
@@ -697,6 +751,14 @@ k4_merge_kernel(const K3Params p, int cg, int ncta, int threshold_only, int list
     for (int attempt = 0; attempt < 4 && !res; ++attempt) {
         const int total = k4_gather(p, cg, ncta, lstep, r, qb, row, kbound, sm);
         const int have = total < K4_P ? total : K4_P;
+        if (threshold_only && attempt == 0 && total <= K4_P) {
+            // bound refresh: only the k-th smallest distance is wanted, no order
+            if (total >= k) {
+                const uint32_t dk = k4_select_dist(sm.buf, total, k, reinterpret_cast<uint32_t*>(sm.out), sm.sel);
+                if (tid == 0) atomicMin(p.gts + qi, dk);
+            }
+            return;
+        }
         if (total <= K4_DIRECT) {  // small enough: sort it all
             if (attempt > 0 && total < k) break;  // the tightened bound cut too deep: exhaustive path
             k4_sort(sm.buf, have, K4_P);
