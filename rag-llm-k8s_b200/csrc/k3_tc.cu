@@ -1145,10 +1145,9 @@ static int launch_k3_any(int cg, int P, int mode, int nh, const CUtensorMap& mq,
     return B2K_EINVAL;
 }
 
-static void launch_k4(bool small, int64_t nq, cudaStream_t st, const K3Params& p, int cg, int ncta, int threshold_only,
+static void launch_k4(int64_t nq, cudaStream_t st, const K3Params& p, int cg, int ncta, int threshold_only,
                       int list_step, float* D, int64_t* I) {
-    if (small) k4_merge_kernel<1024><<<(unsigned)nq, K4_THREADS, sizeof(K4Smem<1024>), st>>>(p, cg, ncta, threshold_only, list_step, D, I);
-    else k4_merge_kernel<4096><<<(unsigned)nq, K4_THREADS, sizeof(K4Smem<4096>), st>>>(p, cg, ncta, threshold_only, list_step, D, I);
+    k4_merge_kernel<4096><<<(unsigned)nq, K4_THREADS, sizeof(K4Smem<4096>), st>>>(p, cg, ncta, threshold_only, list_step, D, I);
 }
 
 int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, const float* norms,
@@ -1219,9 +1218,8 @@ int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, con
     B2K_CUDA(cudaGetLastError());
 
     // (1024-key buffers -- 16 KB per block, every query block resident at once -- were tried for k <= 256:
-    // K4 stayed at ~50 us, it is bound by the dependent loads inside a block, not by residency, and the
-    // smaller re-rank buffer made the 3xTF32 screen overflow on data it otherwise handles)
-    const bool k4_small = false;
+    // K4 did not get faster, it was bound by its sort, not by residency, and the smaller re-rank buffer
+    // made the 3xTF32 screen overflow on data it otherwise handles)
     B2K_CUDA(cudaFuncSetAttribute(k4_merge_kernel<4096>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(K4Smem<4096>)));
     CUtensorMap mq, mql, mx, mxl;
     if (bf16) {
@@ -1260,7 +1258,7 @@ int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, con
         pre.n = (int64_t)nclusters * K3_BN;
         rc = launch_k3_any(L.cg, L.P, sep, nh, mq, mql, mx, mxl, pre, L.ncta, st);
         if (rc) return rc;
-        launch_k4(k4_small, nq, st, pre, L.cg, L.ncta, 1, 1, nullptr, nullptr);
+        launch_k4(nq, st, pre, L.cg, L.ncta, 1, 1, nullptr, nullptr);
         k3_init_kernel<<<(unsigned)((nslots + 255) / 256), 256, 0, st>>>(nslots, p.cnt, p.tau, p.kth, nq, nullptr, p.next_unit, nullptr);
         count_launch(2);
         B2K_CUDA(cudaGetLastError());
@@ -1294,7 +1292,7 @@ int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, con
         K3Params ps = p;
         ps.nunits = seg_end[sg];
         if (sg > 0) {
-            launch_k4(k4_small, nq, st, p, L.cg, L.ncta, 1, 1, nullptr, nullptr);
+            launch_k4(nq, st, p, L.cg, L.ncta, 1, 1, nullptr, nullptr);
             k3_set_counter_kernel<<<1, 1, 0, st>>>(p.next_unit, (u64)seg_end[sg - 1]);
             count_launch(2);
             B2K_CUDA(cudaGetLastError());
@@ -1305,7 +1303,7 @@ int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, con
     if (s->timing) { B2K_CUDA(cudaEventRecord(s->ev1, st)); s->timed = true; }
 
     if (!screen) {
-        launch_k4(k4_small, nq, st, p, L.cg, L.ncta, 0, 1, D, I);
+        launch_k4(nq, st, p, L.cg, L.ncta, 0, 1, D, I);
         count_launch();
         B2K_CUDA(cudaGetLastError());
         return B2K_OK;
@@ -1313,9 +1311,8 @@ int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, con
     // screening: the exact k-th smallest approximate distance per query, then the exact re-rank of
     // everything within the slack of it
     B2K_CUDA(cudaFuncSetAttribute(k6_rerank_kernel<4096>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(K4Smem<4096>)));
-    launch_k4(k4_small, nq, st, p, L.cg, L.ncta, 1, 1, nullptr, nullptr);
-    if (k4_small) k6_rerank_kernel<1024><<<(unsigned)nq, K4_THREADS, sizeof(K4Smem<1024>), st>>>(p, L.cg, L.ncta, x, q, D, I);
-    else k6_rerank_kernel<4096><<<(unsigned)nq, K4_THREADS, sizeof(K4Smem<4096>), st>>>(p, L.cg, L.ncta, x, q, D, I);
+    launch_k4(nq, st, p, L.cg, L.ncta, 1, 1, nullptr, nullptr);
+    k6_rerank_kernel<4096><<<(unsigned)nq, K4_THREADS, sizeof(K4Smem<4096>), st>>>(p, L.cg, L.ncta, x, q, D, I);
     count_launch(2);
     B2K_CUDA(cudaGetLastError());
     // a list or the re-rank buffer could not hold every row inside the slack (masses of near-
