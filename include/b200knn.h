@@ -53,12 +53,17 @@ B2K_API int b2k_create(int d, int device, b2k_index** out);
 B2K_API int b2k_destroy(b2k_index* h);
 
 /* index.add(vectors_np) -- llm/rag.py:80.  Appends n rows; also computes ||x||^2 per row
- * (kernel K1) and, once a batched search has been made, the TF32 residual rows. */
+ * (kernel K1) and keeps the derived copies the search kernels use up to date once they exist
+ * (bf16 copies for the screening passes, TF32 residual rows for the 3xTF32 modes). */
 B2K_API int b2k_add(b2k_index* h, int64_t n, const float* x, int on_device, void* stream);
 
 /* D, I = index.search(xq, k) -- llm/rag.py:116.  For each of nq queries the k smallest
  * squared distances ascending with their row ids; if ntotal < k the tail is I = -1,
- * D = FLT_MAX (3.4028235e38), which is what rag.py:118-119 then indexes metadata with. */
+ * D = FLT_MAX (3.4028235e38), which is what rag.py:118-119 then indexes metadata with.
+ * Results are exact: whatever reduced-precision screen selects the candidates, the returned
+ * distances are fp32 sums of (q - x)^2 over the fp32 rows, ties ordered by id.  A search served
+ * by the tensor-core kernel (batches; see b2k_set_option) synchronises `stream` once even with
+ * on_device != 0, unless option "screen_flag_ptr" is set. */
 B2K_API int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, int64_t* I,
                int on_device, void* stream);
 
