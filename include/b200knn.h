@@ -61,7 +61,9 @@ B2K_API int b2k_add(b2k_index* h, int64_t n, const float* x, int on_device, void
  * squared distances ascending with their row ids; if ntotal < k the tail is I = -1,
  * D = FLT_MAX (3.4028235e38), which is what rag.py:118-119 then indexes metadata with.
  * Results are exact: whatever reduced-precision screen selects the candidates, the returned
- * distances are fp32 sums of (q - x)^2 over the fp32 rows, ties ordered by id.  A search served
+ * distances are fp32 sums of (q - x)^2 over the fp32 rows, ties ordered by id (option
+ * "tensor_mode" = 1 is the exception: it returns the 3xTF32 expansion values, faiss's sgemm
+ * numerics).  A search served
  * by the tensor-core kernel (batches; see b2k_set_option) synchronises `stream` once even with
  * on_device != 0, unless option "screen_flag_ptr" is set. */
 B2K_API int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, int64_t* I,
