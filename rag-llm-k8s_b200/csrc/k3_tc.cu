@@ -1276,7 +1276,9 @@ int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, con
     long long seg_end[8];
     int nseg = 0;
     if (warm_rows > 0 && s->segments) {
-        const double target = s->segments > 1 ? (double)s->segments : 400.0;
+        // one query block: the pass is bound by the row stream, the epilogue idles, survivors are nearly
+        // free and every boundary (drain, K4, refill) is pure loss: 8x fewer, coarser steps
+        const double target = s->segments > 1 ? (double)s->segments : (L.nqb == 1 ? 3200.0 : 400.0);
         const double r = 1.0 + (target > 2.0 * k ? target : 2.0 * k) / (double)k;
         const long long min_step = 4LL * nclusters;  // units
         double g = (double)warm_rows / (double)n * r;
