@@ -559,9 +559,10 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
     // in direct fp32 differences (the tensor path re-ranks), so the switch is purely a matter of speed:
     // the scan costs one pass over the rows per group of <= 4 (bf16) or 8 (fp32) queries, the tensor
     // path ~0.3 ms of fixed work plus one cheap pass for any nq <= 128 (measured at 10M x 384: nq = 8
-    // scan 4.9 ms, tensor 1.9 ms; nq = 16: 9.8 vs 1.9; nq = 2: 1.8 vs 1.9; at 100k rows nq = 4: 0.12 vs 0.16 ms).
+    // scan 4.9 ms, tensor 1.4 ms; nq = 16: 9.8 vs 1.4; nq = 2: 1.8 vs 1.35; at 100k rows nq = 4: 0.12 vs 0.16 ms).
     const double elems = (double)h->ntotal * h->d;
-    const bool tc_pays = nq >= 20 || (h->opt_tensor_mode != 1 && ((nq >= 5 && elems >= 16e6) || (nq >= 3 && elems >= 256e6)));
+    const bool tc_pays = nq >= 20 || (h->opt_tensor_mode != 1 && ((nq >= 5 && elems >= 16e6) || (nq >= 3 && elems >= 256e6) ||
+                                                                  (nq >= 2 && elems >= 2e9)));
     const bool want_tc = h->ntotal > 0 && (h->opt_path == 2 || (h->opt_path == 0 && tc_pays)) && k3_supported(h->d, kk);
 
     // workspace: [queries][D][I] for host callers, then the kernels' scratch
