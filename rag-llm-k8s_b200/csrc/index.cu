@@ -617,6 +617,7 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
         // 3xTF32 screen; every 64th search tries the cheap one again (rows may have changed)
         if ((mode == 2 || mode == 3) && h->opt_tensor_mode == 0 && h->screen_fail_streak >= 2 && (++h->screen_skipped & 63) != 0) mode = 4;
         if (mode == 3 && enable_bf(h, st) != B2K_OK) mode = 2;
+        if (mode == 4 && h->opt_tensor_mode == 0 && enable_lo(h, st) != B2K_OK) mode = 2;  // no room for the residual rows: cheap screen, then the scan
         if (mode == 1 || mode == 4) rc = enable_lo(h, st);
         const bool cheap = mode == 2 || mode == 3;
         bool cheap_failed = false;
@@ -644,9 +645,9 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
                 // the k-th neighbour, or a distribution whose norms dwarf its distances): repeat this chunk
                 // with the 3xTF32 product as the screen, whose zone is ~10^4 times narrower
                 ++h->stat_screen_fallbacks;
-                rc = enable_lo(h, st);
-                if (!rc) rc = k3_search(h->k3, h->x, h->xlo, h->xbf, h->norms, h->done + MAX_NORM_SLOT, h->done + MAX_ERR_SLOT,
-                                        h->ntotal, h->d, qc, nqc, kk, Dd + q0 * kk, Id + q0 * kk, ws_tail, st, 4, &overflowed);
+                if (enable_lo(h, st) == B2K_OK)  // (no room for the residual rows: straight to the scan, overflowed stays set)
+                    rc = k3_search(h->k3, h->x, h->xlo, h->xbf, h->norms, h->done + MAX_NORM_SLOT, h->done + MAX_ERR_SLOT,
+                                   h->ntotal, h->d, qc, nqc, kk, Dd + q0 * kk, Id + q0 * kk, ws_tail, st, 4, &overflowed);
             }
             if (!rc && overflowed) {
                 // even that zone is crowded (exact duplicates by the thousand): the scan kernel is exact whatever the data
