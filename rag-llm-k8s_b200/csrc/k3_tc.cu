@@ -974,13 +974,12 @@ static int k3_P(int k) { return next_pow2(k + K3_BN); }
 // 1.69 vs 2.21 ms at k = 1000, but 48 vs 35 us on 200k rows x 64 queries.
 static int k3_cg_for(int k, int want, int d, bool screen, int64_t n, int64_t nq, int sm_count) {
     if (want == 1 || want == 2) return (want == 1 && !screen && k3_P(k) > 512) ? 2 : want;
-    if (screen) {
-        const int64_t units2 = ((n + K3_BN - 1) / K3_BN) * ((nq + 2 * K3_BM - 1) / (2 * K3_BM));
-        // a pair serves 256 queries per unit: with <= 128 its second CTA would multiply padding
-        return (nq > K3_BM && units2 >= 64LL * (sm_count / 2)) ? 2 : 1;
-    }
-    if (k3_P(k) > 512) return 2;
-    return d >= 512 ? 2 : 1;
+    const int64_t units2 = ((n + K3_BN - 1) / K3_BN) * ((nq + 2 * K3_BM - 1) / (2 * K3_BM));
+    // a pair serves 256 queries per unit: with <= 128 its second CTA would multiply padding
+    const bool enough = nq > K3_BM && units2 >= 64LL * (sm_count / 2);
+    if (screen) return enough ? 2 : 1;
+    if (k3_P(k) > 512 || d >= 512) return 2;
+    return enough ? 2 : 1;  // 3xTF32 at C3: 25.7 ms with pairs, 33.4 ms without
 }
 
 bool k3_supported(int d, int k) {
