@@ -1296,12 +1296,20 @@ int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, con
         // free and every boundary (drain, K4, refill) is pure loss: 8x fewer, coarser steps
         const double target = s->segments > 1 ? (double)s->segments : (L.nqb == 1 ? 3200.0 : 400.0);
         const double r = 1.0 + (target > 2.0 * k ? target : 2.0 * k) / (double)k;
-        const long long min_step = 4LL * nclusters;  // units
-        double g = (double)warm_rows / (double)n * r;
-        while (g < 0.6 && nseg < 6) {
-            const long long end = (long long)(g * (double)ntiles) * L.nqb;
-            if (end >= (nseg ? seg_end[nseg - 1] : 0) + min_step && end + min_step <= p.nunits) seg_end[nseg++] = end;
+        const long long min_step = 4LL * nclusters;  // units: a shorter segment is all drain and refill
+        double g = (double)warm_rows / (double)n;     // fraction of the rows behind the current bound
+        long long prev = 0;
+        while (nseg < 6) {
             g *= r;
+            if (g >= 0.6) break;
+            long long end = (long long)(g * (double)ntiles) * L.nqb;
+            // a boundary that would come too early is moved out, never dropped: dropping it leaves the next
+            // segment r times more permissive (measured: 2.0 instead of 0.94 ms on a 1.25M-row shard)
+            if (end < prev + min_step) end = prev + min_step;
+            if (end + min_step > p.nunits) break;
+            seg_end[nseg++] = end;
+            prev = end;
+            g = (double)end / (double)p.nunits;       // what has really been scanned by then
         }
     }
     seg_end[nseg++] = p.nunits;
