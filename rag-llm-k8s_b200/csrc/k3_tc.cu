@@ -1258,7 +1258,7 @@ int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, con
     // accumulator, 2 TF32 screening, 3 bf16 screening (one product; exact distances from the re-rank kernel)
     const int sep = bf16 ? 3 : mode == 2 ? 2 : mode == 4 ? 4 : (s->sep_mode == 1 || (s->sep_mode == 0 && d >= 512)) ? 1 : 0;
     const int nh = s->epi_halves == 1 ? 1 : 2;  // eight epilogue warps where instantiated (screening modes)
-    const int cols_a = 64;
+    int cols_a = 64;
     int64_t warm_rows = 0;  // rows behind the bound the main pass starts with
     if (ntiles >= 2 * (int64_t)nclusters && (int64_t)nclusters * cols_a >= 2 * (int64_t)k) {
         K3Params pre = p;
@@ -1269,6 +1269,12 @@ int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, con
         // each CTA (pair) only serves every G-th query block, leaving nclusters / G lists of 64 keys per query
         int G = (int)(((int64_t)nclusters * cols_a) / (12 * (int64_t)k));
         G = G < 1 ? 1 : (G > L.nqb ? L.nqb : G);
+        // ... and of fewer than 64 columns when that is still more than the ~12k keys per query a usable
+        // bound needs (few query blocks, small k): the pass keeps every key, so it costs what it keeps
+        int want_cols = (int)((12 * (int64_t)k * G + nclusters - 1) / nclusters);
+        want_cols = (want_cols + 7) & ~7;
+        cols_a = want_cols < 8 ? 8 : (want_cols > 64 ? 64 : want_cols);
+        pre.tile_cols = cols_a;
         pre.static_qb_mod = G;
         pre.nunits = (int64_t)nclusters * L.nqb;
         pre.n = (int64_t)nclusters * K3_BN;
