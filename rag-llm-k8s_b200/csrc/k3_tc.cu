@@ -131,13 +131,13 @@ __device__ __forceinline__ void reg_fence32(uint32_t (&v)[32]) {
                  :: "memory");
 }
 
-// v[c] for a run-time c, without local memory: a binary tree of selects over the 32 registers.
-template <int LO, int N>
-__device__ __forceinline__ float reg_select32(const float (&v)[32], int c) {
+// v[c] for a run-time c, without local memory: a binary tree of selects over SZ registers.
+template <int LO, int N, int SZ>
+__device__ __forceinline__ float reg_select(const float (&v)[SZ], int c) {
     if constexpr (N == 1) {
         return v[LO];
     } else {
-        const float a = reg_select32<LO, N / 2>(v, c), b = reg_select32<LO + N / 2, N / 2>(v, c);
+        const float a = reg_select<LO, N / 2, SZ>(v, c), b = reg_select<LO + N / 2, N / 2, SZ>(v, c);
         return (c & (N / 2)) ? b : a;
     }
 }
@@ -146,7 +146,7 @@ __device__ __forceinline__ float reg_select32(const float (&v)[32], int c) {
 // instructions per element or fewer: s = ||x||^2 - 2 ip (one FFMA) and "any s <= t" over four
 // independent chains (nvcc turns the OR of compares into 3-input FMNMX: 1.5 per element).  With
 // the bound refreshed between segments of the pass a warp meets a survivor in about one chunk
-// out of ten; only then are the columns located (second, mask-building walk).
+// out of ten; only then are the columns located (second, mask-building walk over the chains that fired).
 // v = main accumulator, w = cross-term accumulator (SEP only).
 // SHCNT: the list length lives in shared memory (*cnt_s) and is bumped atomically, because two
 // threads (the two column halves of the row) append to the same list.
@@ -166,32 +166,35 @@ __device__ __forceinline__ void k3_filter_chunk(const uint32_t (&v)[32], const u
         }
     }
     if (any[0] | any[1] | any[2] | any[3]) {
-        // which columns: a bit mask built without branches, then a loop over its set bits (usually
-        // one), the value picked out of the registers by a 5-level select tree
-        uint32_t mask = 0;
-        float ip[32];
+        // which columns: only the chains that reported a survivor are looked at again (chain j = the 8
+        // columns c with c % 4 == j): an 8-bit mask built without branches, then a loop over its set
+        // bits (usually one), the value picked out of the 8 registers by a 3-level select tree
 #pragma unroll
-        for (int c = 0; c < 32; c += 4) {
-            const float4 x4 = *reinterpret_cast<const float4*>(xn + c);
-            const float xs[4] = {x4.x, x4.y, x4.z, x4.w};
+        for (int j = 0; j < 4; ++j) {
+            if (any[j]) {
+                uint32_t mask = 0;
+                float ip[8];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                ip[c + j] = SEP ? __uint_as_float(v[c + j]) + __uint_as_float(w[c + j]) : __uint_as_float(v[c + j]);
-                mask |= (fmaf(-2.f, ip[c + j], xs[j]) <= t_cmp) ? (1u << (c + j)) : 0u;
-            }
-        }
-        while (mask) {
-            const int c = __ffs(mask) - 1;
-            mask &= mask - 1;
-            const float ipc = reg_select32<0, 32>(ip, c);
-            const float xv = xn[c];
-            float dist = (qn + xv) - 2.f * ipc;  // oracle rule (2), then clamp
-            dist = dist < 0.f ? 0.f : dist;
-            if (dist <= tau_eff) {
-                const u64 key = make_key(dist, row0 + c);
-                if (key < kth) {
-                    if constexpr (SHCNT) { list[atomicAdd(cnt_s, 1)] = key; }
-                    else { list[cnt] = key; ++cnt; }
+                for (int i = 0; i < 8; ++i) {
+                    const int c = 4 * i + j;
+                    ip[i] = SEP ? __uint_as_float(v[c]) + __uint_as_float(w[c]) : __uint_as_float(v[c]);
+                    mask |= (fmaf(-2.f, ip[i], xn[c]) <= t_cmp) ? (1u << i) : 0u;
+                }
+                while (mask) {
+                    const int i = __ffs(mask) - 1;
+                    mask &= mask - 1;
+                    const int c = 4 * i + j;
+                    const float ipc = reg_select<0, 8, 8>(ip, i);
+                    const float xv = xn[c];
+                    float dist = (qn + xv) - 2.f * ipc;  // oracle rule (2), then clamp
+                    dist = dist < 0.f ? 0.f : dist;
+                    if (dist <= tau_eff) {
+                        const u64 key = make_key(dist, row0 + c);
+                        if (key < kth) {
+                            if constexpr (SHCNT) { list[atomicAdd(cnt_s, 1)] = key; }
+                            else { list[cnt] = key; ++cnt; }
+                        }
+                    }
                 }
             }
         }
