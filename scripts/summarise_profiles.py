@@ -79,11 +79,14 @@ def to_ms(v, u):
 k3_rep = os.path.join(G, "%s_k3_c3.ncu-rep" % R)
 if os.path.exists(k3_rep):
     allm = raw_metrics_all(k3_rep, WANTED)
-    # launch 0 = warm start (64 columns of one tile per CTA); a second launch that small is the warm
-    # start of the NEXT search: the capture count is fixed, the number of segments is not
+    # launch 0 = warm start; the segments of ONE main pass read the bf16 rows once (7.68 GB at C3, or the
+    # 15.36 GB of fp32 rows in the TF32 modes): the capture count is fixed, the number of segments is
+    # not, so cut where the cumulated DRAM read first covers 90 % of one pass
+    cum = 0.0
     for i in range(1, len(allm)):
-        if to_bytes(*allm[i]["dram__bytes_read.sum"]) < 1.5 * to_bytes(*allm[0]["dram__bytes_read.sum"]):
-            allm = allm[:i]
+        cum += to_bytes(*allm[i]["dram__bytes_read.sum"])
+        if cum >= 0.9 * 10e6 * 384 * 2:
+            allm = allm[:i + 1]
             break
     segs = allm[1:] if len(allm) > 1 else allm
     big = max(segs, key=lambda m: to_ms(*m["gpu__time_duration.sum"]))
