@@ -530,7 +530,7 @@ int launch_scan(const void* X, const float* Q, int64_t n, int d, int qt, int k, 
 // k-th candidate's d~; if the LAST candidate is not strictly beyond that zone, rows outside the
 // candidate list could belong to the answer and *flag is raised (the caller's conditional fp32
 // scan then overwrites D / I).  eta covers the fp32 rounding of the d~ sums themselves.
-static constexpr int RERANK_THREADS = 256;
+static constexpr int RERANK_THREADS = 1024;  // 32 warps: one query is one block, and a single query must not wait for 8 warps to walk 232 rows
 __global__ void __launch_bounds__(RERANK_THREADS)
 scan_rerank_kernel(const float* __restrict__ X, const float* __restrict__ Q, int d, int k, int kp,
                    const float* __restrict__ Da, const int64_t* __restrict__ Ia,
