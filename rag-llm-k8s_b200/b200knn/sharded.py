@@ -47,7 +47,8 @@ class ShardedIndexFlatL2:
             self.device = None
             self.local = _local
             self._tdev = torch.device("cpu")
-            self._flag = None
+            # a stand-in may bring its own overflow word (int32[2] tensor) to exercise the repeat protocol
+            self._flag = getattr(_local, "screen_flag", None)
         self._merge = _merge
         self._tensor_mode = 0
         self._path = 0

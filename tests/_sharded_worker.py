@@ -42,6 +42,32 @@ class OracleShard:
         return torch.from_numpy(D), torch.from_numpy(I)
 
 
+class OverflowingShard(OracleShard):
+    """Stand-in whose cheap screen 'overflows' on ONE rank: it raises its flag word and returns rubbish,
+    as the CUDA shard does when its screening lists cannot hold every candidate.  With tensor_mode 4 it
+    overflows again (if told to); with path 1 (the scan) it answers exactly."""
+
+    def __init__(self, d, bad_rank, fail_mode4):
+        super().__init__(d)
+        self.screen_flag = torch.zeros(2, dtype=torch.int32)
+        self.opts = {"tensor_mode": 0, "path": 0}
+        self.bad = bad_rank
+        self.fail_mode4 = fail_mode4
+        self.calls = []
+
+    def set_option(self, key, value):
+        self.opts[key] = int(value)
+
+    def search(self, xq, k):
+        self.calls.append((self.opts["tensor_mode"], self.opts["path"]))
+        exact = self.opts["path"] == 1 or (self.opts["tensor_mode"] == 4 and not self.fail_mode4)
+        if self.bad and not exact:
+            self.screen_flag[0] = 1
+            nq = np.asarray(xq).shape[0]
+            return torch.zeros((nq, k)), torch.zeros((nq, k), dtype=torch.int64)
+        return super().search(xq, k)
+
+
 def oracle_merge(Dcat, Icat):
     D, I = O.merge(Dcat.numpy(), Icat.numpy())
     return torch.from_numpy(D), torch.from_numpy(I)
@@ -81,6 +107,18 @@ def main():
     D, I = idx.search(q, 4)
     assert np.all(I == -1) and np.all(D == O.FLT_MAX)
     assert split_range(10, 4, 3) == (9, 10) and split_range(2, 4, 3) == (2, 2)
+    # screening overflow on the last rank only: its flag travels with the all-gather, EVERY rank repeats
+    # (3xTF32 screen, then the scan), the options are restored, the answer is the single index's
+    for fail_mode4, expect in ((False, [(0, 0), (4, 0)]), (True, [(0, 0), (4, 0), (0, 1)])):
+        shard = OverflowingShard(d, bad_rank=(rank == world - 1), fail_mode4=fail_mode4)
+        idx2 = ShardedIndexFlatL2(d, _local=shard, _merge=oracle_merge)
+        idx2.add(x)
+        q = O.synth(14, 0, 6, d)
+        D, I = idx2.search(q, 7)
+        Dr, Ir = O.search(x, q, 7)
+        assert np.array_equal(I, Ir) and np.array_equal(D, Dr), (rank, fail_mode4)
+        assert shard.calls == expect, (rank, shard.calls)
+        assert shard.opts == {"tensor_mode": 0, "path": 0}
     dist.barrier()
     if rank == 0:
         print("SHARDED-OK world=%d" % world)
