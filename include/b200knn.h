@@ -152,7 +152,9 @@ B2K_API int b2k_search_rows_noalloc(int device, const float* x_dev, int64_t n, i
  * "screen_flag_ptr" (device address of a caller-owned 32-bit word, 0 = off: batched searches then
  * do not synchronise; they raise the word if the screening lists could not hold every candidate,
  * and the caller must check it after its own synchronisation and repeat that search with
- * "tensor_mode" = 1 -- the row-sharded index ships the word with its all-gather).
+ * "tensor_mode" = 1 -- the row-sharded index ships the word with its all-gather),
+ * "tensor_probe" (measurement only: 1 = batched searches run their main pass with the selection filter
+ * shut -- the dense rate of the MMA pipeline for the chosen "tensor_mode"; the results are all padding).
  * Unknown key -> B2K_EINVAL. */
 B2K_API int b2k_set_option(b2k_index* h, const char* key, int64_t value);
 

@@ -386,3 +386,13 @@ ORC_API int orc_num_threads(void) {
     return 1;
 #endif
 }
+
+/* torchrun exports OMP_NUM_THREADS=1 to its workers; the timed CPU baseline and the parity
+ * checker put the host cores back to work with this. */
+ORC_API void orc_set_num_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}

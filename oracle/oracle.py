@@ -39,6 +39,8 @@ def lib():
         L.orc_synth.argtypes = [ctypes.c_uint64, ctypes.c_int64, ctypes.c_int64, ctypes.c_int, fp]
         L.orc_synth.restype = None
         L.orc_num_threads.restype = ctypes.c_int
+        L.orc_set_num_threads.argtypes = [ctypes.c_int]
+        L.orc_set_num_threads.restype = None
         L.orc_blas_begin.argtypes = [ctypes.c_int64, ctypes.c_int64]
         L.orc_blas_begin.restype = ctypes.c_void_p
         L.orc_norms.argtypes = [fp, ctypes.c_int64, ctypes.c_int, fp]
@@ -128,6 +130,19 @@ def num_threads():
     return lib().orc_num_threads()
 
 
+def use_all_cores():
+    """Undo a launcher's OMP_NUM_THREADS=1 (torchrun exports it) for the oracle's OpenMP loops and
+    for the BLAS behind `search_blas`; returns the thread count now in use."""
+    n = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    lib().orc_set_num_threads(n)
+    try:
+        import torch
+        torch.set_num_threads(n)
+    except Exception:
+        pass
+    return num_threads()
+
+
 def truth_f64(x, q, k, chunk=262144):
     """Independent ground truth: float64 brute force, (distance, id) lexicographic top-k.
 
@@ -167,6 +182,81 @@ def dist_f64(x, q, ids):
         diff = x[ids[i][m]] - q[i][None, :]
         out[i][m] = (diff * diff).sum(1)
     return out
+
+
+def stream_search(rows, n, d, q, k, chunk=1_000_000, mode=MODE_FAISS):
+    """`search` over a row set too large to hold at once: `rows(j0, nb)` yields rows [j0, j0+nb) as
+    float32 (e.g. `lambda j0, nb: synth(seed, j0, nb, d)`), each chunk is searched with the rule the
+    WHOLE query batch selects (so chunking does not change the numerics: every distance depends on
+    its own row only) and the per-chunk results are combined with `merge`.  Same answer as one call
+    on all n rows."""
+    q = np.ascontiguousarray(q, dtype=np.float32)
+    if mode == MODE_FAISS:
+        mode = MODE_EXPAND if q.shape[0] >= 20 else MODE_DIRECT
+    best = None
+    for j0 in range(0, n, chunk):
+        nb = min(chunk, n - j0)
+        D, I = search(rows(j0, nb), q, k, mode)
+        I = np.where(I >= 0, I + j0, I)
+        best = (D, I) if best is None else merge(np.stack([best[0], D]), np.stack([best[1], I]))
+    if best is None:
+        best = search(np.zeros((0, d), np.float32), q, k, mode)
+    return best
+
+
+def compare_knn(D, I, Dref, Iref, row_of, q, rtol=1e-5, expanded=False):
+    """Non-raising form of the parity rule (tests/util.py: assert_knn_matches) for result sets over a
+    row set that is not in host memory: `row_of(ids)` returns the float32 rows of the given global
+    ids.  Distances: |D - Dref| <= rtol * scale (scale = |Dref|, or max(|Dref|, |q|^2 + |x|^2) where
+    the reference used the norm expansion); ids: equal, or the float64 distances of the ids that
+    differ agree position by position within twice that tolerance (ties at rounding level).
+    Returns {"ok", "max_rel_err", "rows_with_other_ids", "why"}."""
+    D = np.asarray(D); I = np.asarray(I)
+    q = np.asarray(q, dtype=np.float32)
+    out = {"ok": False, "max_rel_err": None, "rows_with_other_ids": 0, "why": ""}
+    if D.shape != Dref.shape or I.shape != Iref.shape:
+        out["why"] = "shape"; return out
+    pad = Iref < 0
+    if not np.array_equal(I < 0, pad) or not np.all(D[pad] == FLT_MAX):
+        out["why"] = "padding differs"; return out
+    ids = np.unique(np.concatenate([I[~pad].ravel(), Iref[~pad].ravel()]))
+    xs = row_of(ids).astype(np.float64) if ids.size else np.zeros((0, q.shape[1]))
+    pos = lambda a: np.searchsorted(ids, a)
+    qn = (q.astype(np.float64) ** 2).sum(1)
+    xn = (xs * xs).sum(1)
+    scale = np.abs(Dref.astype(np.float64))
+    if expanded and ids.size:
+        scale = np.maximum(scale, qn[:, None] + xn[pos(np.where(pad, ids[0], Iref))])
+    err = np.abs(D.astype(np.float64) - Dref.astype(np.float64))
+    ok = ~pad
+    rel = err[ok] / np.maximum(scale[ok], 1e-30)
+    out["max_rel_err"] = float(rel.max()) if rel.size else 0.0
+    if rel.size and rel.max() > rtol:
+        out["why"] = "distance beyond tolerance"; return out
+    if np.any(np.diff(np.where(pad, np.inf, D.astype(np.float64)), axis=1) < 0):
+        out["why"] = "D not ascending"; return out
+    for i in np.where((I != Iref).any(1))[0]:
+        out["rows_with_other_ids"] += 1
+        a, b = I[i][~pad[i]], Iref[i][~pad[i]]
+        if len(set(a.tolist())) != len(a):
+            out["why"] = "duplicate ids in row %d" % i; return out
+        da = ((xs[pos(a)] - q[i].astype(np.float64)) ** 2).sum(1)
+        db = ((xs[pos(b)] - q[i].astype(np.float64)) ** 2).sum(1)
+        t = rtol * np.maximum(np.maximum(da, db), (qn[i] + xn[pos(a)]) if expanded else 0) + 1e-30
+        if np.any(np.abs(da - db) > 2 * t):
+            out["why"] = "row %d: ids differ beyond the tie tolerance" % i; return out
+    out["ok"] = True
+    return out
+
+
+def synth_rows(seed, d):
+    """row_of callable for compare_knn over the synthetic stream."""
+    def row_of(ids):
+        out = np.empty((len(ids), d), np.float32)
+        for j, g in enumerate(ids):
+            out[j] = synth(seed, int(g), 1, d)[0]
+        return out
+    return row_of
 
 
 # --------------------------------------------------------------------------------------

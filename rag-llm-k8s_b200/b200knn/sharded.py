@@ -122,6 +122,10 @@ class ShardedIndexFlatL2:
         seg = torch.searchsorted(ls, I.clamp(min=0), right=True) - 1
         return torch.where(I >= 0, I + delta[seg], I)
 
+    def to_global(self, I):
+        """Shard-local row ids (as `self.local.search` returns them) -> global row ids."""
+        return self._to_global(I)
+
     def search(self, x, k):
         """(D, I) of the k nearest rows over ALL shards; identical on every rank."""
         k = int(k)

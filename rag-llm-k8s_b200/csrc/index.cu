@@ -67,6 +67,7 @@ struct b2k_index {
     int opt_scan_rows = 0;  // nq < 20 scan: 0 auto (bf16 copies + exact re-rank for large indexes), 1 fp32 rows, 2 bf16 copies
     bool last_scan_bf = false;
     int opt_epi = 0;
+    int opt_probe = 0;
     int opt_tensor_mode = 0;  // 0 auto (bf16 screening + exact re-rank where d % 8 == 0 and memory allows, else TF32 screening), 1 3xTF32, 2 TF32 screening, 3 bf16 screening, 4 3xTF32 screening
     int64_t stat_screen_fallbacks = 0;
     int screen_fail_streak = 0;      // consecutive searches whose cheap screen overflowed
@@ -185,6 +186,8 @@ int grow(b2k_index* h, int64_t need_rows) {
         return B2K_ENOMEM;
     }
     if (h->ntotal > 0) {
+        // rows may still be landing on a caller's stream (on-device add): order this copy behind them
+        B2K_CUDA(cudaStreamWaitEvent(h->stream, h->ev_rows, 0));
         B2K_CUDA(cudaMemcpyAsync(nx, h->x, (size_t)h->ntotal * row_bytes, cudaMemcpyDeviceToDevice, h->stream));
         B2K_CUDA(cudaMemcpyAsync(nn, h->norms, (size_t)h->ntotal * sizeof(float), cudaMemcpyDeviceToDevice, h->stream));
         if (nl) B2K_CUDA(cudaMemcpyAsync(nl, h->xlo, (size_t)h->ntotal * row_bytes, cudaMemcpyDeviceToDevice, h->stream));
@@ -193,7 +196,6 @@ int grow(b2k_index* h, int64_t need_rows) {
     }
     cudaFree(h->x); cudaFree(h->norms); cudaFree(h->xlo); cudaFree(h->xbf);
     h->x = nx; h->norms = nn; h->xlo = nl; h->xbf = nb; h->capacity = cap;
-    if (h->k3) k3_invalidate_maps(h->k3);
     return B2K_OK;
 }
 
@@ -214,7 +216,6 @@ int enable_lo(b2k_index* h, cudaStream_t st) {
         if (e != cudaSuccess) { cudaGetLastError(); set_error("cudaMalloc for TF32 residual rows failed: %s", cudaGetErrorString(e)); return B2K_ENOMEM; }
     }
     h->lo_enabled = true;
-    if (h->k3) k3_invalidate_maps(h->k3);
     if (h->ntotal > 0) return launch_row_prep(h->x, h->ntotal, h->d, h->norms, h->xlo, nullptr, st);
     return B2K_OK;
 }
@@ -409,6 +410,9 @@ int b2k_set_option(b2k_index* h, const char* key, int64_t value) {
     } else if (!strcmp(key, "scan_rows")) {
         if (value < 0 || value > 2) { set_error("option scan_rows must be 0 (auto), 1 (fp32 rows) or 2 (bf16 copies + exact re-rank)"); return B2K_EINVAL; }
         h->opt_scan_rows = (int)value;
+    } else if (!strcmp(key, "tensor_probe")) {
+        h->opt_probe = value != 0;
+        if (h->k3) k3_set_probe(h->k3, h->opt_probe);
     } else if (!strcmp(key, "timing")) {
         h->opt_timing = value != 0;
         if (h->k3) k3_set_timing(h->k3, h->opt_timing != 0);
@@ -474,7 +478,6 @@ int b2k_reset(b2k_index* h) {
     h->bf_nomem = false;
     h->screen_fail_streak = 0;
     h->ntotal = h->capacity = 0;
-    if (h->k3) k3_invalidate_maps(h->k3);
     B2K_CUDA(cudaMemset(h->done, 0, 256));
     return B2K_OK;
 }
@@ -491,6 +494,9 @@ int b2k_add(b2k_index* h, int64_t n, const float* x, int on_device, void* stream
     cudaStream_t st = on_device ? (cudaStream_t)stream : h->stream;
     float* dst = h->x + h->ntotal * (int64_t)h->d;
     size_t bytes = (size_t)n * h->d * sizeof(float);
+    // ev_rows is one event: before it is re-recorded on this stream, this stream takes over the
+    // dependency on whatever stream recorded it last, so "all rows so far" stays one wait
+    B2K_CUDA(cudaStreamWaitEvent(st, h->ev_rows, 0));
     B2K_CUDA(cudaMemcpyAsync(dst, x, bytes, on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, st));
     rc = prep_new_rows(h, h->ntotal, n, st);
     if (rc) return rc;
@@ -510,10 +516,12 @@ int b2k_add_synthetic(b2k_index* h, int64_t n, uint64_t seed, int64_t first_row)
     DeviceGuard g(h->device);
     int rc = grow(h, h->ntotal + n);
     if (rc) return rc;
+    B2K_CUDA(cudaStreamWaitEvent(h->stream, h->ev_rows, 0));
     rc = launch_synth(seed, first_row, n, h->d, h->x + h->ntotal * (int64_t)h->d, h->stream);
     if (rc) return rc;
     rc = prep_new_rows(h, h->ntotal, n, h->stream);
     if (rc) return rc;
+    B2K_CUDA(cudaEventRecord(h->ev_rows, h->stream));
     h->ntotal += n;
     B2K_CUDA(cudaStreamSynchronize(h->stream));
     return B2K_OK;
@@ -536,6 +544,7 @@ int b2k_get_rows(const b2k_index* h, int64_t i0, int64_t n, float* out, int on_d
     if (i0 + n > h->ntotal) { set_error("b2k_get_rows: rows [%lld,%lld) out of range (ntotal=%lld)", (long long)i0, (long long)(i0 + n), (long long)h->ntotal); return B2K_EINVAL; }
     if (n == 0) return B2K_OK;
     DeviceGuard g(h->device);
+    B2K_CUDA(cudaStreamWaitEvent(h->stream, h->ev_rows, 0));
     B2K_CUDA(cudaMemcpyAsync(out, h->x + i0 * (int64_t)h->d, (size_t)n * h->d * sizeof(float),
                              on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, h->stream));
     B2K_CUDA(cudaStreamSynchronize(h->stream));
@@ -569,7 +578,10 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
     size_t q_bytes = align256((size_t)nq * h->d * sizeof(float));
     size_t d_bytes = align256((size_t)nq * kk * sizeof(float));
     size_t i_bytes = align256((size_t)nq * kk * sizeof(int64_t));
-    size_t io_bytes = on_device ? 0 : q_bytes + d_bytes + i_bytes;
+    // device queries that are not 16-byte aligned (a torch view with an odd storage offset) are staged:
+    // the re-rank kernels and the TMA maps read query rows with 128-bit accesses
+    const bool stage_q = on_device && (reinterpret_cast<uintptr_t>(xq) & 15) != 0;
+    size_t io_bytes = on_device ? (stage_q ? q_bytes : 0) : q_bytes + d_bytes + i_bytes;
     size_t scratch = 0;
     if (h->ntotal > 0) {
         if (want_tc) {
@@ -603,6 +615,10 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
         Dd = reinterpret_cast<float*>(wsb + q_bytes);
         Id = reinterpret_cast<int64_t*>(wsb + q_bytes + d_bytes);
     }
+    if (stage_q) {
+        B2K_CUDA(cudaMemcpyAsync(wsb, xq, (size_t)nq * h->d * sizeof(float), cudaMemcpyDeviceToDevice, st));
+        qd = reinterpret_cast<const float*>(wsb);
+    }
     unsigned char* ws_tail = wsb + io_bytes;
 
     if (h->ntotal == 0) {
@@ -629,6 +645,7 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
             if (!rc) k3_set_segments(h->k3, h->opt_segments);
             if (!rc) k3_set_epi_halves(h->k3, h->opt_epi);
             if (!rc) k3_set_ext_flag(h->k3, h->opt_flag_ptr);
+            if (!rc) k3_set_probe(h->k3, h->opt_probe);
         }
         if (!rc) h->last_path = 2;
         // like faiss (query blocks of 4096), long batches go through in chunks: the candidate-list
@@ -765,6 +782,7 @@ int b2k_write(const b2k_index* hc, const char* path) {
     size_t total = (size_t)h->ntotal * h->d * sizeof(float), done = 0;
     if (!rc && total) {
         rc = ensure_pin(h, total < IO_CHUNK ? total : IO_CHUNK);
+        if (!rc && cudaStreamWaitEvent(h->stream, h->ev_rows, 0) != cudaSuccess) { set_error("b2k_write: cudaStreamWaitEvent failed"); rc = B2K_ECUDA; }
         while (!rc && done < total) {
             size_t n = total - done < IO_CHUNK ? total - done : IO_CHUNK;
             cudaError_t e = cudaMemcpyAsync(h->pin, reinterpret_cast<unsigned char*>(h->x) + done, n, cudaMemcpyDeviceToHost, h->stream);
@@ -806,6 +824,7 @@ int b2k_write_append(const b2k_index* hc, const char* path, int64_t first_row) {
     size_t total = (size_t)(h->ntotal - first_row) * row_bytes, done = 0;
     if (!rc && total) {
         rc = ensure_pin(h, total < IO_CHUNK ? total : IO_CHUNK);
+        if (!rc && cudaStreamWaitEvent(h->stream, h->ev_rows, 0) != cudaSuccess) { set_error("b2k_write_append: cudaStreamWaitEvent failed"); rc = B2K_ECUDA; }
         const unsigned char* src = reinterpret_cast<const unsigned char*>(h->x) + (size_t)first_row * row_bytes;
         while (!rc && done < total) {
             size_t n = total - done < IO_CHUNK ? total - done : IO_CHUNK;

@@ -11,7 +11,6 @@ bool k3_supported(int d, int k);
 size_t k3_scratch_bytes(int sm_count, int d, int64_t nq, int k);
 int k3_create(K3State** out, int device, int sm_count);
 void k3_destroy(K3State* s);
-void k3_invalidate_maps(K3State* s);  // row storage moved / resized
 // D[nq][k], I[nq][k] (device) <- k nearest of rows [0,n) for each of the nq queries (device).
 // mode 1: 3xTF32 (needs xlo).  mode 2: TF32 screening + exact fp32 re-rank (max_norm_bits = float
 // bits of the largest squared row norm).  mode 3: bf16 screening + exact re-rank (needs xbf, the
@@ -34,6 +33,9 @@ void k3_set_epi_halves(K3State* s, int nh); // epilogue warps: 0 auto, 1 four (o
 // flag != null: the screening modes raise *flag (device word, never reset by the library) instead of
 // synchronising and reporting through *overflowed; the caller checks it and repeats the search with mode 1
 void k3_set_ext_flag(K3State* s, unsigned int* flag);
+// dense-rate probe: the main pass runs as usual (TMA, MMAs, TMEM loads, the filter's arithmetic) but no
+// key ever passes, so its time is the kernel's ceiling for that product kind; results are all padding
+void k3_set_probe(K3State* s, int on);
 int k3_last_kernel_ms(K3State* s, float* ms);
 int k3_last_mode(const K3State* s);  // 1 = 3xTF32, 2 = TF32 screening + exact re-rank, 3 = bf16 screening + exact re-rank
 

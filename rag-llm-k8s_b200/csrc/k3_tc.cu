@@ -82,6 +82,7 @@ struct K3Params {
     int static_qb_mod;  // warm-start pass: CTA (pair) c only takes the query blocks qb with qb % static_qb_mod == c % static_qb_mod
     int tile_cols;      // columns (rows of the tile) the epilogue looks at: 256, or fewer in the first warm-start pass
     int64_t static_tile0;
+    int probe;          // 1: dense-rate probe -- every query row is treated as padding, so the filter never fires
 };
 
 static constexpr int K3_NSCHED = 4;  // depth of the unit-id ring between the scheduler and the other roles
@@ -417,7 +418,7 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
         auto qi_of = [&](int qb) -> int64_t { return (int64_t)qb * (K3_BM * CG) + (int64_t)rank * K3_BM + row; };
         auto load_state = [&](int qb, QState& S) {
             const int64_t sidx = sidx_of(qb), qi = qi_of(qb);
-            const bool valid = qi < p.nq;
+            const bool valid = qi < p.nq && !p.probe;
             S.cnt = __ldcg(p.cnt + sidx);
             S.tau = __ldcg(p.tau + sidx);
             S.kth = __ldcg(p.kth + sidx);
@@ -436,7 +437,7 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
             const int64_t t = cur >> 8;  // units arrive as (tile << 8) | query block
             const int qb = (int)(cur & 255);
             const int64_t qi = qi_of(qb);
-            const bool valid = qi < p.nq;
+            const bool valid = qi < p.nq && !p.probe;
             const int64_t sidx = sidx_of(qb);
             int cnt = S.cnt;
             float tau = S.tau;
@@ -856,10 +857,15 @@ k4_merge_kernel(const K3Params p, int cg, int ncta, int threshold_only, int list
 // d~ <= T + 2 sigma_q, and K6 computes the exact fp32 distance (direct differences, as the scan
 // kernel does) of those few hundred rows per query and selects the final k.  The result is exact;
 // the tensor cores only decide which rows are worth an exact look.
+static constexpr float K3_ROUND_SLACK = 8.f * 1.1920929e-7f;  // 2 * (4 ulps) of |q|^2 + max|x|^2
 __global__ void k3_slack_kernel(int64_t nq, const float* __restrict__ qn, const unsigned int* __restrict__ max_norm_bits,
                                 float coef, float* __restrict__ slack2) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < nq) slack2[i] = coef * sqrtf(qn[i]) * sqrtf(__uint_as_float(*max_norm_bits));
+    if (i >= nq) return;
+    const float mx2 = __uint_as_float(*max_norm_bits);
+    // + the fp32 rounding of d~ = (|q|^2 + |x|^2) - 2 ip itself and of the two norms (a few ulps of
+    // |q|^2 + |x|^2): it is all that is left when q = 0 or |q| >> max|x|, where the product term vanishes
+    slack2[i] = coef * sqrtf(qn[i]) * sqrtf(mx2) + K3_ROUND_SLACK * (qn[i] + mx2);
 }
 
 // bf16 screening: q~, x~ are the bf16 roundings.  q.x - q~.x~ = (q - q~).x + q~.(x - x~), so by
@@ -875,7 +881,7 @@ __global__ void k3_slack_bf16_kernel(int64_t nq, const float* __restrict__ qn, c
     const float nqv = sqrtf(qn[i]), eq = sqrtf(slack2[i]);
     const float mx = sqrtf(__uint_as_float(*max_norm_bits)), ex = sqrtf(__uint_as_float(*max_err_bits));
     const float sigma = 2.f * 1.02f * (eq * mx + 1.004f * nqv * ex) + acc_coef * nqv * mx;
-    slack2[i] = 2.f * sigma;
+    slack2[i] = 2.f * sigma + K3_ROUND_SLACK * (qn[i] + mx * mx);  // rounding of d~ and of the norms, see k3_slack_kernel
 }
 
 template <int K4_P>
@@ -966,6 +972,7 @@ struct K3State {
     unsigned int* ext_flag = nullptr;  // caller-owned overflow word (deferred screening check)
     int epi_halves = 0;  // 0 auto (2 where available), 1 four epilogue warps, 2 eight
     int segments = 1;  // cut the main pass into segments with a bound refresh in between (0 = one launch)
+    int probe = 0;     // dense-rate probe (option "tensor_probe"): the pass runs with the filter shut, results are padding
 };
 
 static int k3_P(int k) { return next_pow2(k + K3_BN); }
@@ -1041,13 +1048,15 @@ int k3_create(K3State** out, int device, int sm_count) {
         return B2K_ECUDA;
     }
     s->encode = (EncodeTiledFn)fn;
-    cudaEventCreate(&s->ev0);
-    cudaEventCreate(&s->ev1);
-    if (cudaMallocHost(reinterpret_cast<void**>(&s->flag_host), 64) != cudaSuccess) {
-        set_error("cudaMallocHost failed");
-        cudaEventDestroy(s->ev0); cudaEventDestroy(s->ev1);
+    e = cudaEventCreate(&s->ev0);
+    if (e == cudaSuccess) e = cudaEventCreate(&s->ev1);
+    if (e == cudaSuccess) e = cudaMallocHost(reinterpret_cast<void**>(&s->flag_host), 64);
+    if (e != cudaSuccess) {
+        set_error("tensor kernel state: %s", cudaGetErrorString(e));
+        if (s->ev0) cudaEventDestroy(s->ev0);
+        if (s->ev1) cudaEventDestroy(s->ev1);
         delete s;
-        return B2K_ENOMEM;
+        return e == cudaErrorMemoryAllocation ? B2K_ENOMEM : B2K_ECUDA;
     }
     *out = s;
     return B2K_OK;
@@ -1061,14 +1070,13 @@ void k3_destroy(K3State* s) {
     delete s;
 }
 
-void k3_invalidate_maps(K3State*) {}  // maps are re-encoded on every search (host-side, ~1 us each)
-
 void k3_set_timing(K3State* s, bool on) { s->timing = on; }
 void k3_set_cta_group(K3State* s, int cg) { s->cg = (cg == 1 || cg == 2) ? cg : 0; }
 void k3_set_sep_mode(K3State* s, int m) { s->sep_mode = m; }
 void k3_set_segments(K3State* s, int on) { s->segments = on; }
 void k3_set_epi_halves(K3State* s, int nh) { s->epi_halves = nh; }
 void k3_set_ext_flag(K3State* s, unsigned int* flag) { s->ext_flag = flag; }
+void k3_set_probe(K3State* s, int on) { s->probe = on != 0; }
 int k3_last_mode(const K3State* s) { return s->last_mode; }
 
 int k3_last_kernel_ms(K3State* s, float* ms) {
@@ -1187,6 +1195,7 @@ int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, con
     p.static_qb_mod = 1;
     p.static_tile0 = 0;
     p.tile_cols = K3_BN;
+    p.probe = s->probe;
 
     // queries: norms (+ TF32 residual rows for the exact mode; K1 reused), screening slack, list state reset
     int rc = launch_row_prep(q, nq, d, const_cast<float*>(p.qn), onep ? nullptr : qlo, nullptr, st);

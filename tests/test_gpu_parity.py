@@ -779,3 +779,70 @@ def test_nonfinite_rows_and_queries_on_the_tensor_path(faiss):
         xs = x.copy()
         xs[[5, 17, 300]] = 1e6                       # far away, finite: same neighbours for the oracle
         assert_knn_matches(D[ok], I[ok], xs, q[ok], 8, expanded=True, what="nonfinite mode=%d" % mode)
+
+
+def test_device_adds_are_ordered_before_growth_write_and_readback(faiss, tmp_path):
+    """Rows added from a CUDA tensor land on the caller's stream; a later add that regrows the
+    storage, write_index and reconstruct_n run on the handle's own stream and must wait for them
+    (rag.py:80 add -> :82 write_index, with the rows coming from a device-side encoder)."""
+    import torch
+    d = 256
+    side = torch.cuda.Stream()
+    idx = faiss.IndexFlatL2(d)
+    a = faiss.synth(31, 0, 400_000, d)
+    b = faiss.synth(31, 400_000, 700_000, d)
+    torch.cuda.synchronize()
+    with torch.cuda.stream(side):
+        # keep the side stream busy so the row copy is still pending when the host moves on
+        junk = torch.empty(1 << 28, dtype=torch.float32, device="cuda")
+        for _ in range(4):
+            junk.normal_()
+        idx.add(a)                       # on-device add, enqueued on `side`
+    idx.add(b.cpu().numpy())             # host add on the handle's stream: grows (capacity 400k -> 1.1M)
+    path = str(tmp_path / "ordered.index")
+    faiss.write_index(idx, path)
+    got = idx.reconstruct_n(0, idx.ntotal)
+    want = O.synth(31, 0, 1_100_000, d)
+    assert np.array_equal(got, want)
+    dd, rows = O.read_ixf2(path)
+    assert dd == d and np.array_equal(rows, want)
+    del junk
+
+
+def test_misaligned_device_queries(faiss):
+    """A torch view whose storage offset is not a multiple of 16 bytes is still a valid query batch."""
+    import torch
+    d, n, k = 64, 600_000, 10      # 600k x 64 = 38M elements: the bf16 scan + re-rank serves nq < 20
+    idx = faiss.IndexFlatL2(d)
+    x = O.synth(3, 0, n, d)
+    idx.add(x)
+    for nq in (2, 40):
+        q = O.synth(4, 0, nq, d)
+        buf = torch.empty(nq * d + 1, dtype=torch.float32, device="cuda")
+        qv = buf[1:].view(nq, d)
+        qv.copy_(torch.from_numpy(q))
+        assert qv.data_ptr() % 16 != 0
+        D, I = idx.search(qv, k)
+        assert_knn_matches(D.cpu().numpy(), I.cpu().numpy(), x, q, k, expanded=nq >= 20, what="misaligned nq=%d" % nq)
+
+
+def test_zero_and_far_queries_on_the_screening_path(faiss):
+    """The screening slack must also cover the fp32 rounding of the approximate distance itself: with
+    q = 0, or |q| far beyond every row, the product term of the slack vanishes or is dwarfed."""
+    rng = np.random.default_rng(5)
+    n, d, k = 200_000, 64, 10
+    x = rng.standard_normal((n, d)).astype(np.float32)
+    x[::7] *= 1.0 + 1e-7 * rng.standard_normal((len(x[::7]), 1)).astype(np.float32)   # near-ties in norm
+    q = rng.standard_normal((32, d)).astype(np.float32)
+    q[0] = 0.0
+    q[1] = 1e3
+    q[2] = -3e4
+    idx = _build(faiss, x)
+    for mode in (3, 2, 4):
+        idx.set_option("path", 2)
+        idx.set_option("tensor_mode", mode)
+        D, I = idx.search(q, k)
+        Dt, It = O.truth_f64(x, q, k)
+        d64 = O.dist_f64(x, q, I)
+        assert np.all(np.abs(d64 - Dt) <= 1e-5 * np.maximum(Dt, 1e-30) + 1e-30), "mode %d: a nearer row was missed" % mode
+        assert_knn_matches(D, I, x, q, k, expanded=True, what="zero/far queries, mode %d" % mode)

@@ -132,3 +132,55 @@ def test_blas_backed_variant_matches_plain_restatement():
     D2, I2 = O.search_blas(x, q, 10, db_bs=4096)
     assert np.allclose(D1, D2, rtol=1e-5, atol=1e-4)
     assert (I1 == I2).mean() > 0.99
+
+
+def test_streaming_search_equals_one_call_and_compare_knn_sees_a_missed_neighbour():
+    """O.stream_search (the full-size checker of tests/test_gpu_fullsize.py and bench.py's parity_check)
+    gives the answer of one call on all rows under both numerics; O.compare_knn accepts it and
+    rejects a result with a wrong neighbour, a wrong distance or wrong padding."""
+    d, n, k = 48, 30011, 10
+    x = O.synth(7, 0, n, d)
+    rows = lambda j0, nb: O.synth(7, j0, nb, d)
+    for nq in (3, 25):
+        q = O.synth(8, 0, nq, d)
+        D, I = O.search(x, q, k)
+        Ds, Is = O.stream_search(rows, n, d, q, k, chunk=4096)
+        assert np.array_equal(D, Ds) and np.array_equal(I, Is)
+        ok = O.compare_knn(D, I, Ds, Is, O.synth_rows(7, d), q, expanded=nq >= 20)
+        assert ok["ok"] and ok["rows_with_other_ids"] == 0
+        I2 = I.copy()
+        I2[1, 4] = next(r for r in range(n) if r not in set(I[1].tolist()))
+        assert not O.compare_knn(D, I2, Ds, Is, O.synth_rows(7, d), q, expanded=nq >= 20)["ok"]
+        D2 = D.copy()
+        D2[0, 0] *= 1.001
+        assert not O.compare_knn(D2, I, Ds, Is, O.synth_rows(7, d), q, expanded=nq >= 20)["ok"]
+    Dp, Ip = O.stream_search(rows, 4, d, O.synth(8, 0, 2, d), k, chunk=3)
+    assert (Ip[:, 4:] == -1).all() and (Dp[:, 4:] == O.FLT_MAX).all()
+    assert O.compare_knn(Dp, Ip, Dp, Ip, O.synth_rows(7, d), O.synth(8, 0, 2, d))["ok"]
+    Ibad = Ip.copy(); Ibad[0, 3] = -1
+    assert not O.compare_knn(Dp, Ibad, Dp, Ip, O.synth_rows(7, d), O.synth(8, 0, 2, d))["ok"]
+
+
+def test_oracle_agrees_with_sklearn_brute_force():
+    """A third implementation the builder did not write: scikit-learn's brute-force
+    NearestNeighbors with the squared-euclidean metric, on unit-norm rows (the rag.py:55 distribution)
+    and on N(0,1) rows.  Ids must agree except at float ties; distances within 1e-5 of the magnitudes."""
+    sk = pytest.importorskip("sklearn.neighbors")
+    rng = np.random.default_rng(3)
+    for unit in (False, True):
+        x = rng.standard_normal((5000, 96)).astype(np.float32)
+        q = rng.standard_normal((40, 96)).astype(np.float32)
+        if unit:
+            x /= np.linalg.norm(x, axis=1, keepdims=True)
+            q /= np.linalg.norm(q, axis=1, keepdims=True)
+        nn = sk.NearestNeighbors(n_neighbors=10, algorithm="brute", metric="sqeuclidean").fit(x.astype(np.float64))
+        Dk, Ik = nn.kneighbors(q.astype(np.float64))
+        for qq, mode in ((q, O.MODE_EXPAND), (q[:7], O.MODE_DIRECT)):
+            D, I = O.search(x, qq, 10, mode)
+            m = len(qq)
+            scale = np.maximum(Dk[:m], (qq.astype(np.float64) ** 2).sum(1)[:, None] + 1.0 if mode == O.MODE_EXPAND else Dk[:m])
+            assert np.all(np.abs(D - Dk[:m]) <= 1e-5 * scale)
+            same = (I == Ik[:m])
+            # where the order differs, the two distances involved are equal at rounding level
+            assert np.all(np.abs(D[~same] - Dk[:m][~same]) <= 1e-5 * scale[~same])
+            assert same.mean() > 0.99

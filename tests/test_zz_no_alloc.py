@@ -2,8 +2,10 @@
 (an inference engine has already reserved HBM, or the calling thread cannot afford the
 device-wide synchronisation of cudaMalloc).  Its scratch is a fixed array inside the library, so
 the checks here are: same answers as the regular entry point (b2k_search on the scan path, i.e.
-the same kernel, so the comparison is exact) on two calls in a row that reuse that array, the
-documented size limit is refused loudly, and the call really allocates nothing.
+the same kernel, so the comparison is exact) on two calls in a row that reuse that array -- and,
+since that compares the kernel with itself, the same answers as the CPU oracle under the parity
+rule of the other tests --, the documented size limit is refused loudly, and the call really
+allocates nothing.
 
 Collected last on purpose (file name): a run that stops at the first failure has then already
 run every other test.  Passes alone in a fresh process and after the other tests."""
@@ -11,6 +13,9 @@ import ctypes as C
 
 import numpy as np
 import pytest
+
+from oracle import oracle as O
+from util import assert_knn_matches
 
 pytestmark = pytest.mark.gpu
 
@@ -48,6 +53,8 @@ def test_noalloc_entry_point_matches_regular_search():
     assert rc == 0, _lib.last_error()
     Dr, Ir = ref.search(q1, 10)
     assert torch.equal(I1, Ir) and torch.equal(D1, Dr)
+    xh = O.synth(1234, 0, 300_000, 384)          # the same rows on the CPU, for the oracle
+    assert_knn_matches(D1.cpu().numpy(), I1.cpu().numpy(), xh, O.synth(5678, 0, 1, 384), 10, what="noalloc nq=1")
 
     # second call in a row reuses the array with other sizes: more queries (two query groups),
     # larger k; the previous call's lists and ticket must not leak into it
@@ -63,6 +70,7 @@ def test_noalloc_entry_point_matches_regular_search():
     assert free_after >= free_before, "the no-alloc entry point allocated device memory"
     Dr, Ir = ref.search(q2, 100)
     assert torch.equal(I2, Ir) and torch.equal(D2, Dr)
+    assert_knn_matches(D2.cpu().numpy(), I2.cpu().numpy(), xh, O.synth(999, 0, 11, 384), 100, what="noalloc nq=11")
 
     # and once more the first query: same answer as the first time
     rc, D3, I3 = _noalloc_search(L, dev, x, q1, 10, stream)
