@@ -91,6 +91,28 @@ B2K_API int b2k_write_append(const b2k_index* h, const char* path, int64_t first
 /* faiss.read_index(path) -- llm/rag.py:74, :153, :186.  Missing file -> B2K_EIO. */
 B2K_API int b2k_read(const char* path, int device, b2k_index** out);
 
+/* The same index spread over several GPUs of the node, driven from this one process (llm/rag.py is
+ * one Flask process: rag.py:204; replicas: 1 in llm/ragdeploy.yaml:6).  `devices` lists ndev distinct
+ * CUDA devices; global rows go to them in blocks of 4096 rows, round-robin, ids stay global row
+ * positions.  The handle is used with every other entry point exactly like a single-GPU one
+ * (add / search / ntotal / reset / write / read / view); device pointers (`on_device != 0`) must live
+ * on devices[0].  search: every GPU answers for its rows (its kernels write their k best straight into
+ * a packed buffer on devices[0] through peer memory), then one merge kernel there.  The IxF2 file is
+ * the same single file in global row order, so a file written by one device count loads on any other.
+ * ndev == 1 gives the plain single-GPU handle. */
+B2K_API int b2k_create_multi(int d, const int* devices, int ndev, b2k_index** out);
+B2K_API int b2k_read_multi(const char* path, const int* devices, int ndev, b2k_index** out);
+
+/* A second handle on the first `nrows` rows of `src` (nrows < 0: all of them) that SHARES their
+ * storage in HBM -- what makes faiss.read_index affordable on every request (llm/rag.py:153, :186
+ * reload the file per request and expect an independent index each time): the Python layer keeps the
+ * loaded file resident and hands every caller its own view.  Views are independent indexes: a view
+ * that appends while it sits at the end of the shared rows appends in place (other views keep seeing
+ * their own prefix); one that appends after the rows have moved on first takes a private copy of its
+ * prefix; reset drops only the view's own reference.  Each view has its own stream and workspace, so
+ * views may be searched concurrently from different threads. */
+B2K_API int b2k_view(const b2k_index* src, int64_t nrows, b2k_index** out);
+
 /* Message of the calling thread's last failed call ("" if none). */
 B2K_API const char* b2k_last_error(void);
 
@@ -117,6 +139,16 @@ B2K_API int b2k_add_synthetic(b2k_index* h, int64_t n, uint64_t seed, int64_t fi
 B2K_API int b2k_merge_topk(int device, int nlists, int64_t nq, int64_t k, const float* Din,
                    const int64_t* Iin, const int64_t* id_offset, float* D, int64_t* I,
                    int on_device, void* stream);
+
+/* The same combine step for the sharded indexes' own layouts, device pointers only: list l has its
+ * distances at Din + l*list_stride_d and its ids at Iin + l*list_stride_i (strides in elements, so
+ * the lists may sit inside packed all-gather records), and with cyclic_block = B > 0 the ids are
+ * shard-local rows of the block-cyclic layout above (B rows per block, nlists shards) and come out as
+ * global rows; B = 0 leaves them as they are. */
+B2K_API int b2k_merge_shards(int device, int nlists, int64_t nq, int64_t k, const float* Din,
+                     int64_t list_stride_d, const int64_t* Iin, int64_t list_stride_i,
+                     int64_t cyclic_block, float* D, int64_t* I, void* stream);
+#define B2K_CYCLIC_BLOCK 4096  /* rows per block of the multi-GPU layout */
 
 /* Search without allocating anything.  No counterpart in the reference (llm/rag.py never
  * manages device memory); it exists for callers that cannot call cudaMalloc -- a process
@@ -154,7 +186,9 @@ B2K_API int b2k_search_rows_noalloc(int device, const float* x_dev, int64_t n, i
  * and the caller must check it after its own synchronisation and repeat that search with
  * "tensor_mode" = 1 -- the row-sharded index ships the word with its all-gather),
  * "tensor_probe" (measurement only: 1 = batched searches run their main pass with the selection filter
- * shut -- the dense rate of the MMA pipeline for the chosen "tensor_mode"; the results are all padding).
+ * shut -- the dense rate of the MMA pipeline for the chosen "tensor_mode"; the results are all padding),
+ * "multi_peer_writes" (multi-GPU handles: 0 = shards keep their results locally and a peer memcpy moves
+ * them to devices[0]; 1 = direct peer stores where the GPUs allow it, the default).
  * Unknown key -> B2K_EINVAL. */
 B2K_API int b2k_set_option(b2k_index* h, const char* key, int64_t value);
 
@@ -164,7 +198,9 @@ B2K_API int b2k_set_option(b2k_index* h, const char* key, int64_t value);
  * "tensor_mode_used" (1 / 2 / 3 / 4), "screen_fallbacks" (query chunks repeated with a narrower screen, or by the scan kernel,
  * because the slack zone overflowed), "scan_kernel_ms" / "scan_launches" (the same for the scan kernel launches of the last
  * scan-path search), "scan_rows_used" (1 fp32 rows / 2 bf16 copies + re-rank), "scan_fallback"
- * (1 if the last bf16 scan was redone on the fp32 rows; synchronises the device). */
+ * (1 if the last bf16 scan was redone on the fp32 rows; synchronises the device), "shares_rows" (1 if
+ * another handle shares this one's row storage), "devices" (GPUs the handle spans), "peer_writes"
+ * (multi-GPU: 1 if the shards store their results directly into devices[0]'s memory). */
 B2K_API int b2k_get_stat(b2k_index* h, const char* key, double* out);
 
 /* Number of kernels this library has launched in this process (bench `gpu_launches`). */

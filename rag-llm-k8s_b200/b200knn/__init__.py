@@ -23,8 +23,8 @@ import numpy as np
 from . import _lib
 from ._lib import MAX_K
 
-__all__ = ["IndexFlatL2", "write_index", "read_index", "METRIC_L2", "default_device", "launch_count",
-           "clear_index_cache"]
+__all__ = ["IndexFlatL2", "write_index", "read_index", "METRIC_L2", "default_device", "default_devices",
+           "launch_count", "clear_index_cache"]
 
 METRIC_L2 = 1
 __version__ = "0.1.0"
@@ -37,6 +37,18 @@ def default_device():
         if v not in (None, ""):
             return int(v)
     return 0
+
+
+def default_devices():
+    """GPUs a new index spans: $B200KNN_DEVICES ("0,1,2,3": one index row-sharded over those GPUs, driven
+    from this one process -- what a single Flask process like llm/rag.py needs to use a whole node), else
+    the one GPU of default_device()."""
+    v = os.environ.get("B200KNN_DEVICES")
+    if v not in (None, ""):
+        devs = [int(t) for t in v.replace(" ", "").split(",") if t != ""]
+        if devs:
+            return devs
+    return [default_device()]
 
 
 def launch_count():
@@ -63,24 +75,43 @@ def _as_dev_f32(x, d, device, what):
     return x
 
 
+def _int_array(devs):
+    return (C.c_int * len(devs))(*devs)
+
+
 class IndexFlatL2:
-    """Exact squared-L2 index on one B200; the surface of `faiss.IndexFlatL2` that rag.py uses."""
+    """Exact squared-L2 index on one B200 -- or row-sharded over several (`devices=[...]`, or
+    $B200KNN_DEVICES), still one object in one process; the surface of `faiss.IndexFlatL2` that rag.py uses."""
 
     is_trained = True
     metric_type = METRIC_L2
-    # provenance for the resident-index cache / incremental write_index (see read_index below):
+    # provenance for the incremental write_index (see read_index below):
     _origin = None   # (realpath, stat key, rows in that file) while those rows are a prefix of this index
-    _clean = False   # True while the index content is exactly that file
 
-    def __init__(self, d, device=None, _handle=None):
+    def __init__(self, d, device=None, devices=None, _handle=None):
         self._h = None
-        self.device = default_device() if device is None else int(device)
+        if devices is None:
+            devices = default_devices() if device is None else [int(device)]
+        self.devices = [int(v) for v in devices]
+        assert self.devices, "IndexFlatL2: empty device list"
+        self.device = self.devices[0]          # where device-side inputs / outputs live
         if _handle is not None:
             self._h = _handle
             return
         h = C.c_void_p()
-        _lib.check(_lib.lib().b2k_create(int(d), self.device, C.byref(h)))
+        if len(self.devices) > 1:
+            _lib.check(_lib.lib().b2k_create_multi(int(d), _int_array(self.devices), len(self.devices), C.byref(h)))
+        else:
+            _lib.check(_lib.lib().b2k_create(int(d), self.device, C.byref(h)))
         self._h = h
+
+    def _view(self):
+        """An independent index over the rows this one holds now, sharing their storage in HBM (b2k_view)."""
+        h = C.c_void_p()
+        _lib.check(_lib.lib().b2k_view(self._h, -1, C.byref(h)))
+        v = IndexFlatL2(0, devices=self.devices, _handle=h)
+        v._origin = self._origin
+        return v
 
     def __del__(self):
         h, self._h = getattr(self, "_h", None), None
@@ -105,7 +136,6 @@ class IndexFlatL2:
     def add(self, x):
         """Append rows (rag.py:80).  Ids are row positions, sequential across adds."""
         L = _lib.lib()
-        self._clean = False
         if _is_torch(x) and x.is_cuda:
             x = _as_dev_f32(x, self.d, self.device, "add")
             _lib.check(L.b2k_add(self._h, x.shape[0], C.c_void_p(x.data_ptr()), 1, self._stream()))
@@ -156,7 +186,7 @@ class IndexFlatL2:
         return D, I
 
     def reset(self):
-        self._origin, self._clean = None, False
+        self._origin = None
         _lib.check(_lib.lib().b2k_reset(self._h))
 
     def reserve(self, nrows):
@@ -171,7 +201,6 @@ class IndexFlatL2:
 
     def add_synthetic(self, n, seed, first_row=0):
         """Append n rows of the counter-based synthetic stream, generated on the GPU."""
-        self._clean = False
         _lib.check(_lib.lib().b2k_add_synthetic(self._h, int(n), int(seed), int(first_row)))
 
     def stats(self):
@@ -195,6 +224,8 @@ class IndexFlatL2:
             out["launches"] = int(v.value)
         if out["path"] == "scan" and L.b2k_get_stat(self._h, b"scan_rows_used", C.byref(v)) == 0:
             out["scan_rows"] = {1: "fp32", 2: "bf16+rerank"}.get(int(v.value))
+        if L.b2k_get_stat(self._h, b"devices", C.byref(v)) == 0:
+            out["devices"] = int(v.value)
         return out
 
     def set_option(self, key, value):
@@ -205,15 +236,16 @@ class IndexFlatL2:
 # llm/rag.py re-reads the whole index file on EVERY request (rag.py:153, :186) and rewrites the
 # whole file on every upload (rag.py:74-84).  With the index in HBM that would put a file read
 # plus an H2D copy of the full index in front of every search, so:
-#   * read_index keeps the last few loaded indexes resident, keyed on (realpath, mtime_ns, size,
-#     inode); an unchanged file returns the resident index without touching the disk or the bus;
+#   * read_index keeps the last few loaded files resident, keyed on (realpath, mtime_ns, size,
+#     inode); for an unchanged file it returns a fresh VIEW of the resident rows (b2k_view) without
+#     touching the disk or the bus.  As with faiss, every call returns its own independent index:
+#     rows added through one are invisible to every other (a view appends in place while it is the
+#     only one at the end of the shared rows, and takes a private copy of its prefix otherwise), so
+#     concurrent requests of a threaded Flask server never see each other's half-finished updates;
 #   * write_index of an index that was loaded from `path` and only grew since appends the new
 #     rows and rewrites the 45-byte header instead of rewriting everything (the file stays
 #     byte-identical to a full write).
-# Observable difference from faiss: two read_index calls on an unchanged file return the SAME
-# object, so rows added through one reference are visible through the other until the next
-# read_index (which sees the index is no longer the file and loads a fresh one).
-# B200KNN_INDEX_CACHE=0 restores independent loads; =N keeps N indexes (default 4).
+# B200KNN_INDEX_CACHE=0 turns the residency off (every read loads the file); =N keeps N files (default 4).
 _cache = collections.OrderedDict()
 _cache_lock = threading.Lock()
 
@@ -231,13 +263,14 @@ def _stat_key(path):
 
 
 def _remember(rp, key, index):
+    """`index` is, right now, exactly the file (rp, key): keep a private snapshot view of it resident."""
     index._origin = (rp, key, index.ntotal)
-    index._clean = True
     n = _cache_max()
+    snap = index._view() if n else None      # nobody else holds this handle, so it can never change
     with _cache_lock:
         _cache.pop(rp, None)
         if n:
-            _cache[rp] = (key, index)
+            _cache[rp] = (key, snap)
             while len(_cache) > n:
                 _cache.popitem(last=False)
 
@@ -266,9 +299,11 @@ def write_index(index, path):
     _remember(rp, _stat_key(rp), index)
 
 
-def read_index(path, device=None):
+def read_index(path, device=None, devices=None):
     """faiss.read_index (rag.py:74, :153, :186); a missing file raises RuntimeError."""
-    dev = default_device() if device is None else int(device)
+    if devices is None:
+        devices = default_devices() if device is None else [int(device)]
+    devices = [int(v) for v in devices]
     rp = os.path.realpath(path)
     key = None
     try:
@@ -278,12 +313,15 @@ def read_index(path, device=None):
     if key is not None and _cache_max():
         with _cache_lock:
             ent = _cache.get(rp)
-            if ent is not None and ent[0] == key and ent[1]._clean and ent[1].device == dev:
+            if ent is not None and ent[0] == key and ent[1].devices == devices:
                 _cache.move_to_end(rp)
-                return ent[1]
+                return ent[1]._view()
     h = C.c_void_p()
-    _lib.check(_lib.lib().b2k_read(os.fsencode(path), dev, C.byref(h)))
-    idx = IndexFlatL2(0, device=dev, _handle=h)
+    if len(devices) > 1:
+        _lib.check(_lib.lib().b2k_read_multi(os.fsencode(path), _int_array(devices), len(devices), C.byref(h)))
+    else:
+        _lib.check(_lib.lib().b2k_read(os.fsencode(path), devices[0], C.byref(h)))
+    idx = IndexFlatL2(0, devices=devices, _handle=h)
     if key is not None and _stat_key(rp) == key:
         _remember(rp, key, idx)
     return idx
@@ -326,4 +364,14 @@ def merge_topk(Dl, Il, id_offset=None, device=None):
     I = np.empty((nq, k), np.int64)
     _lib.check(L.b2k_merge_topk(dev, nl, nq, k, Dl.ctypes.data_as(C.c_void_p), Il.ctypes.data_as(C.c_void_p), off,
                                 D.ctypes.data_as(C.c_void_p), I.ctypes.data_as(C.c_void_p), 0, None))
+    return D, I
+
+
+def merge_shards(Dpk, stride_d, Ipk, stride_i, nlists, nq, k, D, I, cyclic_block=_lib.CYCLIC_BLOCK):
+    """Combine step over device-side lists with their own strides (see b2k_merge_shards); torch CUDA tensors."""
+    import torch
+    dev = D.device.index
+    st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+    _lib.check(_lib.lib().b2k_merge_shards(dev, int(nlists), int(nq), int(k), C.c_void_p(Dpk), int(stride_d), C.c_void_p(Ipk),
+                                           int(stride_i), int(cyclic_block), C.c_void_p(D.data_ptr()), C.c_void_p(I.data_ptr()), st))
     return D, I

@@ -12,6 +12,7 @@ LIB_PATH = os.path.join(_HERE, "libb200knn.so")
 
 OK, EINVAL, ECUDA, EIO, ENOMEM, ELIMIT = 0, -1, -2, -3, -4, -5
 MAX_K = 1024
+CYCLIC_BLOCK = 4096   # B2K_CYCLIC_BLOCK
 
 _f32p = C.POINTER(C.c_float)
 _i64p = C.POINTER(C.c_int64)
@@ -28,6 +29,9 @@ SIGNATURES = {
     "b2k_write": (C.c_int, [C.c_void_p, C.c_char_p]),
     "b2k_write_append": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int64]),
     "b2k_read": (C.c_int, [C.c_char_p, C.c_int, C.POINTER(C.c_void_p)]),
+    "b2k_create_multi": (C.c_int, [C.c_int, C.POINTER(C.c_int), C.c_int, C.POINTER(C.c_void_p)]),
+    "b2k_read_multi": (C.c_int, [C.c_char_p, C.POINTER(C.c_int), C.c_int, C.POINTER(C.c_void_p)]),
+    "b2k_view": (C.c_int, [C.c_void_p, C.c_int64, C.POINTER(C.c_void_p)]),
     "b2k_last_error": (C.c_char_p, []),
     "b2k_reserve": (C.c_int, [C.c_void_p, C.c_int64]),
     "b2k_get_rows": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_int]),
@@ -35,6 +39,8 @@ SIGNATURES = {
     "b2k_add_synthetic": (C.c_int, [C.c_void_p, C.c_int64, C.c_uint64, C.c_int64]),
     "b2k_merge_topk": (C.c_int, [C.c_int, C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
                                  C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
+    "b2k_merge_shards": (C.c_int, [C.c_int, C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64,
+                                   C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
     "b2k_search_rows_noalloc": (C.c_int, [C.c_int, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_int64, C.c_int64,
                                           C.c_void_p, C.c_void_p, C.c_void_p]),
     "b2k_set_option": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int64]),

@@ -1,48 +1,70 @@
-"""Row-sharded IndexFlatL2 across the GPUs of one node.
+"""Row-sharded IndexFlatL2 across the GPUs of one node, one process per GPU.
 
-One process per GPU (torchrun); every rank makes the same calls (SPMD).  Each rank keeps a
-contiguous slice of every `add` batch in its own `IndexFlatL2` (C ABI, one B200) and answers
-`search` with its shard-local top-k; the per-rank (D, I) are exchanged with ONE NCCL all-gather
-of a packed buffer and combined by the merge kernel (K5, `b2k_merge_topk`).  Ids are global row
-positions, exactly as a single index would number them, so `llm/rag.py`'s rule "row id == index
-into the metadata list" (rag.py:81, :119) still holds.
+Launched under torchrun; every rank makes the same calls (SPMD).  Global rows go to the ranks in
+blocks of `block` rows, round-robin (block b lives on rank b % world as its local block
+b // world) -- the same layout the single-process multi-GPU handle uses (csrc/multi.cu), pure
+arithmetic in both directions, so no id table is kept and adds of any size stay balanced.  Each
+rank answers `search` with its shard-local top-k (C ABI, one B200; the kernels write straight into
+the packed send buffer), the per-rank records are exchanged with ONE NCCL all-gather, and the merge
+kernel (K5, `b2k_merge_shards`) reads the gathered records in place, turning shard-local rows into
+global row ids on the way.  Ids are global row positions, exactly as a single index would number
+them, so `llm/rag.py`'s rule "row id == index into the metadata list" (rag.py:81, :119) still holds.
 
 The reference is single-process and has no counterpart of this file; the behaviour it must
-reproduce is that of one `faiss.IndexFlatL2` holding all rows (rag.py:61-86, :116).
+reproduce is that of one `faiss.IndexFlatL2` holding all rows (rag.py:61-86, :116).  An index that
+must be driven from ONE process (rag.py is one Flask process) uses `IndexFlatL2(d, devices=[...])`
+instead; this class is the one-process-per-GPU form the benchmarks launch.
 """
 
 import numpy as np
 import torch
 import torch.distributed as dist
 
+CYCLIC_BLOCK = 4096
+
 
 def split_range(n, world, rank):
-    """Rows [lo, hi) of a batch of n rows kept by `rank`: contiguous blocks of ceil(n/world)."""
+    """Rows [lo, hi) of n rows a rank would keep under a contiguous split (kept for callers that shard that way)."""
     per = -(-n // world) if n else 0
     lo = min(rank * per, n)
     hi = min(lo + per, n)
     return lo, hi
 
 
+def cyclic_pieces(n0, n, world, rank, block):
+    """[(global first row, count)] of the global rows [n0, n0+n) that live on `rank`."""
+    out = []
+    g = n0
+    end = n0 + n
+    while g < end:
+        e = min((g // block + 1) * block, end)
+        if (g // block) % world == rank:
+            out.append((g, e - g))
+        g = e
+    return out
+
+
 class ShardedIndexFlatL2:
     is_trained = True
     metric_type = 1
 
-    def __init__(self, d, device=None, group=None, _local=None, _merge=None):
+    def __init__(self, d, device=None, group=None, block=CYCLIC_BLOCK, _local=None, _merge=None):
         """`_local` / `_merge` replace the CUDA shard index and merge kernel; only the CPU (gloo)
         tests of the host logic use them."""
         self.group = group
         self.world = dist.get_world_size(group)
         self.rank = dist.get_rank(group)
+        self.block = int(block)
         self._d = int(d)
-        if _local is None:
+        self._cuda = _local is None
+        if self._cuda:
             from . import IndexFlatL2, default_device
             self.device = default_device() if device is None else int(device)
             self.local = IndexFlatL2(d, device=self.device)
             self._tdev = torch.device("cuda", self.device)
-            # screening-overflow word owned by this object (see b2k_set_option "screen_flag_ptr")
-            self._flag = torch.zeros(2, dtype=torch.int32, device=self._tdev)
-            self.local.set_option("screen_flag_ptr", self._flag.data_ptr())
+            self._flag = None
+            self._flag_ptr = 0
+            self._flags_pin = torch.zeros(self.world, dtype=torch.int64, pin_memory=True)
         else:
             self.device = None
             self.local = _local
@@ -50,12 +72,10 @@ class ShardedIndexFlatL2:
             # a stand-in may bring its own overflow word (int32[2] tensor) to exercise the repeat protocol
             self._flag = getattr(_local, "screen_flag", None)
         self._merge = _merge
+        self._bufs = {}          # (nq, k) -> (send, recv): the exchange buffers are reused across searches
         self._tensor_mode = 0
         self._path = 0
         self._ntotal = 0
-        # segments of this rank's shard: local rows [ls, ls+cnt) are global rows [gs, gs+cnt)
-        self._seg_local = []
-        self._seg_global = []
 
     # ---- faiss surface -------------------------------------------------------------------
     @property
@@ -66,39 +86,35 @@ class ShardedIndexFlatL2:
     def ntotal(self):
         return self._ntotal
 
-    def _note_segment(self, gstart, count):
-        if count <= 0:
-            return
-        lstart = self.local.ntotal - count
-        if self._seg_local and self._seg_global[-1] + (lstart - self._seg_local[-1]) == gstart:
-            return  # contiguous with the previous segment
-        self._seg_local.append(lstart)
-        self._seg_global.append(gstart)
-
     def add(self, x):
-        """Every rank passes the same batch; rank r keeps rows split_range(n, world, r)."""
+        """Every rank passes the same batch; each keeps the blocks of the global row order that are its own."""
         n = int(x.shape[0])
         assert x.shape[1] == self._d, "add: dimension mismatch"
-        lo, hi = split_range(n, self.world, self.rank)
-        if hi > lo:
-            self.local.add(x[lo:hi])
-            self._note_segment(self._ntotal + lo, hi - lo)
+        pieces = cyclic_pieces(self._ntotal, n, self.world, self.rank, self.block)
+        if pieces:
+            parts = [x[g - self._ntotal: g - self._ntotal + c] for g, c in pieces]
+            if len(parts) == 1:
+                mine = parts[0]
+            elif torch.is_tensor(x):
+                mine = torch.cat(parts, 0)
+            else:
+                mine = np.concatenate([np.asarray(p) for p in parts], 0)
+            self.local.add(mine)
         self._ntotal += n
 
     def add_synthetic_global(self, n, seed):
-        """Benchmark helper: global rows [ntotal, ntotal+n) of the synthetic stream, each rank
-        generating only its own slice on its own GPU (100M x 768 never exists in one place)."""
-        lo, hi = split_range(n, self.world, self.rank)
-        if hi > lo:
-            self.local.reserve(self.local.ntotal + hi - lo)
-            self.local.add_synthetic(hi - lo, seed, self._ntotal + lo)
-            self._note_segment(self._ntotal + lo, hi - lo)
+        """Benchmark helper: global rows [ntotal, ntotal+n) get the synthetic stream's rows of the same
+        numbers, each rank generating only its own blocks on its own GPU (100M x 768 never exists in one place)."""
+        pieces = cyclic_pieces(self._ntotal, n, self.world, self.rank, self.block)
+        if pieces:
+            self.local.reserve(self.local.ntotal + sum(c for _, c in pieces))
+            for g, c in pieces:
+                self.local.add_synthetic(c, seed, g)
         self._ntotal += n
 
     def reset(self):
         self.local.reset()
         self._ntotal = 0
-        self._seg_local, self._seg_global = [], []
 
     def set_option(self, key, value):
         if key == "tensor_mode":
@@ -110,21 +126,14 @@ class ShardedIndexFlatL2:
     def stats(self):
         return self.local.stats()
 
-    def _to_global(self, I):
-        """Shard-local row ids -> global ids (-1 stays -1)."""
-        if not self._seg_local:
-            return I
-        if len(self._seg_local) == 1:
-            return torch.where(I >= 0, I + (self._seg_global[0] - self._seg_local[0]), I)
-        ls = torch.tensor(self._seg_local, dtype=torch.int64, device=I.device)
-        delta = torch.tensor([g - l for g, l in zip(self._seg_global, self._seg_local)], dtype=torch.int64,
-                             device=I.device)
-        seg = torch.searchsorted(ls, I.clamp(min=0), right=True) - 1
-        return torch.where(I >= 0, I + delta[seg], I)
-
     def to_global(self, I):
-        """Shard-local row ids (as `self.local.search` returns them) -> global row ids."""
-        return self._to_global(I)
+        """Shard-local row ids (as `self.local.search` returns them) -> global row ids (-1 stays -1)."""
+        B, W = self.block, self.world
+        if torch.is_tensor(I):
+            g = (torch.div(I, B, rounding_mode="floor") * W + self.rank) * B + I % B
+            return torch.where(I >= 0, g, I)
+        I = np.asarray(I)
+        return np.where(I >= 0, ((I // B) * W + self.rank) * B + I % B, I)
 
     def search(self, x, k):
         """(D, I) of the k nearest rows over ALL shards; identical on every rank."""
@@ -150,34 +159,61 @@ class ShardedIndexFlatL2:
             return torch.as_tensor(Dm).cpu().numpy(), torch.as_tensor(Im).cpu().numpy()
         return Dm, Im
 
+    def _buffers(self, nq, k):
+        nk = nq * k
+        words = nk + (nk + 1) // 2      # nk int64 ids, then nk float32 distances (8-byte aligned), then one flag word
+        b = self._bufs.get((nq, k))
+        if b is None:
+            if len(self._bufs) >= 8:
+                self._bufs.clear()
+            b = (torch.zeros(words + 1, dtype=torch.int64, device=self._tdev),
+                 torch.empty(self.world * (words + 1), dtype=torch.int64, device=self._tdev))
+            self._bufs[(nq, k)] = b
+        return nk, words, b[0], b[1]
+
     def _search_once(self, xq, k):
         nq = xq.shape[0]
-        nk = nq * k
-        # packed send buffer: nk int64 ids, nk float32 distances (8-byte aligned), one flag word
-        words = nk + (nk + 1) // 2
-        send = torch.empty(words + 1, dtype=torch.int64, device=self._tdev)
+        nk, words, send, recv = self._buffers(nq, k)
         I_loc = send[:nk].view(nq, k)
         D_loc = send[nk:words].view(torch.float32)[:nk].view(nq, k)
+        if self._cuda:
+            return self._search_once_cuda(xq, k, nq, nk, words, send, recv, D_loc, I_loc)
+        # ---- stand-in path (CPU tests of the host logic): same record layout, ids made global before the exchange
         if self._flag is not None:
             self._flag.zero_()
-        # with the flag word installed the shard search does not synchronise: the exchange and the merge
-        # are queued behind it while it runs, and the screening check travels with the all-gather
         D, I = self.local.search(xq, k)
         D_loc.copy_(torch.as_tensor(D))
-        I_loc.copy_(self._to_global(torch.as_tensor(I).to(self._tdev)))
+        I_loc.copy_(torch.as_tensor(self.to_global(torch.as_tensor(I))))
         if self._flag is not None:
             send[words:].copy_(self._flag.view(torch.int64))
         else:
             send[words:].zero_()
-        recv = torch.empty(self.world * (words + 1), dtype=torch.int64, device=self._tdev)
         dist.all_gather_into_tensor(recv, send, group=self.group)     # the one collective of the path
-        recv = recv.view(self.world, words + 1)
-        Icat = recv[:, :nk].reshape(self.world, nq, k)
-        Dcat = recv[:, nk:words].contiguous().view(torch.float32)[:, :nk].reshape(self.world, nq, k)
-        if self._merge is not None:
-            Dm, Im = self._merge(Dcat, Icat)
-        else:
-            from . import merge_topk
-            Dm, Im = merge_topk(Dcat, Icat)
-        redo = self._flag is not None and bool((recv[:, words] != 0).any().item())
+        rv = recv.view(self.world, words + 1)
+        Icat = rv[:, :nk].reshape(self.world, nq, k)
+        Dcat = rv[:, nk:words].contiguous().view(torch.float32)[:, :nk].reshape(self.world, nq, k)
+        Dm, Im = self._merge(Dcat, Icat)
+        redo = self._flag is not None and bool((rv[:, words] != 0).any().item())
+        return Dm, Im, redo
+
+    def _search_once_cuda(self, xq, k, nq, nk, words, send, recv, D_loc, I_loc):
+        from . import merge_shards
+        # the screening-overflow word of the shard search IS the last word of the send record: with it
+        # installed the search does not synchronise, the exchange and the merge are queued behind it
+        # while it runs, and the word travels with the all-gather
+        fp = send.data_ptr() + 8 * words
+        if fp != self._flag_ptr:
+            self.local.set_option("screen_flag_ptr", fp)
+            self._flag_ptr = fp
+        send[words:].zero_()
+        self.local.search(xq, k, D=D_loc, I=I_loc)             # kernels write the record in place
+        dist.all_gather_into_tensor(recv, send, group=self.group)     # the one collective of the path
+        Dm = torch.empty((nq, k), dtype=torch.float32, device=self._tdev)
+        Im = torch.empty((nq, k), dtype=torch.int64, device=self._tdev)
+        # the merge kernel reads the gathered records where they are and turns shard-local rows into global ids
+        merge_shards(recv.data_ptr() + 8 * nk, 2 * (words + 1), recv.data_ptr(), words + 1, self.world, nq, k, Dm, Im,
+                     cyclic_block=self.block)
+        self._flags_pin.copy_(recv[words::words + 1], non_blocking=True)
+        torch.cuda.current_stream(self.device).synchronize()
+        redo = bool(self._flags_pin.any())
         return Dm, Im, redo

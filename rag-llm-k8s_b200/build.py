@@ -12,7 +12,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "b200knn", "libb200knn.so")
 OBJ = os.path.join(HERE, "build")
-SOURCES = ["index.cu", "k1_prep.cu", "k2_scan.cu", "k3_tc.cu", "k5_merge.cu", "noalloc.cu"]
+SOURCES = ["index.cu", "multi.cu", "k1_prep.cu", "k2_scan.cu", "k3_tc.cu", "k5_merge.cu", "noalloc.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
          "-Xcompiler", "-fPIC,-fvisibility=hidden", "--expt-relaxed-constexpr"]

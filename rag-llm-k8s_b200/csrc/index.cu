@@ -1,13 +1,16 @@
 // index.cu -- the C ABI of libb200knn.so (declared in include/b200knn.h): index lifecycle,
-// row storage in HBM, IxF2 persistence and the search dispatch.
+// row storage in HBM, IxF2 persistence and the search dispatch of the single-GPU handle; handles
+// that span several GPUs are forwarded to multi.cu.
 //
 // Mirrors the `faiss.IndexFlatL2` surface used by /root/reference/llm/rag.py
 // (:61/:71 construct, :80 add, :116 search, :86/:190-191 ntotal/d, :62/:82 write_index,
-// :74/:153/:186 read_index).  HBM layout per handle:
+// :74/:153/:186 read_index).  HBM layout per row store (index_internal.h):
 //     x     [capacity][d] float32  row-major, the rows as given            (K2, K3 "hi" operand)
 //     norms [capacity]    float32  ||x||^2, written by K1 at add()         (K3 epilogue)
-//     xlo   [capacity][d] float32  TF32 residual rows, only once a batched (K3 "lo" operand)
-//                                  search has been made on this handle
+//     xlo   [capacity][d] float32  TF32 residual rows, only once a 3xTF32  (K3 "lo" operand)
+//                                  search has been made on this store
+//     xbf   [capacity][d] bf16     copies for the screening pass / bf16 scan, once one has run
+// and per handle
 //     ws    scratch: device copies of queries / results for host callers, per-CTA partial
 //           top-k lists, K3 candidate lists.
 #include <errno.h>
@@ -21,6 +24,7 @@
 #include "common.cuh"
 #include "kernels.h"
 #include "k3_api.h"
+#include "index_internal.h"
 
 namespace b2k {
 
@@ -36,70 +40,19 @@ void set_error(const char* fmt, ...) {
     t_err = buf;
 }
 
-}  // namespace b2k
-
-using namespace b2k;
-
-struct b2k_index {
-    int d = 0, device = 0, sm_count = 148;
-    int64_t ntotal = 0, capacity = 0;
-    float* x = nullptr;
-    float* norms = nullptr;
-    float* xlo = nullptr;
-    bool lo_enabled = false;
-    void* xbf = nullptr;  // bf16 copies of the rows (bf16 screening mode), allocated on first use
-    bool bf_enabled = false;
-    bool bf_nomem = false;  // the bf16 copies did not fit next to the rows: TF32 screening serves from then on
-    cudaStream_t stream = nullptr;
-    mutable std::mutex mu;
-    void* ws = nullptr;
-    size_t ws_bytes = 0;
-    void* pin = nullptr;
-    size_t pin_bytes = 0;
-    unsigned int* done = nullptr;
-    int opt_path = 0;
-    int opt_scan_ctas_per_sm = 4;  // upper bound; each variant is clamped to its own residency (64 regs x 256 threads -> 4)
-    int opt_timing = 0;
-    int opt_cta_group = 0;  // 0 = library default
-    int opt_sep = 0;
-    int opt_segments = 1;
-    unsigned int* opt_flag_ptr = nullptr;
-    int opt_scan_rows = 0;  // nq < 20 scan: 0 auto (bf16 copies + exact re-rank for large indexes), 1 fp32 rows, 2 bf16 copies
-    bool last_scan_bf = false;
-    int opt_epi = 0;
-    int opt_probe = 0;
-    int opt_tensor_mode = 0;  // 0 auto (bf16 screening + exact re-rank where d % 8 == 0 and memory allows, else TF32 screening), 1 3xTF32, 2 TF32 screening, 3 bf16 screening, 4 3xTF32 screening
-    int64_t stat_screen_fallbacks = 0;
-    int screen_fail_streak = 0;      // consecutive searches whose cheap screen overflowed
-    unsigned int screen_skipped = 0;  // searches that started at the 3xTF32 screen because of that
-    int last_path = 0;
-    int sticky = 0;
-    K3State* k3 = nullptr;
-    // cross-stream ordering: rows written (add) -> later searches; workspace users -> next user
-    cudaEvent_t ev_rows = nullptr, ev_ws = nullptr;
-    cudaEvent_t ev_t0 = nullptr, ev_t1 = nullptr;  // option timing: around the scan launches
-    int scan_launches = 0;
-    bool scan_timed = false;
-};
+RowStore::~RowStore() {
+    DeviceGuard g(device);
+    cudaDeviceSynchronize();  // kernels of handles that shared this store may still be reading it
+    cudaFree(x); cudaFree(norms); cudaFree(xlo); cudaFree(xbf); cudaFree(stat);
+    if (ev_rows) cudaEventDestroy(ev_rows);
+}
 
 static constexpr int64_t MAX_ROWS = 0xFFFFFFFEll;  // row index lives in the low 32 bits of a key
 static constexpr size_t IO_CHUNK = (size_t)64 << 20;
-static constexpr int MAX_NORM_SLOT = 2;  // h->done[0] ticket, [1] scan work counter, [2] bits of the largest squared row norm
-static constexpr int SCAN_FLAG_SLOT = 4;  // [4] raised by the bf16 scan's re-rank when its candidates did not cover the slack zone
-static constexpr int MAX_ERR_SLOT = 3;   // [3] bits of the largest squared bf16 rounding-error norm of a row
+static constexpr int SCAN_FLAG_SLOT = 4;  // h->done: [0] scan ticket, [1] scan work counter, [4] raised by the bf16 scan's re-rank when its candidates did not cover the slack zone
+static constexpr int MAX_NORM_SLOT = 0;   // rs->stat: [0] bits of the largest squared row norm
+static constexpr int MAX_ERR_SLOT = 1;    //           [1] bits of the largest squared bf16 rounding-error norm of a row
 static constexpr int64_t TC_QUERY_CHUNK = 4096;  // queries per tensor-core pass (faiss: distance_compute_blas_query_bs)
-
-namespace {
-
-struct DeviceGuard {
-    int prev = -1;
-    bool ok = false;
-    explicit DeviceGuard(int dev) {
-        if (cudaGetDevice(&prev) != cudaSuccess) { prev = -1; }
-        ok = (cudaSetDevice(dev) == cudaSuccess);
-    }
-    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
-};
 
 // Validated devices are cached: cudaGetDeviceProperties costs about a millisecond, far too much
 // for per-call use (the merge entry point is on the sharded search's critical path).
@@ -134,6 +87,15 @@ int check_device(int device, int* sm_count) {
     return B2K_OK;
 }
 
+// true if p is page-locked host memory known to CUDA (cudaMallocHost / cudaHostRegister / torch pin_memory)
+bool is_pinned_host(const void* p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return a.type == cudaMemoryTypeHost;
+}
+
+namespace {
+
 int ensure_ws(b2k_index* h, size_t bytes) {
     if (bytes <= h->ws_bytes) return B2K_OK;
     if (h->ws) { B2K_CUDA(cudaFree(h->ws)); h->ws = nullptr; h->ws_bytes = 0; }  // cudaFree synchronises
@@ -154,16 +116,29 @@ int ensure_pin(b2k_index* h, size_t bytes) {
     return B2K_OK;
 }
 
-int grow(b2k_index* h, int64_t need_rows) {
-    if (need_rows <= h->capacity) return B2K_OK;
+int new_store(int d, int device, std::shared_ptr<RowStore>* out) {
+    std::shared_ptr<RowStore> rs(new (std::nothrow) RowStore());
+    if (!rs) { set_error("out of host memory"); return B2K_ENOMEM; }
+    rs->d = d; rs->device = device;
+    cudaError_t e = cudaMalloc(&rs->stat, 256);
+    if (e == cudaSuccess) e = cudaMemset(rs->stat, 0, 256);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&rs->ev_rows, cudaEventDisableTiming);
+    if (e != cudaSuccess) { cudaGetLastError(); set_error("row store: %s", cudaGetErrorString(e)); return B2K_ECUDA; }
+    *out = rs;
+    return B2K_OK;
+}
+
+// Make room for need_rows rows.  Caller holds rs->mu exclusively.  `st`: the stream the old rows are copied on.
+int grow(RowStore* rs, int64_t need_rows, cudaStream_t st) {
+    if (need_rows <= rs->capacity) return B2K_OK;
     if (need_rows > MAX_ROWS) { set_error("index limited to %lld rows per GPU", (long long)MAX_ROWS); return B2K_ELIMIT; }
-    int64_t cap = h->capacity * 2;
+    int64_t cap = rs->capacity * 2;
     if (cap < need_rows) cap = need_rows;
     if (cap < 1024) cap = 1024;
     if (cap > MAX_ROWS) cap = MAX_ROWS;
     float *nx = nullptr, *nn = nullptr, *nl = nullptr;
     void* nb = nullptr;
-    size_t row_bytes = (size_t)h->d * sizeof(float);
+    size_t row_bytes = (size_t)rs->d * sizeof(float);
     cudaError_t e = cudaMalloc(&nx, (size_t)cap * row_bytes);
     if (e != cudaSuccess && cap > need_rows) {  // doubling did not fit: take exactly what is needed
         cudaGetLastError();
@@ -171,74 +146,84 @@ int grow(b2k_index* h, int64_t need_rows) {
         e = cudaMalloc(&nx, (size_t)cap * row_bytes);
     }
     if (e == cudaSuccess) e = cudaMalloc(&nn, (size_t)cap * sizeof(float));
-    if (e == cudaSuccess && h->lo_enabled) e = cudaMalloc(&nl, (size_t)cap * row_bytes);
-    if (e == cudaSuccess && h->bf_enabled && cudaMalloc(&nb, (size_t)cap * row_bytes / 2) != cudaSuccess) {
+    if (e == cudaSuccess && rs->lo_enabled) e = cudaMalloc(&nl, (size_t)cap * row_bytes);
+    if (e == cudaSuccess && rs->bf_enabled && cudaMalloc(&nb, (size_t)cap * row_bytes / 2) != cudaSuccess) {
         // no room for the bf16 copies next to the grown rows: drop them, TF32 screening needs none
         cudaGetLastError();
         nb = nullptr;
-        h->bf_enabled = false;
-        h->bf_nomem = true;
+        rs->bf_enabled = false;
+        rs->bf_nomem = true;
     }
     if (e != cudaSuccess) {
         cudaGetLastError();
         cudaFree(nx); cudaFree(nn); cudaFree(nl); cudaFree(nb);
-        set_error("cudaMalloc for %lld rows x %d failed: %s", (long long)cap, h->d, cudaGetErrorString(e));
+        set_error("cudaMalloc for %lld rows x %d failed: %s", (long long)cap, rs->d, cudaGetErrorString(e));
         return B2K_ENOMEM;
     }
-    if (h->ntotal > 0) {
+    if (rs->filled > 0) {
         // rows may still be landing on a caller's stream (on-device add): order this copy behind them
-        B2K_CUDA(cudaStreamWaitEvent(h->stream, h->ev_rows, 0));
-        B2K_CUDA(cudaMemcpyAsync(nx, h->x, (size_t)h->ntotal * row_bytes, cudaMemcpyDeviceToDevice, h->stream));
-        B2K_CUDA(cudaMemcpyAsync(nn, h->norms, (size_t)h->ntotal * sizeof(float), cudaMemcpyDeviceToDevice, h->stream));
-        if (nl) B2K_CUDA(cudaMemcpyAsync(nl, h->xlo, (size_t)h->ntotal * row_bytes, cudaMemcpyDeviceToDevice, h->stream));
-        if (nb) B2K_CUDA(cudaMemcpyAsync(nb, h->xbf, (size_t)h->ntotal * row_bytes / 2, cudaMemcpyDeviceToDevice, h->stream));
-        B2K_CUDA(cudaStreamSynchronize(h->stream));
+        B2K_CUDA(cudaStreamWaitEvent(st, rs->ev_rows, 0));
+        B2K_CUDA(cudaMemcpyAsync(nx, rs->x, (size_t)rs->filled * row_bytes, cudaMemcpyDeviceToDevice, st));
+        B2K_CUDA(cudaMemcpyAsync(nn, rs->norms, (size_t)rs->filled * sizeof(float), cudaMemcpyDeviceToDevice, st));
+        if (nl) B2K_CUDA(cudaMemcpyAsync(nl, rs->xlo, (size_t)rs->filled * row_bytes, cudaMemcpyDeviceToDevice, st));
+        if (nb) B2K_CUDA(cudaMemcpyAsync(nb, rs->xbf, (size_t)rs->filled * row_bytes / 2, cudaMemcpyDeviceToDevice, st));
+        B2K_CUDA(cudaStreamSynchronize(st));
     }
-    cudaFree(h->x); cudaFree(h->norms); cudaFree(h->xlo); cudaFree(h->xbf);
-    h->x = nx; h->norms = nn; h->xlo = nl; h->xbf = nb; h->capacity = cap;
+    // cudaFree waits for everything already enqueued on the device, including searches of other
+    // handles that read the old buffers (they enqueued under the shared lock, before this point)
+    cudaFree(rs->x); cudaFree(rs->norms); cudaFree(rs->xlo); cudaFree(rs->xbf);
+    rs->x = nx; rs->norms = nn; rs->xlo = nl; rs->xbf = nb; rs->capacity = cap;
     return B2K_OK;
 }
 
-// Rows [first, first+n) of h->x are in place: compute their norms (and residual rows).
-int prep_new_rows(b2k_index* h, int64_t first, int64_t n, cudaStream_t st) {
-    int rc = launch_row_prep(h->x + first * (int64_t)h->d, n, h->d, h->norms + first,
-                             h->lo_enabled ? h->xlo + first * (int64_t)h->d : nullptr, h->done + MAX_NORM_SLOT, st);
-    if (!rc && h->bf_enabled)
-        rc = launch_row_bf16(h->x + first * (int64_t)h->d, n, h->d,
-                             static_cast<unsigned short*>(h->xbf) + first * (int64_t)h->d, nullptr, h->done + MAX_ERR_SLOT, st);
+// Rows [first, first+n) of rs->x are in place: compute their norms (and the derived copies that exist).
+int prep_new_rows(RowStore* rs, int64_t first, int64_t n, cudaStream_t st) {
+    int rc = launch_row_prep(rs->x + first * (int64_t)rs->d, n, rs->d, rs->norms + first,
+                             rs->lo_enabled ? rs->xlo + first * (int64_t)rs->d : nullptr, rs->stat + MAX_NORM_SLOT, st);
+    if (!rc && rs->bf_enabled)
+        rc = launch_row_bf16(rs->x + first * (int64_t)rs->d, n, rs->d,
+                             static_cast<unsigned short*>(rs->xbf) + first * (int64_t)rs->d, nullptr, rs->stat + MAX_ERR_SLOT, st);
     return rc;
 }
 
-int enable_lo(b2k_index* h, cudaStream_t st) {
-    if (h->lo_enabled) return B2K_OK;
-    if (h->capacity > 0) {
-        cudaError_t e = cudaMalloc(&h->xlo, (size_t)h->capacity * h->d * sizeof(float));
-        if (e != cudaSuccess) { cudaGetLastError(); set_error("cudaMalloc for TF32 residual rows failed: %s", cudaGetErrorString(e)); return B2K_ENOMEM; }
+// The derived copies are created on first use, on the stream of the search that needs them, under
+// the exclusive lock; ev_rows is re-recorded so that other handles' searches wait for the pass.
+int enable_lo(RowStore* rs, cudaStream_t st) {
+    if (rs->lo_enabled) return B2K_OK;
+    std::unique_lock<std::shared_mutex> lk(rs->mu);
+    if (rs->lo_enabled) return B2K_OK;
+    if (rs->capacity > 0) {
+        cudaError_t e = cudaMalloc(&rs->xlo, (size_t)rs->capacity * rs->d * sizeof(float));
+        if (e != cudaSuccess) { cudaGetLastError(); rs->xlo = nullptr; set_error("cudaMalloc for TF32 residual rows failed: %s", cudaGetErrorString(e)); return B2K_ENOMEM; }
     }
-    h->lo_enabled = true;
-    if (h->ntotal > 0) return launch_row_prep(h->x, h->ntotal, h->d, h->norms, h->xlo, nullptr, st);
-    return B2K_OK;
+    int rc = B2K_OK;
+    if (rs->filled > 0) {
+        B2K_CUDA(cudaStreamWaitEvent(st, rs->ev_rows, 0));
+        rc = launch_row_prep(rs->x, rs->filled, rs->d, rs->norms, rs->xlo, nullptr, st);
+        if (!rc) B2K_CUDA(cudaEventRecord(rs->ev_rows, st));
+    }
+    if (!rc) rs->lo_enabled = true;
+    return rc;
 }
 
-// bf16 copies of the rows for the bf16 screening mode (half the size of the rows themselves).
-int enable_bf(b2k_index* h, cudaStream_t st) {
-    if (h->bf_enabled) return B2K_OK;
-    if (h->capacity > 0) {
-        cudaError_t e = cudaMalloc(&h->xbf, (size_t)h->capacity * h->d * 2);
-        if (e != cudaSuccess) { cudaGetLastError(); h->bf_nomem = true; set_error("cudaMalloc for bf16 rows failed: %s", cudaGetErrorString(e)); return B2K_ENOMEM; }
+// bf16 copies of the rows for the bf16 screening mode / bf16 scan (half the size of the rows themselves).
+int enable_bf(RowStore* rs, cudaStream_t st) {
+    if (rs->bf_enabled) return B2K_OK;
+    std::unique_lock<std::shared_mutex> lk(rs->mu);
+    if (rs->bf_enabled) return B2K_OK;
+    if (rs->bf_nomem) { set_error("no room for the bf16 copies"); return B2K_ENOMEM; }
+    if (rs->capacity > 0) {
+        cudaError_t e = cudaMalloc(&rs->xbf, (size_t)rs->capacity * rs->d * 2);
+        if (e != cudaSuccess) { cudaGetLastError(); rs->xbf = nullptr; rs->bf_nomem = true; set_error("cudaMalloc for bf16 rows failed: %s", cudaGetErrorString(e)); return B2K_ENOMEM; }
     }
-    h->bf_enabled = true;
-    if (h->ntotal > 0) return launch_row_bf16(h->x, h->ntotal, h->d, h->xbf, nullptr, h->done + MAX_ERR_SLOT, st);
-    return B2K_OK;
-}
-
-size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
-
-// true if p is page-locked host memory known to CUDA (cudaMallocHost / cudaHostRegister / torch pin_memory)
-bool is_pinned_host(const void* p) {
-    cudaPointerAttributes a;
-    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
-    return a.type == cudaMemoryTypeHost;
+    int rc = B2K_OK;
+    if (rs->filled > 0) {
+        B2K_CUDA(cudaStreamWaitEvent(st, rs->ev_rows, 0));
+        rc = launch_row_bf16(rs->x, rs->filled, rs->d, rs->xbf, nullptr, rs->stat + MAX_ERR_SLOT, st);
+        if (!rc) B2K_CUDA(cudaEventRecord(rs->ev_rows, st));
+    }
+    if (!rc) rs->bf_enabled = true;
+    return rc;
 }
 
 // Candidates the bf16 scan selects for a request of k (0: the bf16 scan cannot serve this k).
@@ -250,7 +235,7 @@ int scan_bf_candidates(int k) {
 // The bf16 scan pays once the rows are large enough for HBM time to matter: below 128 MB of rows
 // the extra re-rank launch costs more than the halved row stream saves.
 bool scan_wants_bf(const b2k_index* h, int k) {
-    if (h->opt_scan_rows == 1 || h->bf_nomem || h->d % 8 != 0 || scan_bf_candidates(k) == 0) return false;
+    if (h->opt_scan_rows == 1 || h->rs->bf_nomem || h->d % 8 != 0 || scan_bf_candidates(k) == 0) return false;
     if (h->opt_scan_rows == 2) return true;
     return (double)h->ntotal * h->d >= 32e6;
 }
@@ -264,6 +249,7 @@ size_t scan_ws_bytes(const b2k_index* h, int64_t nq, int k, bool bf) {
 
 int scan_search(b2k_index* h, int64_t nq, const float* qd, int k, float* Dd, int64_t* Id, unsigned char* ws_tail,
                 cudaStream_t st, bool bf) {
+    const RowStore* rs = h->rs.get();
     const int grid = scan_grid(h->ntotal, h->sm_count, h->opt_scan_ctas_per_sm);
     u64* partial = reinterpret_cast<u64*>(ws_tail);
     if (h->opt_timing) {
@@ -284,18 +270,18 @@ int scan_search(b2k_index* h, int64_t nq, const float* qd, int k, float* Dd, int
         for (int64_t q0 = 0; q0 < nq;) {
             int qt = scan_pick_qt(nq - q0, kp);
             if (qt > 4) qt = 4;  // 8 queries per pass would make the bf16 variant ALU-bound
-            int rc = launch_scan(h->xbf, qd + q0 * (int64_t)h->d, h->ntotal, h->d, qt, kp, grid, partial, h->done,
+            int rc = launch_scan(rs->xbf, qd + q0 * (int64_t)h->d, h->ntotal, h->d, qt, kp, grid, partial, h->done,
                                  Da + q0 * kp, Ia + q0 * kp, st, true, nullptr);
             if (rc) return rc;
             q0 += qt;
             ++h->scan_launches;
         }
         if (h->opt_timing) { B2K_CUDA(cudaEventRecord(h->ev_t1, st)); h->scan_timed = true; }
-        int rc = launch_scan_rerank(h->x, qd, nq, h->d, k, kp, Da, Ia, h->done + MAX_ERR_SLOT, Dd, Id, flag, st);
+        int rc = launch_scan_rerank(rs->x, qd, nq, h->d, k, kp, Da, Ia, rs->stat + MAX_ERR_SLOT, Dd, Id, flag, st);
         if (rc) return rc;
         for (int64_t q0 = 0; q0 < nq;) {
             int qt = scan_pick_qt(nq - q0, k);
-            rc = launch_scan(h->x, qd + q0 * (int64_t)h->d, h->ntotal, h->d, qt, k, grid, partial, h->done,
+            rc = launch_scan(rs->x, qd + q0 * (int64_t)h->d, h->ntotal, h->d, qt, k, grid, partial, h->done,
                              Dd + q0 * k, Id + q0 * k, st, false, flag);
             if (rc) return rc;
             q0 += qt;
@@ -304,7 +290,7 @@ int scan_search(b2k_index* h, int64_t nq, const float* qd, int k, float* Dd, int
     }
     for (int64_t q0 = 0; q0 < nq;) {
         int qt = scan_pick_qt(nq - q0, k);
-        int rc = launch_scan(h->x, qd + q0 * (int64_t)h->d, h->ntotal, h->d, qt, k, grid, partial, h->done,
+        int rc = launch_scan(rs->x, qd + q0 * (int64_t)h->d, h->ntotal, h->d, qt, k, grid, partial, h->done,
                              Dd + q0 * k, Id + q0 * k, st);
         if (rc) return rc;
         q0 += qt;
@@ -316,11 +302,131 @@ int scan_search(b2k_index* h, int64_t nq, const float* qd, int k, float* Dd, int
 
 
 
+// A handle over `rs` seeing its first n rows.
+int make_handle(int d, int device, int sm, std::shared_ptr<RowStore> rs, int64_t n, b2k_index** out) {
+    b2k_index* h = new (std::nothrow) b2k_index();
+    if (!h) { set_error("out of host memory"); return B2K_ENOMEM; }
+    h->d = d; h->device = device; h->sm_count = sm;
+    h->rs = std::move(rs);
+    h->ntotal = n;
+    cudaError_t e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaMalloc(&h->done, 256);
+    if (e == cudaSuccess) e = cudaMemset(h->done, 0, 256);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_ws, cudaEventDisableTiming);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        set_error("b2k_create: %s", cudaGetErrorString(e));
+        if (h->stream) cudaStreamDestroy(h->stream);
+        cudaFree(h->done);
+        if (h->ev_ws) cudaEventDestroy(h->ev_ws);
+        delete h;
+        return B2K_ECUDA;
+    }
+    *out = h;
+    return B2K_OK;
+}
+
+// Give h a private store holding exactly its own rows (it shared one that has since moved on, or
+// it is about to drop its rows).  keep = false: start empty.
+int detach(b2k_index* h, bool keep) {
+    std::shared_ptr<RowStore> ns;
+    int rc = new_store(h->d, h->device, &ns);
+    if (rc) return rc;
+    if (keep && h->ntotal > 0) {
+        RowStore* os = h->rs.get();
+        std::shared_lock<std::shared_mutex> lk(os->mu);
+        rc = grow(ns.get(), h->ntotal, h->stream);
+        if (rc) return rc;
+        B2K_CUDA(cudaStreamWaitEvent(h->stream, os->ev_rows, 0));
+        B2K_CUDA(cudaMemcpyAsync(ns->x, os->x, (size_t)h->ntotal * h->d * sizeof(float), cudaMemcpyDeviceToDevice, h->stream));
+        ns->filled = h->ntotal;
+        rc = prep_new_rows(ns.get(), 0, h->ntotal, h->stream);
+        if (rc) return rc;
+        B2K_CUDA(cudaEventRecord(ns->ev_rows, h->stream));
+        B2K_CUDA(cudaStreamSynchronize(h->stream));
+    }
+    h->rs = ns;  // the old store goes away with its last handle
+    h->screen_fail_streak = 0;
+    return B2K_OK;
+}
+
+// Before rows are appended through h: h must sit at the end of its store.  Returns with rs->mu NOT held.
+int own_the_tail(b2k_index* h) {
+    bool at_end;
+    {
+        std::shared_lock<std::shared_mutex> lk(h->rs->mu);
+        at_end = h->rs->filled == h->ntotal;
+    }
+    // (another view that appends between this check and the caller's exclusive lock is caught there)
+    return at_end ? B2K_OK : detach(h, true);
+}
+
+// Appends n rows that `fill` writes at rs->x + first*d on stream st (a copy, or the generator).
+template <class Fill>
+int append_rows(b2k_index* h, int64_t n, cudaStream_t st, bool sync_after, Fill fill) {
+    int rc = own_the_tail(h);
+    if (rc) return rc;
+    std::unique_lock<std::shared_mutex> sl(h->rs->mu);
+    if (h->rs->filled != h->ntotal) {  // another view appended in the meantime
+        sl.unlock();
+        rc = detach(h, true);
+        if (rc) return rc;
+        sl = std::unique_lock<std::shared_mutex>(h->rs->mu);
+    }
+    RowStore* rs = h->rs.get();
+    rc = grow(rs, rs->filled + n, h->stream);
+    if (rc) return rc;
+    // ev_rows is one event: before it is re-recorded on this stream, this stream takes over the
+    // dependency on whatever stream recorded it last, so "all rows so far" stays one wait
+    B2K_CUDA(cudaStreamWaitEvent(st, rs->ev_rows, 0));
+    rc = fill(rs->x + rs->filled * (int64_t)rs->d, st);
+    if (rc) return rc;
+    rc = prep_new_rows(rs, rs->filled, n, st);
+    if (rc) return rc;
+    B2K_CUDA(cudaEventRecord(rs->ev_rows, st));
+    rs->filled += n;
+    h->ntotal += n;
+    if (sync_after) {
+        cudaError_t e = cudaStreamSynchronize(st);
+        if (e != cudaSuccess) { h->sticky = (int)e; set_error("b2k_add: %s", cudaGetErrorString(e)); return B2K_ECUDA; }
+    }
+    return B2K_OK;
+}
+
 }  // namespace
+
+void ixf2_put_header(unsigned char* b, int d, int64_t n) {
+    memcpy(b, "IxF2", 4);
+    int32_t d32 = d; memcpy(b + 4, &d32, 4);
+    memcpy(b + 8, &n, 8);
+    int64_t dummy = 1 << 20; memcpy(b + 16, &dummy, 8); memcpy(b + 24, &dummy, 8);
+    b[32] = 1;
+    int32_t metric = 1; memcpy(b + 33, &metric, 4);
+    uint64_t count = (uint64_t)n * (uint64_t)d; memcpy(b + 37, &count, 8);
+}
+
+int ixf2_parse_header(const unsigned char* hdr, const char* path, int* d, int64_t* n) {
+    if (memcmp(hdr, "IxF2", 4) != 0) {
+        set_error("%s: index type '%.4s' not supported (only IxF2 = IndexFlatL2)", path, (const char*)hdr);
+        return B2K_EIO;
+    }
+    int32_t d32, metric; int64_t nn; uint64_t count;
+    memcpy(&d32, hdr + 4, 4); memcpy(&nn, hdr + 8, 8); memcpy(&metric, hdr + 33, 4); memcpy(&count, hdr + 37, 8);
+    if (d32 <= 0 || nn < 0 || metric != 1 || count != (uint64_t)nn * (uint64_t)d32) {
+        set_error("%s: inconsistent IxF2 header (d=%d ntotal=%lld metric=%d count=%llu)", path, d32, (long long)nn, metric, (unsigned long long)count);
+        return B2K_EIO;
+    }
+    *d = d32; *n = nn;
+    return B2K_OK;
+}
+
+}  // namespace b2k
+
+using namespace b2k;
 
 extern "C" {
 
-int b2k_version(void) { return 100; }
+int b2k_version(void) { return 200; }
 
 const char* b2k_last_error(void) { return t_err.c_str(); }
 
@@ -334,37 +440,45 @@ int b2k_create(int d, int device, b2k_index** out) {
     int rc = check_device(device, &sm);
     if (rc) return rc;
     DeviceGuard g(device);
-    b2k_index* h = new (std::nothrow) b2k_index();
-    if (!h) { set_error("out of host memory"); return B2K_ENOMEM; }
-    h->d = d; h->device = device; h->sm_count = sm;
-    cudaError_t e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
-    if (e == cudaSuccess) e = cudaMalloc(&h->done, 256);
-    if (e == cudaSuccess) e = cudaMemset(h->done, 0, 256);
-    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_rows, cudaEventDisableTiming);
-    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_ws, cudaEventDisableTiming);
-    if (e != cudaSuccess) {
-        set_error("b2k_create: %s", cudaGetErrorString(e));
-        if (h->stream) cudaStreamDestroy(h->stream);
-        cudaFree(h->done);
-        delete h;
-        return B2K_ECUDA;
-    }
-    *out = h;
-    return B2K_OK;
+    std::shared_ptr<RowStore> rs;
+    rc = new_store(d, device, &rs);
+    if (rc) return rc;
+    return make_handle(d, device, sm, rs, 0, out);
+}
+
+int b2k_create_multi(int d, const int* devices, int ndev, b2k_index** out) {
+    if (!out) { set_error("b2k_create_multi: out is null"); return B2K_EINVAL; }
+    *out = nullptr;
+    if (!devices || ndev <= 0) { set_error("b2k_create_multi: empty device list"); return B2K_EINVAL; }
+    if (ndev == 1) return b2k_create(d, devices[0], out);
+    return multi_create(d, devices, ndev, out);
+}
+
+int b2k_view(const b2k_index* src, int64_t nrows, b2k_index** out) {
+    if (!src || !out) { set_error("b2k_view: null argument"); return B2K_EINVAL; }
+    *out = nullptr;
+    if (src->multi) return multi_view(src, nrows, out);
+    std::lock_guard<std::mutex> lk(src->mu);
+    const int64_t n = (nrows < 0 || nrows > src->ntotal) ? src->ntotal : nrows;
+    DeviceGuard g(src->device);
+    return make_handle(src->d, src->device, src->sm_count, src->rs, n, out);
 }
 
 int b2k_destroy(b2k_index* h) {
     if (!h) return B2K_OK;
+    if (h->multi) { multi_destroy(h); return B2K_OK; }
     DeviceGuard g(h->device);
-    cudaDeviceSynchronize();
+    // work of this handle may still be in flight; work of other handles on a shared store is the store's business
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    if (h->ev_ws) cudaEventSynchronize(h->ev_ws);
     if (h->k3) k3_destroy(h->k3);
-    cudaFree(h->x); cudaFree(h->norms); cudaFree(h->xlo); cudaFree(h->xbf); cudaFree(h->ws); cudaFree(h->done);
+    cudaFree(h->ws); cudaFree(h->done);
     if (h->pin) cudaFreeHost(h->pin);
-    if (h->ev_rows) cudaEventDestroy(h->ev_rows);
     if (h->ev_ws) cudaEventDestroy(h->ev_ws);
     if (h->ev_t0) cudaEventDestroy(h->ev_t0);
     if (h->ev_t1) cudaEventDestroy(h->ev_t1);
     if (h->stream) cudaStreamDestroy(h->stream);
+    h->rs.reset();
     delete h;
     return B2K_OK;
 }
@@ -374,6 +488,7 @@ int b2k_d(const b2k_index* h) { return h ? h->d : -1; }
 
 int b2k_set_option(b2k_index* h, const char* key, int64_t value) {
     if (!h || !key) { set_error("b2k_set_option: null argument"); return B2K_EINVAL; }
+    if (h->multi) return multi_set_option(h, key, value);
     std::lock_guard<std::mutex> lk(h->mu);
     if (!strcmp(key, "path")) {
         if (value < 0 || value > 2) { set_error("option path must be 0, 1 or 2"); return B2K_EINVAL; }
@@ -404,7 +519,7 @@ int b2k_set_option(b2k_index* h, const char* key, int64_t value) {
         // device address of a caller-owned 32-bit word (0 = off): batched searches then do not
         // synchronise; they raise the word when the screening lists could not hold every candidate,
         // and the caller must check it (after its own synchronisation) and repeat that search with
-        // tensor_mode = 1.  Used by the sharded index, which ships the word with its all-gather.
+        // tensor_mode = 1.  Used by the sharded indexes, which collect the words of all shards.
         h->opt_flag_ptr = reinterpret_cast<unsigned int*>(static_cast<uintptr_t>(value));
         if (h->k3) k3_set_ext_flag(h->k3, h->opt_flag_ptr);
     } else if (!strcmp(key, "scan_rows")) {
@@ -425,11 +540,14 @@ int b2k_set_option(b2k_index* h, const char* key, int64_t value) {
 
 int b2k_get_stat(b2k_index* h, const char* key, double* out) {
     if (!h || !key || !out) { set_error("b2k_get_stat: null argument"); return B2K_EINVAL; }
+    if (h->multi) return multi_get_stat(h, key, out);
     std::lock_guard<std::mutex> lk(h->mu);
     if (!strcmp(key, "last_path")) { *out = h->last_path; return B2K_OK; }
     if (!strcmp(key, "tensor_mode_used")) { *out = h->k3 ? k3_last_mode(h->k3) : 0; return B2K_OK; }
     if (!strcmp(key, "screen_fallbacks")) { *out = (double)h->stat_screen_fallbacks; return B2K_OK; }
     if (!strcmp(key, "scan_rows_used")) { *out = h->last_scan_bf ? 2 : 1; return B2K_OK; }
+    if (!strcmp(key, "shares_rows")) { *out = h->rs.use_count() > 1 ? 1 : 0; return B2K_OK; }
+    if (!strcmp(key, "devices")) { *out = 1; return B2K_OK; }
     if (!strcmp(key, "scan_fallback")) {  // 1 if the last bf16 scan had to be redone on the fp32 rows (synchronises)
         DeviceGuard g(h->device);
         unsigned int f = 0;
@@ -442,6 +560,7 @@ int b2k_get_stat(b2k_index* h, const char* key, double* out) {
     }
     if (!strcmp(key, "tensor_kernel_ms")) {
         float ms = 0.f;
+        DeviceGuard g(h->device);
         if (!h->k3 || k3_last_kernel_ms(h->k3, &ms)) { set_error("no timed tensor-core kernel yet (set option timing=1)"); return B2K_EINVAL; }
         *out = ms;
         return B2K_OK;
@@ -462,22 +581,23 @@ int b2k_get_stat(b2k_index* h, const char* key, double* out) {
 
 int b2k_reserve(b2k_index* h, int64_t nrows) {
     if (!h || nrows < 0) { set_error("b2k_reserve: bad argument"); return B2K_EINVAL; }
+    if (h->multi) return multi_reserve(h, nrows);
     std::lock_guard<std::mutex> lk(h->mu);
     DeviceGuard g(h->device);
-    return grow(h, nrows);
+    std::unique_lock<std::shared_mutex> sl(h->rs->mu);
+    return grow(h->rs.get(), nrows, h->stream);
 }
 
 int b2k_reset(b2k_index* h) {
     if (!h) { set_error("b2k_reset: null handle"); return B2K_EINVAL; }
+    if (h->multi) return multi_reset(h);
     std::lock_guard<std::mutex> lk(h->mu);
     DeviceGuard g(h->device);
-    B2K_CUDA(cudaDeviceSynchronize());
-    cudaFree(h->x); cudaFree(h->norms); cudaFree(h->xlo); cudaFree(h->xbf);
-    h->x = h->norms = h->xlo = nullptr;
-    h->xbf = nullptr;
-    h->bf_nomem = false;
-    h->screen_fail_streak = 0;
-    h->ntotal = h->capacity = 0;
+    B2K_CUDA(cudaStreamSynchronize(h->stream));
+    B2K_CUDA(cudaEventSynchronize(h->ev_ws));
+    int rc = detach(h, false);  // a fresh empty store; the old one is freed with its last handle
+    if (rc) return rc;
+    h->ntotal = 0;
     B2K_CUDA(cudaMemset(h->done, 0, 256));
     return B2K_OK;
 }
@@ -486,45 +606,29 @@ int b2k_add(b2k_index* h, int64_t n, const float* x, int on_device, void* stream
     if (!h) { set_error("b2k_add: null handle"); return B2K_EINVAL; }
     if (n < 0 || (n > 0 && !x)) { set_error("b2k_add: bad argument (n=%lld)", (long long)n); return B2K_EINVAL; }
     if (n == 0) return B2K_OK;
+    if (h->multi) return multi_add(h, n, x, on_device, stream);
     std::lock_guard<std::mutex> lk(h->mu);
     if (h->sticky) { set_error("handle has a sticky CUDA error (%d)", h->sticky); return B2K_ECUDA; }
     DeviceGuard g(h->device);
-    int rc = grow(h, h->ntotal + n);
-    if (rc) return rc;
     cudaStream_t st = on_device ? (cudaStream_t)stream : h->stream;
-    float* dst = h->x + h->ntotal * (int64_t)h->d;
-    size_t bytes = (size_t)n * h->d * sizeof(float);
-    // ev_rows is one event: before it is re-recorded on this stream, this stream takes over the
-    // dependency on whatever stream recorded it last, so "all rows so far" stays one wait
-    B2K_CUDA(cudaStreamWaitEvent(st, h->ev_rows, 0));
-    B2K_CUDA(cudaMemcpyAsync(dst, x, bytes, on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, st));
-    rc = prep_new_rows(h, h->ntotal, n, st);
-    if (rc) return rc;
-    B2K_CUDA(cudaEventRecord(h->ev_rows, st));
-    h->ntotal += n;
-    if (!on_device) {
-        cudaError_t e = cudaStreamSynchronize(st);
-        if (e != cudaSuccess) { h->sticky = (int)e; set_error("b2k_add: %s", cudaGetErrorString(e)); return B2K_ECUDA; }
-    }
-    return B2K_OK;
+    const size_t bytes = (size_t)n * h->d * sizeof(float);
+    return append_rows(h, n, st, !on_device, [&](float* dst, cudaStream_t s) -> int {
+        // (cudaMemcpyDefault: a device source may live on another GPU of the process -- the multi-GPU handle's adds)
+        B2K_CUDA(cudaMemcpyAsync(dst, x, bytes, on_device ? cudaMemcpyDefault : cudaMemcpyHostToDevice, s));
+        return B2K_OK;
+    });
 }
 
 int b2k_add_synthetic(b2k_index* h, int64_t n, uint64_t seed, int64_t first_row) {
     if (!h || n < 0) { set_error("b2k_add_synthetic: bad argument"); return B2K_EINVAL; }
     if (n == 0) return B2K_OK;
+    if (h->multi) return multi_add_synthetic(h, n, seed, first_row);
     std::lock_guard<std::mutex> lk(h->mu);
     DeviceGuard g(h->device);
-    int rc = grow(h, h->ntotal + n);
-    if (rc) return rc;
-    B2K_CUDA(cudaStreamWaitEvent(h->stream, h->ev_rows, 0));
-    rc = launch_synth(seed, first_row, n, h->d, h->x + h->ntotal * (int64_t)h->d, h->stream);
-    if (rc) return rc;
-    rc = prep_new_rows(h, h->ntotal, n, h->stream);
-    if (rc) return rc;
-    B2K_CUDA(cudaEventRecord(h->ev_rows, h->stream));
-    h->ntotal += n;
-    B2K_CUDA(cudaStreamSynchronize(h->stream));
-    return B2K_OK;
+    const int d = h->d;
+    return append_rows(h, n, h->stream, true, [&](float* dst, cudaStream_t s) -> int {
+        return launch_synth(seed, first_row, n, d, dst, s);
+    });
 }
 
 int b2k_synth(int device, uint64_t seed, int64_t row0, int64_t nrows, int d, float* out_dev, void* stream) {
@@ -538,15 +642,18 @@ int b2k_synth(int device, uint64_t seed, int64_t row0, int64_t nrows, int d, flo
     return B2K_OK;
 }
 
-int b2k_get_rows(const b2k_index* h, int64_t i0, int64_t n, float* out, int on_device) {
+int b2k_get_rows(const b2k_index* hc, int64_t i0, int64_t n, float* out, int on_device) {
+    b2k_index* h = const_cast<b2k_index*>(hc);
     if (!h || i0 < 0 || n < 0 || (n > 0 && !out)) { set_error("b2k_get_rows: bad argument"); return B2K_EINVAL; }
+    if (h->multi) return multi_get_rows(h, i0, n, out, on_device);
     std::lock_guard<std::mutex> lk(h->mu);
     if (i0 + n > h->ntotal) { set_error("b2k_get_rows: rows [%lld,%lld) out of range (ntotal=%lld)", (long long)i0, (long long)(i0 + n), (long long)h->ntotal); return B2K_EINVAL; }
     if (n == 0) return B2K_OK;
     DeviceGuard g(h->device);
-    B2K_CUDA(cudaStreamWaitEvent(h->stream, h->ev_rows, 0));
-    B2K_CUDA(cudaMemcpyAsync(out, h->x + i0 * (int64_t)h->d, (size_t)n * h->d * sizeof(float),
-                             on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, h->stream));
+    std::shared_lock<std::shared_mutex> sl(h->rs->mu);
+    B2K_CUDA(cudaStreamWaitEvent(h->stream, h->rs->ev_rows, 0));
+    B2K_CUDA(cudaMemcpyAsync(out, h->rs->x + i0 * (int64_t)h->d, (size_t)n * h->d * sizeof(float),
+                             on_device ? cudaMemcpyDefault : cudaMemcpyDeviceToHost, h->stream));
     B2K_CUDA(cudaStreamSynchronize(h->stream));
     return B2K_OK;
 }
@@ -558,9 +665,11 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
     if (nq < 0 || (nq > 0 && (!xq || !D || !I))) { set_error("b2k_search: bad argument"); return B2K_EINVAL; }
     if (k > B2K_MAX_K) { set_error("b2k_search: k=%lld exceeds B2K_MAX_K=%d", (long long)k, B2K_MAX_K); return B2K_ELIMIT; }
     if (nq == 0) return B2K_OK;
+    if (h->multi) return multi_search(h, nq, xq, k, D, I, on_device, stream);
     std::lock_guard<std::mutex> lk(h->mu);
     if (h->sticky) { set_error("handle has a sticky CUDA error (%d)", h->sticky); return B2K_ECUDA; }
     DeviceGuard g(h->device);
+    RowStore* rs = h->rs.get();
     const int kk = (int)k;
     cudaStream_t st = on_device ? (cudaStream_t)stream : h->stream;
 
@@ -593,7 +702,7 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
     }
     int rc = ensure_ws(h, io_bytes + align256(scratch));
     if (rc) return rc;
-    B2K_CUDA(cudaStreamWaitEvent(st, h->ev_rows, 0));
+    B2K_CUDA(cudaStreamWaitEvent(st, rs->ev_rows, 0));
     B2K_CUDA(cudaStreamWaitEvent(st, h->ev_ws, 0));
     unsigned char* wsb = static_cast<unsigned char*>(h->ws);
     const float* qd = xq;
@@ -628,13 +737,14 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
         // 16-byte bf16 pitch; if the bf16 copies do not fit in memory the TF32 screening serves
         // instead), 4 = 3xTF32 as a screen.  2, 3 and 4 end in the exact fp32 re-rank.
         int mode = h->opt_tensor_mode == 0 ? 3 : h->opt_tensor_mode;
-        if (mode == 3 && (h->d % 8 != 0 || h->bf_nomem)) mode = 2;
+        if (mode == 3 && (h->d % 8 != 0 || rs->bf_nomem)) mode = 2;
         // an index whose cheap screen keeps overflowing (outlier norms, offset data) starts at the
         // 3xTF32 screen; every 64th search tries the cheap one again (rows may have changed)
         if ((mode == 2 || mode == 3) && h->opt_tensor_mode == 0 && h->screen_fail_streak >= 2 && (++h->screen_skipped & 63) != 0) mode = 4;
-        if (mode == 3 && enable_bf(h, st) != B2K_OK) mode = 2;
-        if (mode == 4 && h->opt_tensor_mode == 0 && enable_lo(h, st) != B2K_OK) mode = 2;  // no room for the residual rows: cheap screen, then the scan
-        if (mode == 1 || mode == 4) rc = enable_lo(h, st);
+        // (the derived copies are created before the shared lock is taken: creating them needs it exclusively)
+        if (mode == 3 && enable_bf(rs, st) != B2K_OK) mode = 2;
+        if (mode == 4 && h->opt_tensor_mode == 0 && enable_lo(rs, st) != B2K_OK) mode = 2;  // no room for the residual rows: cheap screen, then the scan
+        if (mode == 1 || mode == 4) rc = enable_lo(rs, st);
         const bool cheap = mode == 2 || mode == 3;
         bool cheap_failed = false;
         if (!rc && !h->k3) {
@@ -654,22 +764,28 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
             const int64_t nqc = nq - q0 < TC_QUERY_CHUNK ? nq - q0 : TC_QUERY_CHUNK;
             const float* qc = qd + q0 * (int64_t)h->d;
             int overflowed = 0;
-            rc = k3_search(h->k3, h->x, h->xlo, h->xbf, h->norms, h->done + MAX_NORM_SLOT, h->done + MAX_ERR_SLOT, h->ntotal,
-                           h->d, qc, nqc, kk, Dd + q0 * kk, Id + q0 * kk, ws_tail, st, mode, &overflowed);
+            {
+                std::shared_lock<std::shared_mutex> sl(rs->mu);
+                rc = k3_search(h->k3, rs->x, rs->xlo, rs->xbf, rs->norms, rs->stat + MAX_NORM_SLOT, rs->stat + MAX_ERR_SLOT, h->ntotal,
+                               h->d, qc, nqc, kk, Dd + q0 * kk, Id + q0 * kk, ws_tail, st, mode, &overflowed);
+            }
             if (!rc && overflowed && mode != 4) {
                 cheap_failed = true;
                 // the slack zone of the cheap screen did not fit its lists (masses of near-duplicates around
                 // the k-th neighbour, or a distribution whose norms dwarf its distances): repeat this chunk
                 // with the 3xTF32 product as the screen, whose zone is ~10^4 times narrower
                 ++h->stat_screen_fallbacks;
-                if (enable_lo(h, st) == B2K_OK)  // (no room for the residual rows: straight to the scan, overflowed stays set)
-                    rc = k3_search(h->k3, h->x, h->xlo, h->xbf, h->norms, h->done + MAX_NORM_SLOT, h->done + MAX_ERR_SLOT,
+                if (enable_lo(rs, st) == B2K_OK) {  // (no room for the residual rows: straight to the scan, overflowed stays set)
+                    std::shared_lock<std::shared_mutex> sl(rs->mu);
+                    rc = k3_search(h->k3, rs->x, rs->xlo, rs->xbf, rs->norms, rs->stat + MAX_NORM_SLOT, rs->stat + MAX_ERR_SLOT,
                                    h->ntotal, h->d, qc, nqc, kk, Dd + q0 * kk, Id + q0 * kk, ws_tail, st, 4, &overflowed);
+                }
             }
             if (!rc && overflowed) {
                 // even that zone is crowded (exact duplicates by the thousand): the scan kernel is exact whatever the data
                 ++h->stat_screen_fallbacks;
                 h->last_path = 1;
+                std::shared_lock<std::shared_mutex> sl(rs->mu);
                 rc = scan_search(h, nqc, qc, kk, Dd + q0 * kk, Id + q0 * kk, ws_tail, st, false);
             }
         }
@@ -677,7 +793,8 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
     } else {
         h->last_path = 1;
         bool bf = scan_wants_bf(h, kk);
-        if (bf && enable_bf(h, st) != B2K_OK) bf = false;  // no room for the copies: fp32 rows (the workspace is large enough for either)
+        if (bf && enable_bf(rs, st) != B2K_OK) bf = false;  // no room for the copies: fp32 rows (the workspace is large enough for either)
+        std::shared_lock<std::shared_mutex> sl(rs->mu);
         rc = scan_search(h, nq, qd, kk, Dd, Id, ws_tail, st, bf);
     }
     if (rc) return rc;
@@ -697,6 +814,13 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
     return B2K_OK;
 }
 
+// Device-side scratch of b2k_merge_topk for host callers / id offsets: one small buffer per device, grown on demand
+// (no cudaMalloc / cudaFree per call), guarded by a mutex that also serialises its users.
+namespace {
+struct MergeScratch { std::mutex mu; void* p = nullptr; size_t bytes = 0; };
+MergeScratch g_merge_scratch[64];
+}  // namespace
+
 int b2k_merge_topk(int device, int nlists, int64_t nq, int64_t k, const float* Din, const int64_t* Iin,
                    const int64_t* id_offset, float* D, int64_t* I, int on_device, void* stream) {
     if (nlists <= 0 || nq < 0 || k <= 0 || (nq > 0 && (!Din || !Iin || !D || !I))) {
@@ -707,47 +831,64 @@ int b2k_merge_topk(int device, int nlists, int64_t nq, int64_t k, const float* D
     if (nq == 0) return B2K_OK;
     int rc = check_device(device, nullptr);
     if (rc) return rc;
+    if (device >= 64) { set_error("b2k_merge_topk: device %d out of range", device); return B2K_EINVAL; }
     DeviceGuard g(device);
     cudaStream_t st = (cudaStream_t)stream;
     size_t in_n = (size_t)nlists * nq * k, out_n = (size_t)nq * k;
     int64_t* off_d = nullptr;
     float *Din_d = const_cast<float*>(Din), *D_d = D;
     int64_t *Iin_d = const_cast<int64_t*>(Iin), *I_d = I;
-    unsigned char* tmp = nullptr;
     size_t off_bytes = align256(id_offset ? (size_t)nlists * 8 : 0);
     size_t a = align256(in_n * 4), b = align256(in_n * 8), c = align256(out_n * 4), e2 = align256(out_n * 8);
     size_t need = off_bytes + (on_device ? 0 : a + b + c + e2);
-    if (need) {
-        cudaError_t e = cudaMalloc(&tmp, need);
+    if (!need) return launch_merge_lists(nlists, nq, (int)k, Din_d, Iin_d, nullptr, D_d, I_d, st);
+    MergeScratch& ms = g_merge_scratch[device];
+    std::lock_guard<std::mutex> lk(ms.mu);
+    if (need > ms.bytes) {
+        if (ms.p) { cudaDeviceSynchronize(); cudaFree(ms.p); ms.p = nullptr; ms.bytes = 0; }
+        cudaError_t e = cudaMalloc(&ms.p, need + need / 2);
         if (e != cudaSuccess) { cudaGetLastError(); set_error("b2k_merge_topk: cudaMalloc failed: %s", cudaGetErrorString(e)); return B2K_ENOMEM; }
+        ms.bytes = need + need / 2;
     }
-    rc = B2K_OK;
-    do {
-        cudaError_t e = cudaSuccess;
-        if (id_offset) {
-            off_d = reinterpret_cast<int64_t*>(tmp);
-            e = cudaMemcpyAsync(off_d, id_offset, (size_t)nlists * 8, cudaMemcpyHostToDevice, st);
-        }
-        if (e == cudaSuccess && !on_device) {
-            Din_d = reinterpret_cast<float*>(tmp + off_bytes);
-            Iin_d = reinterpret_cast<int64_t*>(tmp + off_bytes + a);
-            D_d = reinterpret_cast<float*>(tmp + off_bytes + a + b);
-            I_d = reinterpret_cast<int64_t*>(tmp + off_bytes + a + b + c);
-            e = cudaMemcpyAsync(Din_d, Din, in_n * 4, cudaMemcpyHostToDevice, st);
-            if (e == cudaSuccess) e = cudaMemcpyAsync(Iin_d, Iin, in_n * 8, cudaMemcpyHostToDevice, st);
-        }
-        if (e != cudaSuccess) { set_error("b2k_merge_topk: %s", cudaGetErrorString(e)); rc = B2K_ECUDA; break; }
-        rc = launch_merge_lists(nlists, nq, (int)k, Din_d, Iin_d, off_d, D_d, I_d, st);
-        if (rc) break;
-        if (!on_device) {
-            e = cudaMemcpyAsync(D, D_d, out_n * 4, cudaMemcpyDeviceToHost, st);
-            if (e == cudaSuccess) e = cudaMemcpyAsync(I, I_d, out_n * 8, cudaMemcpyDeviceToHost, st);
-        }
-        if (e == cudaSuccess && tmp) e = cudaStreamSynchronize(st);  // tmp is freed below
-        if (e != cudaSuccess) { set_error("b2k_merge_topk: %s", cudaGetErrorString(e)); rc = B2K_ECUDA; }
-    } while (0);
-    if (tmp) cudaFree(tmp);
-    return rc;
+    unsigned char* tmp = static_cast<unsigned char*>(ms.p);
+    cudaError_t e = cudaSuccess;
+    if (id_offset) {
+        off_d = reinterpret_cast<int64_t*>(tmp);
+        e = cudaMemcpyAsync(off_d, id_offset, (size_t)nlists * 8, cudaMemcpyHostToDevice, st);
+    }
+    if (e == cudaSuccess && !on_device) {
+        Din_d = reinterpret_cast<float*>(tmp + off_bytes);
+        Iin_d = reinterpret_cast<int64_t*>(tmp + off_bytes + a);
+        D_d = reinterpret_cast<float*>(tmp + off_bytes + a + b);
+        I_d = reinterpret_cast<int64_t*>(tmp + off_bytes + a + b + c);
+        e = cudaMemcpyAsync(Din_d, Din, in_n * 4, cudaMemcpyHostToDevice, st);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(Iin_d, Iin, in_n * 8, cudaMemcpyHostToDevice, st);
+    }
+    if (e != cudaSuccess) { set_error("b2k_merge_topk: %s", cudaGetErrorString(e)); return B2K_ECUDA; }
+    rc = launch_merge_lists(nlists, nq, (int)k, Din_d, Iin_d, off_d, D_d, I_d, st);
+    if (rc) return rc;
+    if (!on_device) {
+        e = cudaMemcpyAsync(D, D_d, out_n * 4, cudaMemcpyDeviceToHost, st);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(I, I_d, out_n * 8, cudaMemcpyDeviceToHost, st);
+    }
+    // the scratch is shared: the next user may overwrite it, so this call's work is finished before the lock goes
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) { set_error("b2k_merge_topk: %s", cudaGetErrorString(e)); return B2K_ECUDA; }
+    return B2K_OK;
+}
+
+int b2k_merge_shards(int device, int nlists, int64_t nq, int64_t k, const float* Din, int64_t list_stride_d,
+                     const int64_t* Iin, int64_t list_stride_i, int64_t cyclic_block, float* D, int64_t* I, void* stream) {
+    if (nlists <= 0 || nq < 0 || k <= 0 || cyclic_block < 0 || (nq > 0 && (!Din || !Iin || !D || !I))) {
+        set_error("b2k_merge_shards: bad argument");
+        return B2K_EINVAL;
+    }
+    if ((int64_t)nlists * k > 8192) { set_error("b2k_merge_shards: nlists*k = %lld exceeds 8192", (long long)nlists * k); return B2K_ELIMIT; }
+    if (nq == 0) return B2K_OK;
+    int rc = check_device(device, nullptr);
+    if (rc) return rc;
+    DeviceGuard g(device);
+    return launch_merge_shards(nlists, nq, (int)k, Din, list_stride_d, Iin, list_stride_i, cyclic_block, D, I, (cudaStream_t)stream);
 }
 
 // ---- IxF2 persistence ------------------------------------------------------------------
@@ -755,45 +896,42 @@ int b2k_merge_topk(int device, int nlists, int64_t nq, int64_t k, const float* D
 //   "IxF2" | d int32 | ntotal int64 | 1<<20 int64 | 1<<20 int64 | is_trained u8 (1) |
 //   metric_type int32 (1 = L2) | count u64 (= ntotal*d) | count float32
 
-static const size_t IXF2_HEADER = 45;
-
-static void put_header(unsigned char* b, int d, int64_t n) {
-    memcpy(b, "IxF2", 4);
-    int32_t d32 = d; memcpy(b + 4, &d32, 4);
-    memcpy(b + 8, &n, 8);
-    int64_t dummy = 1 << 20; memcpy(b + 16, &dummy, 8); memcpy(b + 24, &dummy, 8);
-    b[32] = 1;
-    int32_t metric = 1; memcpy(b + 33, &metric, 4);
-    uint64_t count = (uint64_t)n * (uint64_t)d; memcpy(b + 37, &count, 8);
+// rows [row0, row0 + nrows) of the handle -> f, through the pinned staging buffer
+static int write_rows(b2k_index* h, FILE* f, int64_t row0, int64_t nrows, const char* what) {
+    const size_t row_bytes = (size_t)h->d * sizeof(float);
+    size_t total = (size_t)nrows * row_bytes, done = 0;
+    if (!total) return B2K_OK;
+    int rc = ensure_pin(h, total < IO_CHUNK ? total : IO_CHUNK);
+    if (rc) return rc;
+    std::shared_lock<std::shared_mutex> sl(h->rs->mu);
+    B2K_CUDA(cudaStreamWaitEvent(h->stream, h->rs->ev_rows, 0));
+    const unsigned char* src = reinterpret_cast<const unsigned char*>(h->rs->x) + (size_t)row0 * row_bytes;
+    while (done < total) {
+        size_t n = total - done < IO_CHUNK ? total - done : IO_CHUNK;
+        cudaError_t e = cudaMemcpyAsync(h->pin, src + done, n, cudaMemcpyDeviceToHost, h->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+        if (e != cudaSuccess) { set_error("%s: %s", what, cudaGetErrorString(e)); return B2K_ECUDA; }
+        if (fwrite(h->pin, 1, n, f) != n) { set_error("%s: write error: %s", what, strerror(errno)); return B2K_EIO; }
+        done += n;
+    }
+    return B2K_OK;
 }
 
 int b2k_write(const b2k_index* hc, const char* path) {
     b2k_index* h = const_cast<b2k_index*>(hc);
     if (!h || !path) { set_error("b2k_write: null argument"); return B2K_EINVAL; }
+    if (h->multi) return multi_write(h, path, 0, false);
     std::lock_guard<std::mutex> lk(h->mu);
     DeviceGuard g(h->device);
     std::string tmp = std::string(path) + ".tmp";
     FILE* f = fopen(tmp.c_str(), "wb");
     if (!f) { set_error("could not open %s for writing: %s", tmp.c_str(), strerror(errno)); return B2K_EIO; }
     unsigned char hdr[IXF2_HEADER];
-    put_header(hdr, h->d, h->ntotal);
+    ixf2_put_header(hdr, h->d, h->ntotal);
     int rc = B2K_OK;
-    if (fwrite(hdr, 1, IXF2_HEADER, f) != IXF2_HEADER) rc = B2K_EIO;
-    size_t total = (size_t)h->ntotal * h->d * sizeof(float), done = 0;
-    if (!rc && total) {
-        rc = ensure_pin(h, total < IO_CHUNK ? total : IO_CHUNK);
-        if (!rc && cudaStreamWaitEvent(h->stream, h->ev_rows, 0) != cudaSuccess) { set_error("b2k_write: cudaStreamWaitEvent failed"); rc = B2K_ECUDA; }
-        while (!rc && done < total) {
-            size_t n = total - done < IO_CHUNK ? total - done : IO_CHUNK;
-            cudaError_t e = cudaMemcpyAsync(h->pin, reinterpret_cast<unsigned char*>(h->x) + done, n, cudaMemcpyDeviceToHost, h->stream);
-            if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
-            if (e != cudaSuccess) { set_error("b2k_write: %s", cudaGetErrorString(e)); rc = B2K_ECUDA; break; }
-            if (fwrite(h->pin, 1, n, f) != n) { rc = B2K_EIO; break; }
-            done += n;
-        }
-    }
-    if (fclose(f) != 0 && !rc) rc = B2K_EIO;
-    if (rc == B2K_EIO) set_error("error writing %s: %s", tmp.c_str(), strerror(errno));
+    if (fwrite(hdr, 1, IXF2_HEADER, f) != IXF2_HEADER) { set_error("error writing %s: %s", tmp.c_str(), strerror(errno)); rc = B2K_EIO; }
+    if (!rc) rc = write_rows(h, f, 0, h->ntotal, "b2k_write");
+    if (fclose(f) != 0 && !rc) { set_error("error writing %s: %s", tmp.c_str(), strerror(errno)); rc = B2K_EIO; }
     if (!rc && rename(tmp.c_str(), path) != 0) { set_error("could not rename %s to %s: %s", tmp.c_str(), path, strerror(errno)); rc = B2K_EIO; }
     if (rc) remove(tmp.c_str());
     return rc;
@@ -802,13 +940,14 @@ int b2k_write(const b2k_index* hc, const char* path) {
 int b2k_write_append(const b2k_index* hc, const char* path, int64_t first_row) {
     b2k_index* h = const_cast<b2k_index*>(hc);
     if (!h || !path || first_row < 0) { set_error("b2k_write_append: bad argument"); return B2K_EINVAL; }
+    if (h->multi) return multi_write(h, path, first_row, true);
     std::lock_guard<std::mutex> lk(h->mu);
     if (first_row > h->ntotal) { set_error("b2k_write_append: first_row %lld > ntotal %lld", (long long)first_row, (long long)h->ntotal); return B2K_EINVAL; }
     DeviceGuard g(h->device);
     FILE* f = fopen(path, "r+b");
     if (!f) { set_error("could not open %s for appending: %s", path, strerror(errno)); return B2K_EIO; }
     unsigned char hdr[IXF2_HEADER], want[IXF2_HEADER];
-    put_header(want, h->d, first_row);
+    ixf2_put_header(want, h->d, first_row);
     int rc = B2K_OK;
     if (fread(hdr, 1, IXF2_HEADER, f) != IXF2_HEADER || memcmp(hdr, want, IXF2_HEADER) != 0) {
         set_error("%s does not hold exactly the first %lld rows of a d=%d IxF2 index", path, (long long)first_row, h->d);
@@ -821,24 +960,11 @@ int b2k_write_append(const b2k_index* hc, const char* path, int64_t first_row) {
             rc = B2K_EINVAL;
         }
     }
-    size_t total = (size_t)(h->ntotal - first_row) * row_bytes, done = 0;
-    if (!rc && total) {
-        rc = ensure_pin(h, total < IO_CHUNK ? total : IO_CHUNK);
-        if (!rc && cudaStreamWaitEvent(h->stream, h->ev_rows, 0) != cudaSuccess) { set_error("b2k_write_append: cudaStreamWaitEvent failed"); rc = B2K_ECUDA; }
-        const unsigned char* src = reinterpret_cast<const unsigned char*>(h->x) + (size_t)first_row * row_bytes;
-        while (!rc && done < total) {
-            size_t n = total - done < IO_CHUNK ? total - done : IO_CHUNK;
-            cudaError_t e = cudaMemcpyAsync(h->pin, src + done, n, cudaMemcpyDeviceToHost, h->stream);
-            if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
-            if (e != cudaSuccess) { set_error("b2k_write_append: %s", cudaGetErrorString(e)); rc = B2K_ECUDA; break; }
-            if (fwrite(h->pin, 1, n, f) != n) { set_error("error appending to %s: %s", path, strerror(errno)); rc = B2K_EIO; break; }
-            done += n;
-        }
-    }
+    if (!rc) rc = write_rows(h, f, first_row, h->ntotal - first_row, "b2k_write_append");
     if (!rc) {
         // rows first, header last: a reader that opens the file in between still sees a consistent
         // (old) header and ignores the extra bytes behind the payload it describes
-        put_header(want, h->d, h->ntotal);
+        ixf2_put_header(want, h->d, h->ntotal);
         if (fflush(f) != 0 || fseeko(f, 0, SEEK_SET) != 0 || fwrite(want, 1, IXF2_HEADER, f) != IXF2_HEADER) {
             set_error("error updating the header of %s: %s", path, strerror(errno));
             rc = B2K_EIO;
@@ -855,56 +981,61 @@ int b2k_read(const char* path, int device, b2k_index** out) {
     if (!f) { set_error("could not open %s for reading: %s", path, strerror(errno)); return B2K_EIO; }
     unsigned char hdr[IXF2_HEADER];
     if (fread(hdr, 1, IXF2_HEADER, f) != IXF2_HEADER) { fclose(f); set_error("%s: short read of the index header", path); return B2K_EIO; }
-    if (memcmp(hdr, "IxF2", 4) != 0) {
-        fclose(f);
-        set_error("%s: index type '%.4s' not supported (only IxF2 = IndexFlatL2)", path, (const char*)hdr);
-        return B2K_EIO;
-    }
-    int32_t d32, metric; int64_t n; uint64_t count;
-    memcpy(&d32, hdr + 4, 4); memcpy(&n, hdr + 8, 8); memcpy(&metric, hdr + 33, 4); memcpy(&count, hdr + 37, 8);
-    if (d32 <= 0 || n < 0 || metric != 1 || count != (uint64_t)n * (uint64_t)d32) {
-        fclose(f);
-        set_error("%s: inconsistent IxF2 header (d=%d ntotal=%lld metric=%d count=%llu)", path, d32, (long long)n, metric, (unsigned long long)count);
-        return B2K_EIO;
-    }
+    int d32 = 0; int64_t n = 0;
+    int rc = ixf2_parse_header(hdr, path, &d32, &n);
+    if (rc) { fclose(f); return rc; }
     b2k_index* h = nullptr;
-    int rc = b2k_create(d32, device, &h);
+    rc = b2k_create(d32, device, &h);
     if (rc) { fclose(f); return rc; }
     {
         std::lock_guard<std::mutex> lk(h->mu);
         DeviceGuard g(h->device);
+        RowStore* rs = h->rs.get();
+        std::unique_lock<std::shared_mutex> sl(rs->mu);
         size_t total = (size_t)n * d32 * sizeof(float), done = 0;
-        if (n > 0) rc = grow(h, n);
+        if (n > 0) rc = grow(rs, n, h->stream);
         if (!rc && total) {
             // two pinned halves: the H2D copy of one overlaps the fread of the other
             size_t half = total < IO_CHUNK ? total : IO_CHUNK;
             rc = ensure_pin(h, 2 * half);
             int which = 0;
             cudaEvent_t ev[2] = {nullptr, nullptr};
-            if (!rc) { cudaEventCreateWithFlags(&ev[0], cudaEventDisableTiming); cudaEventCreateWithFlags(&ev[1], cudaEventDisableTiming); }
+            if (!rc && (cudaEventCreateWithFlags(&ev[0], cudaEventDisableTiming) != cudaSuccess ||
+                        cudaEventCreateWithFlags(&ev[1], cudaEventDisableTiming) != cudaSuccess)) {
+                set_error("b2k_read: cudaEventCreate failed"); rc = B2K_ECUDA;
+            }
             while (!rc && done < total) {
                 size_t nb = total - done < half ? total - done : half;
                 unsigned char* buf = static_cast<unsigned char*>(h->pin) + (size_t)which * half;
                 cudaEventSynchronize(ev[which]);
                 if (fread(buf, 1, nb, f) != nb) { set_error("%s: truncated IxF2 payload", path); rc = B2K_EIO; break; }
-                cudaError_t e = cudaMemcpyAsync(reinterpret_cast<unsigned char*>(h->x) + done, buf, nb, cudaMemcpyHostToDevice, h->stream);
+                cudaError_t e = cudaMemcpyAsync(reinterpret_cast<unsigned char*>(rs->x) + done, buf, nb, cudaMemcpyHostToDevice, h->stream);
                 if (e == cudaSuccess) e = cudaEventRecord(ev[which], h->stream);
                 if (e != cudaSuccess) { set_error("b2k_read: %s", cudaGetErrorString(e)); rc = B2K_ECUDA; break; }
                 done += nb;
                 which ^= 1;
             }
-            if (!rc) rc = prep_new_rows(h, 0, n, h->stream);
+            if (!rc) rc = prep_new_rows(rs, 0, n, h->stream);
+            if (!rc && cudaEventRecord(rs->ev_rows, h->stream) != cudaSuccess) { set_error("b2k_read: cudaEventRecord failed"); rc = B2K_ECUDA; }
             cudaError_t e = cudaStreamSynchronize(h->stream);
             if (!rc && e != cudaSuccess) { set_error("b2k_read: %s", cudaGetErrorString(e)); rc = B2K_ECUDA; }
             if (ev[0]) cudaEventDestroy(ev[0]);
             if (ev[1]) cudaEventDestroy(ev[1]);
         }
-        if (!rc) h->ntotal = n;
+        if (!rc) { rs->filled = n; h->ntotal = n; }
     }
     fclose(f);
     if (rc) { b2k_destroy(h); return rc; }
     *out = h;
     return B2K_OK;
+}
+
+int b2k_read_multi(const char* path, const int* devices, int ndev, b2k_index** out) {
+    if (!path || !out) { set_error("b2k_read_multi: null argument"); return B2K_EINVAL; }
+    *out = nullptr;
+    if (!devices || ndev <= 0) { set_error("b2k_read_multi: empty device list"); return B2K_EINVAL; }
+    if (ndev == 1) return b2k_read(path, devices[0], out);
+    return multi_read(path, devices, ndev, out);
 }
 
 }  // extern "C"

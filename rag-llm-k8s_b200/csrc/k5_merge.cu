@@ -24,10 +24,16 @@ __device__ __forceinline__ bool cand_less(u64 a, u64 b, const int64_t* ids) {
     return (uint32_t)a < (uint32_t)b;
 }
 
+// List l holds [nq][k] distances at Din + l*stride_d and ids at Iin + l*stride_i (strides in elements;
+// contiguous [nlists][nq][k] arrays have stride nq*k, the packed all-gather records of the sharded
+// index have their own).  Ids are translated to global row numbers on the way in: + id_offset[l]
+// (contiguous shards), or, with cyc_block = B > 0, by the block-cyclic rule of the sharded indexes
+// (global rows go to the shards in blocks of B, round-robin): local row r of shard l is global row
+// ((r / B) * nlists + l) * B + r % B.
 __global__ void __launch_bounds__(MERGE_THREADS)
-merge_lists_kernel(int nlists, int64_t nq, int k, int P, const float* __restrict__ Din,
-                   const int64_t* __restrict__ Iin, const int64_t* __restrict__ id_offset,
-                   float* __restrict__ D, int64_t* __restrict__ I) {
+merge_lists_kernel(int nlists, int64_t nq, int k, int P, const float* __restrict__ Din, int64_t stride_d,
+                   const int64_t* __restrict__ Iin, int64_t stride_i, const int64_t* __restrict__ id_offset,
+                   int64_t cyc_block, float* __restrict__ D, int64_t* __restrict__ I) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     u64* keys = reinterpret_cast<u64*>(smem_raw);
     int64_t* ids = reinterpret_cast<int64_t*>(smem_raw + (size_t)P * 8);
@@ -38,10 +44,11 @@ merge_lists_kernel(int nlists, int64_t nq, int k, int P, const float* __restrict
         u64 key = KEY_EMPTY;
         if (s < m) {
             int l = s / k, j = s - l * k;
-            int64_t o = ((int64_t)l * nq + q) * k + j;
-            int64_t id = Iin[o];
-            float dv = Din[o];
+            const int64_t o = q * k + j;
+            int64_t id = Iin[(int64_t)l * stride_i + o];
+            float dv = Din[(int64_t)l * stride_d + o];
             if (id >= 0 && dv < FLT_MAX) {
+                if (cyc_block > 0) id = ((id / cyc_block) * nlists + l) * cyc_block + id % cyc_block;
                 ids[s] = id + (id_offset ? id_offset[l] : 0);
                 key = make_key(dv, (uint32_t)s);
             } else {
@@ -76,8 +83,9 @@ merge_lists_kernel(int nlists, int64_t nq, int k, int P, const float* __restrict
     }
 }
 
-int launch_merge_lists(int nlists, int64_t nq, int k, const float* Din, const int64_t* Iin,
-                       const int64_t* id_offset_dev, float* D, int64_t* I, cudaStream_t st) {
+static int launch_merge_any(int nlists, int64_t nq, int k, const float* Din, int64_t stride_d, const int64_t* Iin,
+                            int64_t stride_i, const int64_t* id_offset_dev, int64_t cyc_block, float* D, int64_t* I,
+                            cudaStream_t st) {
     if (nq <= 0) return B2K_OK;
     const int m = nlists * k;
     if (m > 8192) {
@@ -88,10 +96,21 @@ int launch_merge_lists(int nlists, int64_t nq, int k, const float* Din, const in
     size_t smem = (size_t)P * 8 + (size_t)m * 8;
     if (smem > 48 * 1024)  // per-device attribute: set on every large launch (a handle may live on any GPU)
         B2K_CUDA(cudaFuncSetAttribute(merge_lists_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    merge_lists_kernel<<<(unsigned)nq, MERGE_THREADS, smem, st>>>(nlists, nq, k, P, Din, Iin, id_offset_dev, D, I);
+    merge_lists_kernel<<<(unsigned)nq, MERGE_THREADS, smem, st>>>(nlists, nq, k, P, Din, stride_d, Iin, stride_i, id_offset_dev,
+                                                                  cyc_block, D, I);
     count_launch();
     B2K_CUDA(cudaGetLastError());
     return B2K_OK;
+}
+
+int launch_merge_lists(int nlists, int64_t nq, int k, const float* Din, const int64_t* Iin,
+                       const int64_t* id_offset_dev, float* D, int64_t* I, cudaStream_t st) {
+    return launch_merge_any(nlists, nq, k, Din, nq * k, Iin, nq * k, id_offset_dev, 0, D, I, st);
+}
+
+int launch_merge_shards(int nlists, int64_t nq, int k, const float* Din, int64_t stride_d, const int64_t* Iin,
+                        int64_t stride_i, int64_t cyc_block, float* D, int64_t* I, cudaStream_t st) {
+    return launch_merge_any(nlists, nq, k, Din, stride_d, Iin, stride_i, nullptr, cyc_block, D, I, st);
 }
 
 }  // namespace b2k

@@ -31,5 +31,8 @@ int launch_fill_empty(float* D, int64_t* I, int64_t count, cudaStream_t st);
 // K5 (k5_merge.cu): per query, k smallest (distance,id) of nlists*k candidates.
 int launch_merge_lists(int nlists, int64_t nq, int k, const float* Din, const int64_t* Iin,
                        const int64_t* id_offset_dev, float* D, int64_t* I, cudaStream_t st);
+// the same over lists with their own strides (elements) and block-cyclic shard-local ids (cyc_block rows per block; 0 = ids are global)
+int launch_merge_shards(int nlists, int64_t nq, int k, const float* Din, int64_t stride_d, const int64_t* Iin,
+                        int64_t stride_i, int64_t cyc_block, float* D, int64_t* I, cudaStream_t st);
 
 }  // namespace b2k

@@ -37,16 +37,17 @@ def main():
     q = O.synth(5678, 0, 40, d)
     D, I = idx.search(q, 10)
     assert_knn_matches(D, I, xs, q, 10, expanded=True, what="sharded synthetic")
-    # screening overflow on ONE shard only (near-duplicates all land on the last rank): the flag
+    # screening overflow on ONE shard only (the near-duplicates are the rows the last rank keeps): the flag
     # travels with the all-gather, every rank repeats the search (3xTF32 screen, then the scan), results stay exact
     idx.reset()
     rng = np.random.default_rng(0)
     base = rng.standard_normal((1, 64)).astype(np.float32)
     per = 20000
     z = rng.standard_normal((per * world, 64)).astype(np.float32)
-    z[per * (world - 1):] = base + rng.standard_normal((per, 64)).astype(np.float32) * 1e-6
-    z[per * (world - 1)::1000] = rng.standard_normal((20, 64)).astype(np.float32)
     idx2 = ShardedIndexFlatL2(64, device=lr)
+    last = np.where((np.arange(per * world) // idx2.block) % world == world - 1)[0]   # the rows the last rank keeps
+    z[last] = base + rng.standard_normal((len(last), 64)).astype(np.float32) * 1e-6
+    z[last[::1000]] = rng.standard_normal((len(last[::1000]), 64)).astype(np.float32)
     idx2.add(z)
     qz = (base + rng.standard_normal((30, 64)).astype(np.float32) * 0.05).astype(np.float32)
     D, I = idx2.search(qz, 10)

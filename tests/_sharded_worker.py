@@ -14,7 +14,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "rag-llm-k8s_b200"))
 from oracle import oracle as O  # noqa: E402
-from b200knn.sharded import ShardedIndexFlatL2, split_range  # noqa: E402
+from b200knn.sharded import ShardedIndexFlatL2, cyclic_pieces, split_range  # noqa: E402
 
 
 class OracleShard:
@@ -77,9 +77,9 @@ def main():
     dist.init_process_group("gloo")
     rank, world = dist.get_rank(), dist.get_world_size()
     d = 24
-    idx = ShardedIndexFlatL2(d, _local=OracleShard(d), _merge=oracle_merge)
+    idx = ShardedIndexFlatL2(d, block=16, _local=OracleShard(d), _merge=oracle_merge)
     x = O.synth(11, 0, 1003, d)
-    # several adds of awkward sizes (including fewer rows than ranks) -> several id segments per rank
+    # several adds of awkward sizes (including fewer rows than ranks) that straddle the 16-row blocks of the cyclic layout
     cuts = [0, 1, 2, 400, 401, 1003]
     for a, b in zip(cuts[:-1], cuts[1:]):
         idx.add(x[a:b])
@@ -107,11 +107,15 @@ def main():
     D, I = idx.search(q, 4)
     assert np.all(I == -1) and np.all(D == O.FLT_MAX)
     assert split_range(10, 4, 3) == (9, 10) and split_range(2, 4, 3) == (2, 2)
+    assert cyclic_pieces(10, 30, 2, 1, 16) == [(16, 16)] and cyclic_pieces(10, 30, 2, 0, 16) == [(10, 6), (32, 8)]
+    ids = np.arange(40)
+    mine = np.concatenate([np.arange(g, g + c) for g, c in cyclic_pieces(0, 40, world, rank, 16)] or [np.zeros(0, np.int64)])
+    assert np.array_equal(idx.to_global(np.arange(len(mine))), mine)     # local row -> global row is the inverse of the split
     # screening overflow on the last rank only: its flag travels with the all-gather, EVERY rank repeats
     # (3xTF32 screen, then the scan), the options are restored, the answer is the single index's
     for fail_mode4, expect in ((False, [(0, 0), (4, 0)]), (True, [(0, 0), (4, 0), (0, 1)])):
         shard = OverflowingShard(d, bad_rank=(rank == world - 1), fail_mode4=fail_mode4)
-        idx2 = ShardedIndexFlatL2(d, _local=shard, _merge=oracle_merge)
+        idx2 = ShardedIndexFlatL2(d, block=16, _local=shard, _merge=oracle_merge)
         idx2.add(x)
         q = O.synth(14, 0, 6, d)
         D, I = idx2.search(q, 7)

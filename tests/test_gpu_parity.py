@@ -199,6 +199,10 @@ def test_ixf2_bytes_and_round_trip(faiss, tmp_path):
 
 
 def test_rag_py_call_pattern(faiss, tmp_path):
+    rag_py_call_pattern(faiss, tmp_path)
+
+
+def rag_py_call_pattern(faiss, tmp_path):
     """ensure_index_exists / update_index / search_documents restated (rag.py:57-86,114-120) with
     the encoder stubbed: row id == index into the metadata list, -1 padding reaches metadata[-1]."""
     INDEX_PATH = str(tmp_path / "faiss_index")
@@ -408,11 +412,20 @@ def test_large_k_large_batch_stress(faiss):
         assert len(set(I[qi].cpu().tolist()) ^ set(Is[j].cpu().tolist())) <= 4
 
 
+def _stat(idx, key):
+    import ctypes as C
+    from b200knn import _lib
+    v = C.c_double()
+    _lib.check(_lib.lib().b2k_get_stat(idx._h, key.encode(), C.byref(v)))
+    return v.value
+
+
 def test_resident_index_cache_and_incremental_write(faiss, tmp_path, monkeypatch):
     """rag.py re-reads the index file on every request (rag.py:153) and
-    rewrites it on every upload (rag.py:74-84).  An unchanged file must come back resident (same
-    object, no reload); an index that only grew since it was loaded is appended to the file, and the
-    file stays byte-identical to a full write; any other change falls back to load / full write."""
+    rewrites it on every upload (rag.py:74-84).  An unchanged file must come back resident (its rows
+    shared in HBM, no reload) but, as with faiss, as an INDEPENDENT index each time; an index that
+    only grew since it was loaded is appended to the file, and the file stays byte-identical to a
+    full write; any other change falls back to load / full write."""
     monkeypatch.delenv("B200KNN_INDEX_CACHE", raising=False)
     faiss.clear_index_cache()
     p = str(tmp_path / "faiss_index")
@@ -422,35 +435,108 @@ def test_resident_index_cache_and_incremental_write(faiss, tmp_path, monkeypatch
     faiss.write_index(idx, p)
     a = faiss.read_index(p)
     b = faiss.read_index(p)
-    assert a is b                                   # resident: no second load
+    assert a is not b and a.ntotal == b.ntotal == 2000
+    assert _stat(a, "shares_rows") == 1 and _stat(b, "shares_rows") == 1      # resident: no second load
     a.add(x[2000:3500])                             # update_index: read -> add -> write
-    c = faiss.read_index(p)                         # the file still has 2000 rows: fresh load, not the dirty object
-    assert c is not a and c.ntotal == 2000
+    assert a.ntotal == 3500 and b.ntotal == 2000    # ... invisible to the request that holds b
+    q = O.synth(4, 0, 2, 64)
+    Db, Ib = b.search(q, 3)
+    assert_knn_matches(Db, Ib, x[:2000], q, 3, what="other view after add")
+    c = faiss.read_index(p)                         # the file still has 2000 rows
+    assert c.ntotal == 2000
+    b.add(x[4000:4100])                             # a second writer: the shared rows have moved on -> private copy
+    assert b.ntotal == 2100 and a.ntotal == 3500 and c.ntotal == 2000
+    assert np.array_equal(b.reconstruct_n(1990, 110), np.concatenate([x[1990:2000], x[4000:4100]]))
+    assert np.array_equal(a.reconstruct_n(1990, 20), x[1990:2010])
     size_before = os.path.getsize(p)
     faiss.write_index(a, p)                         # appended in place
     assert os.path.getsize(p) == 45 + 4 * 3500 * 64 and os.path.getsize(p) > size_before
     ref = str(tmp_path / "ref")
     O.write_ixf2(ref, x[:3500])
     assert open(p, "rb").read() == open(ref, "rb").read()
-    assert faiss.read_index(p) is a                 # cache follows the write
+    f = faiss.read_index(p)                         # cache follows the write: no load, rows shared with a
+    assert f.ntotal == 3500 and _stat(f, "shares_rows") == 1
+    a.add(x[3500:3600])                             # ... and what a does next does not reach f
+    assert f.ntotal == 3500
+    Df, If = f.search(q, 3)
+    assert_knn_matches(Df, If, x[:3500], q, 3, what="view of the written file")
     d2, x2 = O.read_ixf2(p)
     assert d2 == 64 and np.array_equal(x2, x[:3500])
     # a file changed behind our back is reloaded
     O.write_ixf2(p, x[:100])
     os.utime(p, ns=(1, 1))
     e = faiss.read_index(p)
-    assert e is not a and e.ntotal == 100
+    assert e.ntotal == 100
     # a reset index is written in full, not appended
     a.reset()
     a.add(x[:10])
     faiss.write_index(a, p)
     assert os.path.getsize(p) == 45 + 4 * 10 * 64
-    q = O.synth(4, 0, 2, 64)
     D, I = faiss.read_index(p).search(q, 3)
     assert_knn_matches(D, I, x[:10], q, 3, what="after rewrite")
+    assert f.ntotal == 3500 and np.array_equal(f.reconstruct_n(3490, 10), x[3490:3500])   # old views live on
     # cache off: independent loads, as faiss
     monkeypatch.setenv("B200KNN_INDEX_CACHE", "0")
-    assert faiss.read_index(p) is not faiss.read_index(p)
+    g1, g2 = faiss.read_index(p), faiss.read_index(p)
+    assert g1 is not g2 and _stat(g1, "shares_rows") == 0
+
+
+def test_requests_racing_an_upload_see_consistent_indexes(faiss, tmp_path, monkeypatch):
+    """Flask's dev server is threaded (rag.py:204): /generate (rag.py:153-157: read_index + metadata pickle +
+    search) runs while /upload_pdf (rag.py:141 -> update_index: read, add, write) runs.  Every request must
+    get an index whose rows match SOME state of the file, never rows it has no metadata for."""
+    import threading
+    monkeypatch.delenv("B200KNN_INDEX_CACHE", raising=False)
+    faiss.clear_index_cache()
+    p = str(tmp_path / "faiss_index")
+    d = 32
+    x = O.synth(9, 0, 4000, d)
+    idx = faiss.IndexFlatL2(d)
+    idx.add(x[:1000])
+    faiss.write_index(idx, p)
+    pickle.dump(list(range(1000)), open(p + ".metadata", "wb"))
+    lock = threading.Lock()          # rag.py has none; the pickle and the index file are two writes, so the test
+    errors, stop = [], []            # serialises (file, pickle) PAIRS -- what is checked is the index object itself
+
+    def uploader():
+        try:
+            for i in range(10):
+                with lock:
+                    index = faiss.read_index(p)
+                    meta = pickle.load(open(p + ".metadata", "rb"))
+                n0 = index.ntotal
+                index.add(x[n0:n0 + 300])            # outside the lock: other requests hold views meanwhile
+                with lock:
+                    faiss.write_index(index, p)
+                    pickle.dump(meta + list(range(n0, n0 + 300)), open(p + ".metadata", "wb"))
+        except Exception as e:       # noqa: BLE001
+            errors.append(repr(e))
+        stop.append(1)
+
+    def searcher(seed):
+        try:
+            q = O.synth(seed, 0, 1, d)
+            while not stop:
+                with lock:
+                    index = faiss.read_index(p)
+                    meta = pickle.load(open(p + ".metadata", "rb"))
+                n = index.ntotal
+                assert n == len(meta), (n, len(meta))
+                D, I = index.search(q, 5)
+                assert I.max() < n and I.min() >= 0
+                [meta[i] for i in I[0]]                # rag.py:118-119
+                Dr, Ir = O.search(x[:n], q, 5)
+                assert np.array_equal(I, Ir), (n, I, Ir)
+        except Exception as e:       # noqa: BLE001
+            errors.append(repr(e))
+
+    ts = [threading.Thread(target=uploader)] + [threading.Thread(target=searcher, args=(100 + i,)) for i in range(3)]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join()
+    assert not errors, errors[:3]
+    assert faiss.read_index(p).ntotal == 4000
 
 
 def test_long_query_batch_is_chunked(faiss):
