@@ -155,6 +155,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--rows", type=int, default=0, help="override N (debug)")
+    ap.add_argument("--c4-rows", type=int, default=0, help="also run the c4 block (d=768, nq=256) with this many rows at any --gpus (debug)")
     ap.add_argument("--tensor-mode", type=int, default=0, choices=[0, 1, 2, 3],
                     help="batched-search numerics: 0 library default, 1 3xTF32, 2 TF32 screening, 3 bf16 screening (all exact results)")
     args = ap.parse_args()
@@ -201,17 +202,18 @@ def main():
 
     res = run_workload(ctx, args.workload, N, d, nq, k, args.steps, args.warmup, extras=True)
     c4 = None
-    if world == 8 and args.workload == "c3" and not args.rows:
+    if (world == 8 and args.workload == "c3" and not args.rows) or args.c4_rows:
         # BASELINE.json configs[3] needs all eight GPUs: measured here, where the driver's scaling run looks
         Nc, dc, nqc, kc = WORKLOADS["c4"]
+        Nc = args.c4_rows or Nc
         r4 = run_workload(ctx, "c4", Nc, dc, nqc, kc, args.steps, args.warmup, extras=False)
         if rank == 0:
-            c4 = {"workload": "c4: IndexFlatL2 %dx%d fp32 row-sharded x8, nq=%d, k=%d" % (Nc, dc, nqc, kc),
+            c4 = {"workload": "c4: IndexFlatL2 %dx%d fp32 row-sharded x%d, nq=%d, k=%d" % (Nc, dc, world, nqc, kc),
                   "qps": r4["qps"], "ms_per_step": r4["ms_step"], "e2e": r4["e2e"], "roofline": r4["roofline"],
                   "parity_check": r4["parity_check"], "p50_nq1_ms": r4["p50_nq1_ms"], "roofline_nq1": r4["roofline_nq1"],
-                  "note": "per-GPU shard 12.5M x 768; compare qps with 8x the single-GPU rate of a 12.5M x 768 index "
-                          "(= this shard's main pass alone: nq / roofline.launch_ms)",
-                  "shard_only_qps_x8": 8 * nqc / (r4["roofline"]["launch_ms"] * 1e-3) if r4["roofline"].get("launch_ms") else None}
+                  "note": "per-GPU shard %d x 768; shard_main_pass_qps = nq / roofline.launch_ms is what one GPU's main pass "
+                          "alone would allow for the whole batch" % (Nc // world),
+                  "shard_main_pass_qps": nqc / (r4["roofline"]["launch_ms"] * 1e-3) if r4["roofline"].get("launch_ms") else None}
 
     if rank != 0:
         if dist is not None:
@@ -319,8 +321,8 @@ def tf32_peaks(ctx, index, q_dev, k):
     out = {"cublas_burst": 2 * 8192 ** 3 / (best * 1e-3) / 1e12,
            "cublas_sustained": 2 * 8192 ** 3 * reps / (e0.elapsed_time(e1) * 1e-3) / 1e12,
            "how": "torch.matmul fp32 8192^3 with allow_tf32 (cuBLAS), CUDA events, best of 5 / 1.5 s loop; "
-                  "own = this library's one-product kind::tf32 pass over the bench index with the filter shut "
-                  "(2*nq*N*d flop / in-library CUDA-event time), best of 3"}
+                  "own_dense_pass(_3products) = this library's kind::tf32 pass over the bench index with one (three) product(s) per "
+                  "k-step and the selection filter shut (executed flop / in-library CUDA-event time), best of 3"}
     del a, b
     torch.backends.cuda.matmul.allow_tf32 = False
     return out
@@ -502,22 +504,23 @@ def run_workload(ctx, name, N, d, nq, k, steps, warmup, extras):
             # north_star: ">= 60% of the 3xTF32 tensor-core roofline at nq = 1024": the contraction with three
             # TF32 products per k-step (tensor_mode = 1), against the TF32 dense rate measured on this box
             tp = tf32_peaks(ctx, index, q_dev, k) if rank == 0 else {}
-            probe_ms = None
-            try:
-                loc.set_option("tensor_mode", 2)
-                loc.set_option("tensor_probe", 1)
-                for i in range(4):
-                    index.search(q_dev, k)
-                    torch.cuda.synchronize()
-                    ms_i = index.stats().get("main_kernel_ms")
-                    if i >= 1 and ms_i:
-                        probe_ms = ms_i if probe_ms is None else min(probe_ms, ms_i)
-            finally:
-                loc.set_option("tensor_probe", 0)
-                loc.set_option("tensor_mode", 0)
-            if probe_ms:
-                tp["own_dense_pass"] = 2.0 * nq * n_local * d / (probe_ms * 1e-3) / 1e12
-                tp["own_dense_pass_ms"] = probe_ms
+            for pm, key, nprod in ((2, "own_dense_pass", 1), (1, "own_dense_pass_3products", 3)):
+                probe_ms = None
+                try:
+                    loc.set_option("tensor_mode", pm)
+                    loc.set_option("tensor_probe", 1)
+                    for i in range(4):
+                        index.search(q_dev, k)
+                        torch.cuda.synchronize()
+                        ms_i = index.stats().get("main_kernel_ms")
+                        if i >= 1 and ms_i:
+                            probe_ms = ms_i if probe_ms is None else min(probe_ms, ms_i)
+                finally:
+                    loc.set_option("tensor_probe", 0)
+                    loc.set_option("tensor_mode", 0)
+                if probe_ms:
+                    tp[key] = nprod * 2.0 * nq * n_local * d / (probe_ms * 1e-3) / 1e12
+                    tp[key + "_ms"] = probe_ms
             loc.set_option("tensor_mode", 1)
             try:
                 ms3, _, _ = timed(lambda: index.search(q_dev, k), 3, 2)
@@ -527,13 +530,18 @@ def run_workload(ctx, name, N, d, nq, k, steps, warmup, extras):
             if st3.get("main_kernel_ms") and rank == 0:
                 k3ms = st3["main_kernel_ms"]
                 executed = 3 * 2.0 * nq * n_local * d / (k3ms * 1e-3) / 1e12
-                cands = [v for v in (tp.get("cublas_burst"), tp.get("cublas_sustained"), tp.get("own_dense_pass")) if v]
-                peak3 = max(cands) if cands else pk["bf16_sus"] / 2.0
+                tp["derived_bf16_burst_over_2"] = pk["bf16"] / 2.0
+                cands = {kk: tp[kk] for kk in ("cublas_burst", "cublas_sustained", "own_dense_pass", "own_dense_pass_3products",
+                                               "derived_bf16_burst_over_2") if tp.get(kk)}
+                peak_name = max(cands, key=cands.get)
+                peak3 = cands[peak_name]
                 out["roofline_3xtf32"] = {
                     "bound": "tensor", "kernel": "k3_tf32x3_topk", "tensor_mode": st3.get("tensor_mode"),
                     "launch_ms": k3ms, "ms_per_step": ms3 / 3, "qps": nq / (ms3 / 3 * 1e-3),
                     "achieved": executed, "unit": "TFLOP/s", "peak": peak3, "frac": executed / peak3,
-                    "peak_source": "the largest TF32 dense rate measured in this run (tf32_peak: cuBLAS burst / sustained, own dense pass)",
+                    "peak_source": "tf32_peak.%s: the largest of the TF32 dense rates measured in this run (cuBLAS burst / sustained, this "
+                                   "library's kind::tf32 passes with the filter shut) and %s bf16 burst / 2 (derived; it is the ceiling "
+                                   "whenever no TF32 run reaches it)" % (peak_name, pk["source"]),
                     "algorithmic": "SURVEY.md 8(d): 3 * 2*nq*N*d executed tensor flops per batch",
                     "fp32_equivalent_tflops": executed / 3}
             out["tf32_peak"] = tp

@@ -187,6 +187,9 @@ B2K_API int b2k_search_rows_noalloc(int device, const float* x_dev, int64_t n, i
  * "tensor_mode" = 1 -- the row-sharded index ships the word with its all-gather),
  * "tensor_probe" (measurement only: 1 = batched searches run their main pass with the selection filter
  * shut -- the dense rate of the MMA pipeline for the chosen "tensor_mode"; the results are all padding),
+ * "tensor_query_stationary" (1: in the one-product screening modes a CTA pair keeps its query block resident in
+ * shared memory over a run of row tiles when it fits -- d <= 512 in bf16 --; 0, the default: both operands stream.
+ * Same results either way; measured equally fast),
  * "multi_peer_writes" (multi-GPU handles: 0 = shards keep their results locally and a peer memcpy moves
  * them to devices[0]; 1 = direct peer stores where the GPUs allow it, the default).
  * Unknown key -> B2K_EINVAL. */

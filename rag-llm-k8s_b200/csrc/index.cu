@@ -525,8 +525,11 @@ int b2k_set_option(b2k_index* h, const char* key, int64_t value) {
     } else if (!strcmp(key, "scan_rows")) {
         if (value < 0 || value > 2) { set_error("option scan_rows must be 0 (auto), 1 (fp32 rows) or 2 (bf16 copies + exact re-rank)"); return B2K_EINVAL; }
         h->opt_scan_rows = (int)value;
+    } else if (!strcmp(key, "tensor_query_stationary")) {
+        h->opt_qs = value != 0;
+        if (h->k3) k3_set_query_stationary(h->k3, h->opt_qs);
     } else if (!strcmp(key, "tensor_probe")) {
-        h->opt_probe = value != 0;
+        h->opt_probe = (int)(value < 0 ? 0 : (value > 3 ? 3 : value));
         if (h->k3) k3_set_probe(h->k3, h->opt_probe);
     } else if (!strcmp(key, "timing")) {
         h->opt_timing = value != 0;
@@ -756,6 +759,7 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
             if (!rc) k3_set_epi_halves(h->k3, h->opt_epi);
             if (!rc) k3_set_ext_flag(h->k3, h->opt_flag_ptr);
             if (!rc) k3_set_probe(h->k3, h->opt_probe);
+            if (!rc) k3_set_query_stationary(h->k3, h->opt_qs);
         }
         if (!rc) h->last_path = 2;
         // like faiss (query blocks of 4096), long batches go through in chunks: the candidate-list

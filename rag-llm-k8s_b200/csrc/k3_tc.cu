@@ -83,25 +83,44 @@ struct K3Params {
     int tile_cols;      // columns (rows of the tile) the epilogue looks at: 256, or fewer in the first warm-start pass
     int64_t static_tile0;
     int probe;          // 1: dense-rate probe -- every query row is treated as padding, so the filter never fires
+    // query-stationary schedule (QS kernels): this launch covers tiles [qs_t0, qs_t1); work items are
+    // (run of T consecutive tiles, query block), handed out run-major; runs are qs_T1 tiles long up to
+    // tile qs_tA and qs_T2 (shorter: the tail balances better) from there on
+    long long qs_t0, qs_tA, qs_t1;
+    long long qs_itemsA;  // items of the first region = ceil((qs_tA - qs_t0) / qs_T1) * nqb
+    int qs_T1, qs_T2;
 };
+
+// A unit as it travels through the ring: (tile << 8) | query block, plus, for the query-stationary
+// kernels, whether it is the first / last tile of its work item (the A operand is loaded with the
+// first and released with the last).
+static constexpr long long K3_U_FIRST = 1ll << 44, K3_U_LAST = 1ll << 45;
+__device__ __forceinline__ int64_t unit_tile(long long u) { return (u >> 8) & 0xFFFFFFFFll; }
+static constexpr int K3_QS_NA = 8;  // most k-chunks of a resident query block (d <= 512 in bf16, <= 256 in TF32)
 
 static constexpr int K3_NSCHED = 4;  // depth of the unit-id ring between the scheduler and the other roles
 
-template <int CG, int NS, int MODE>
+// Shared memory: [QS: the resident query block, nkc chunks of 16 KB][NS operand stages][tail].
+// Stage = [Q_hi][Q_lo?][X_hi][X_lo?], or just [X] for the query-stationary kernels.  The tail holds
+// the tile norms, barriers, unit ring, TMEM slot, list lengths and the compaction scratch; its
+// offsets are relative because the part before it depends on d at run time.
+template <int CG, int NS, int MODE, bool QS>
 struct K3Smem {
     static constexpr int B_ROWS = K3_BN / CG;
     static constexpr int B_BYTES = B_ROWS * K3_BK * 4;
     static constexpr int NPART = (MODE == 2 || MODE == 3) ? 1 : 2;  // one operand pair (one-product screening), or hi + lo (3xTF32)
-    static constexpr int OFF_B = NPART * K3_A_BYTES;  // stage = [Q_hi][Q_lo?][X_hi][X_lo?]
-    static constexpr int STAGE_BYTES = NPART * (K3_A_BYTES + B_BYTES);
-    static constexpr int OFF_XN = NS * STAGE_BYTES;            // float[2][256]
-    static constexpr int OFF_BAR = OFF_XN + 2 * K3_BN * 4;     // full[NS] empty[NS] tfull[2] tempty[2] sfull[4] sempty[4]
-    static constexpr int NBAR = 2 * NS + 4 + 2 * K3_NSCHED;
-    static constexpr int OFF_SCHED = OFF_BAR + NBAR * 8;       // long long[K3_NSCHED]
-    static constexpr int OFF_TMEM = OFF_SCHED + K3_NSCHED * 8;
-    static constexpr int OFF_CNT = (OFF_TMEM + 16 + 15) & ~15;      // int[128]: list lengths of the unit in flight (NH = 2)
-    static constexpr int OFF_SCRATCH = OFF_CNT + K3_BM * 4;         // 4 warps x P keys
-    static size_t bytes(int P) { return (size_t)OFF_SCRATCH + (size_t)4 * P * 8; }
+    static constexpr int OFF_B = QS ? 0 : NPART * K3_A_BYTES;
+    static constexpr int STAGE_BYTES = QS ? B_BYTES : NPART * (K3_A_BYTES + B_BYTES);
+    static constexpr int REL_XN = 0;                            // float[2][256]
+    static constexpr int REL_BAR = REL_XN + 2 * K3_BN * 4;      // full[NS] empty[NS] tfull[2] tempty[2] sfull[4] sempty[4] (afull[8] aempty[8])
+    static constexpr int NBAR = 2 * NS + 4 + 2 * K3_NSCHED + (QS ? 2 * K3_QS_NA : 0);
+    static constexpr int REL_SCHED = REL_BAR + NBAR * 8;        // long long[K3_NSCHED]
+    static constexpr int REL_TMEM = REL_SCHED + K3_NSCHED * 8;
+    static constexpr int REL_CNT = (REL_TMEM + 16 + 15) & ~15;  // int[128]: list lengths of the unit in flight (NH = 2)
+    static constexpr int REL_SCRATCH = REL_CNT + K3_BM * 4;     // 4 warps x P keys
+    static size_t bytes(int P, int nkc) {
+        return (size_t)(QS ? nkc * K3_A_BYTES : 0) + (size_t)NS * STAGE_BYTES + REL_SCRATCH + (size_t)4 * P * 8;
+    }
 };
 
 // Consumer side of the unit-id ring: wait for slot `ss`, read the unit, release the slot to the
@@ -210,7 +229,7 @@ __device__ __forceinline__ void k3_filter_chunk(const uint32_t (&v)[32], const u
 // double buffering (the MMAs of the next tile wait for the epilogue), so it is used for long
 // rows (d >= 512) where the relative cost is a few percent and the error would otherwise
 // exceed 1e-5 of ||q||^2 + ||x||^2 on near-duplicate unit-norm vectors.
-template <int CG, int NS, int MODE, int NH>
+template <int CG, int NS, int MODE, int NH, bool QS>
 __global__ void __launch_bounds__(k3_threads(NH), 1)
 k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_ql,
                       const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_xl,
@@ -223,7 +242,8 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
     constexpr bool SCREEN = (ONEP || MODE == 4);     // keep everything within the error slack; exact distances come from the re-rank kernel
     constexpr bool BF16 = (MODE == 3);                  // the screening product runs on bf16 copies of the rows (kind::f16)
     constexpr int BKE = BF16 ? 64 : 32;                 // elements per k-chunk: one 128-byte swizzle row either way
-    using L = K3Smem<CG, NS, MODE>;
+    static_assert(!QS || ONEP, "the query-stationary schedule is for the one-product modes");
+    using L = K3Smem<CG, NS, MODE, QS>;
     // No integer round-trip on this pointer: the compiler must keep seeing shared memory here, or
     // every access through it becomes a generic LD/ST (that cost 2k cycles per 32 accumulator
     // columns in the epilogue).  The kernel has no static shared memory, so the dynamic window
@@ -231,27 +251,31 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     unsigned char* smem = smem_raw;
     if ((ptx::smem_u32(smem) & 1023u) != 0) __trap();
-    float* xn_s = reinterpret_cast<float*>(smem + L::OFF_XN);
-    uint64_t* full = reinterpret_cast<uint64_t*>(smem + L::OFF_BAR);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = (CG == 2) ? ptx::cluster_ctarank() : 0u;
+    const int nkc = (p.d + BKE - 1) / BKE;
+    unsigned char* stages = smem + (QS ? nkc * K3_A_BYTES : 0);  // QS: the query block's nkc chunks stay in front
+    unsigned char* tail = stages + NS * L::STAGE_BYTES;
+    float* xn_s = reinterpret_cast<float*>(tail + L::REL_XN);
+    uint64_t* full = reinterpret_cast<uint64_t*>(tail + L::REL_BAR);
     uint64_t* empty = full + NS;
     uint64_t* tfull = empty + NS;
     uint64_t* tempty = tfull + 2;
     uint64_t* sfull = tempty + 2;
     uint64_t* sempty = sfull + K3_NSCHED;
-    long long* sched_u = reinterpret_cast<long long*>(smem + L::OFF_SCHED);
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + L::OFF_TMEM);
-    u64* scratch = reinterpret_cast<u64*>(smem + L::OFF_SCRATCH);
-    int* cnt_s = reinterpret_cast<int*>(smem + L::OFF_CNT);
-
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const uint32_t rank = (CG == 2) ? ptx::cluster_ctarank() : 0u;
-    const int nkc = (p.d + BKE - 1) / BKE;
+    uint64_t* afull = sempty + K3_NSCHED;   // QS only: chunk kc of the resident query block has landed
+    uint64_t* aempty = afull + K3_QS_NA;    //          ... has been read by the last MMA of its work item
+    long long* sched_u = reinterpret_cast<long long*>(tail + L::REL_SCHED);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tail + L::REL_TMEM);
+    u64* scratch = reinterpret_cast<u64*>(tail + L::REL_SCRATCH);
+    int* cnt_s = reinterpret_cast<int*>(tail + L::REL_CNT);
 
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tmap(&tm_q); ptx::prefetch_tmap(&tm_ql); ptx::prefetch_tmap(&tm_x); ptx::prefetch_tmap(&tm_xl);
         for (int s = 0; s < NS; ++s) { ptx::mbar_init(&full[s], CG); ptx::mbar_init(&empty[s], 1); }
         for (int s = 0; s < 2; ++s) { ptx::mbar_init(&tfull[s], 1); ptx::mbar_init(&tempty[s], 4 * NH * CG); }
         for (int s = 0; s < K3_NSCHED; ++s) { ptx::mbar_init(&sfull[s], 1); ptx::mbar_init(&sempty[s], (1 + 4 * NH) * CG); }
+        if (QS) for (int s = 0; s < K3_QS_NA; ++s) { ptx::mbar_init(&afull[s], CG); ptx::mbar_init(&aempty[s], 1); }
         ptx::fence_barrier_init();
     }
     if (warp == 1) {
@@ -268,13 +292,43 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
         // ===================== scheduler + TMA producer =====================
         if (lane == 0) {
             int stage = 0, ss = 0, static_i = 0;
-            uint32_t phase = 0, sph = 0;
+            uint32_t phase = 0, sph = 0, aph = 0;
+            long long item_tile = 0, item_end = 0;  // QS: tiles left of the current work item
+            int item_qb = 0;
             for (;;) {
                 long long u;
                 if (rank == 0) {
                     // dynamic scheduling: units are handed out in order, so the CTAs running at any
                     // moment work on neighbouring database tiles and share them through L2
                     ptx::mbar_wait(&sempty[ss], sph ^ 1);
+                    if constexpr (QS) {
+                        // work item = (run of consecutive tiles, query block), run-major: the pairs working at
+                        // any moment hold different query blocks but walk the same few runs of tiles
+                        bool first = false;
+                        if (item_tile >= item_end) {
+                            const unsigned long long i = atomicAdd(p.next_unit, 1ull);
+                            first = true;
+                            if ((long long)i < p.qs_itemsA) {
+                                const long long run = (long long)(i / (unsigned)p.nqb);
+                                item_qb = (int)(i - (unsigned long long)run * (unsigned)p.nqb);
+                                item_tile = p.qs_t0 + run * p.qs_T1;
+                                item_end = item_tile + p.qs_T1 < p.qs_tA ? item_tile + p.qs_T1 : p.qs_tA;
+                            } else {
+                                const unsigned long long j = i - (unsigned long long)p.qs_itemsA;
+                                const long long run = (long long)(j / (unsigned)p.nqb);
+                                item_qb = (int)(j - (unsigned long long)run * (unsigned)p.nqb);
+                                item_tile = p.qs_tA + run * p.qs_T2;
+                                item_end = item_tile + p.qs_T2 < p.qs_t1 ? item_tile + p.qs_T2 : p.qs_t1;
+                            }
+                        }
+                        if (item_tile >= item_end) {
+                            u = -1;
+                        } else {
+                            u = (item_tile << 8) | (long long)item_qb | (first ? K3_U_FIRST : 0);
+                            ++item_tile;
+                            if (item_tile == item_end) u |= K3_U_LAST;
+                        }
+                    } else {
                     if (p.static_mode) {
                         const int c = blockIdx.x / CG, G = p.static_qb_mod;
                         const int mine = (p.nqb - (c % G) + G - 1) / G;  // query blocks of this CTA (pair)
@@ -296,6 +350,7 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
                         const uint32_t tt = (uint32_t)u / (uint32_t)p.nqb;  // nunits < 2^31 (2^24 tiles x 32 query blocks)
                         u = ((long long)tt << 8) | (long long)((uint32_t)u - tt * (uint32_t)p.nqb);
                     }
+                    }
                     sched_u[ss] = u;
                     ptx::mbar_arrive(&sfull[ss]);
                     if (CG == 2) ptx::st_async_b64_cluster(&sched_u[ss], &sfull[ss], 1, (uint64_t)u);
@@ -306,29 +361,44 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
                 }
                 if (++ss == K3_NSCHED) { ss = 0; sph ^= 1; }
                 if (u < 0) break;
-                const int64_t t = u >> 8;
+                const int64_t t = unit_tile(u);
                 const int qb = (int)(u & 255);
+                const bool load_a = QS && (u & K3_U_FIRST) != 0;
                 const int qrow0 = qb * (K3_BM * CG) + (int)rank * K3_BM;
                 const int64_t xrow0 = t * K3_BN + (int64_t)rank * L::B_ROWS;
                 for (int kc = 0; kc < nkc; ++kc) {
+                    if (load_a) {
+                        // chunk kc of the new query block replaces the old one as soon as the last MMA that read it has retired
+                        ptx::mbar_wait(&aempty[kc], aph ^ 1);
+                        unsigned char* sa = smem + kc * K3_A_BYTES;
+                        if (CG == 1) {
+                            ptx::mbar_arrive_expect_tx(&afull[kc], K3_A_BYTES);
+                            ptx::tma_load_2d(sa, &tm_q, &afull[kc], kc * BKE, qrow0);
+                        } else {
+                            if (rank == 0) ptx::mbar_arrive_expect_tx(&afull[kc], 2 * K3_A_BYTES);
+                            else ptx::mbar_arrive_cluster(&afull[kc], 0);
+                            ptx::tma_load_2d_pair(sa, &tm_q, &afull[kc], kc * BKE, qrow0);
+                        }
+                    }
                     ptx::mbar_wait(&empty[stage], phase ^ 1);
-                    unsigned char* sb = smem + stage * L::STAGE_BYTES;
+                    unsigned char* sb = stages + stage * L::STAGE_BYTES;
                     if (CG == 1) {
                         ptx::mbar_arrive_expect_tx(&full[stage], L::STAGE_BYTES);
-                        ptx::tma_load_2d(sb, &tm_q, &full[stage], kc * BKE, qrow0);
+                        if (!QS) ptx::tma_load_2d(sb, &tm_q, &full[stage], kc * BKE, qrow0);
                         if (!ONEP) ptx::tma_load_2d(sb + K3_A_BYTES, &tm_ql, &full[stage], kc * BKE, qrow0);
                         ptx::tma_load_2d(sb + L::OFF_B, &tm_x, &full[stage], kc * BKE, (int)xrow0);
                         if (!ONEP) ptx::tma_load_2d(sb + L::OFF_B + L::B_BYTES, &tm_xl, &full[stage], kc * BKE, (int)xrow0);
                     } else {
                         if (rank == 0) ptx::mbar_arrive_expect_tx(&full[stage], 2 * L::STAGE_BYTES);
                         else ptx::mbar_arrive_cluster(&full[stage], 0);
-                        ptx::tma_load_2d_pair(sb, &tm_q, &full[stage], kc * BKE, qrow0);
+                        if (!QS) ptx::tma_load_2d_pair(sb, &tm_q, &full[stage], kc * BKE, qrow0);
                         if (!ONEP) ptx::tma_load_2d_pair(sb + K3_A_BYTES, &tm_ql, &full[stage], kc * BKE, qrow0);
                         ptx::tma_load_2d_pair(sb + L::OFF_B, &tm_x, &full[stage], kc * BKE, (int)xrow0);
                         if (!ONEP) ptx::tma_load_2d_pair(sb + L::OFF_B + L::B_BYTES, &tm_xl, &full[stage], kc * BKE, (int)xrow0);
                     }
                     if (++stage == NS) { stage = 0; phase ^= 1; }
                 }
+                if (load_a) aph ^= 1;
             }
         }
     } else if (warp == 1) {
@@ -336,21 +406,23 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
         if (rank == 0) {
             constexpr uint32_t idesc = BF16 ? ptx::umma_idesc_bf16(K3_BM * CG, K3_BN) : ptx::umma_idesc_tf32(K3_BM * CG, K3_BN);
             int stage = 0, as = 0, ss = 0;
-            uint32_t phase = 0, aphase = 0, sph = 0;
+            uint32_t phase = 0, aphase = 0, sph = 0, afph = 0;
             for (;;) {
                 const long long u = sched_take_warp<CG>(sfull, sempty, sched_u, ss, sph, rank, lane);
                 if (++ss == K3_NSCHED) { ss = 0; sph ^= 1; }
                 if (u < 0) break;
+                const bool a_first = QS && (u & K3_U_FIRST) != 0, a_last = QS && (u & K3_U_LAST) != 0;
                 ptx::mbar_wait(&tempty[as], aphase ^ 1);  // epilogue has drained this accumulator
                 ptx::tc_fence_after();
                 const uint32_t d_tmem = tmem_base + (uint32_t)(as * K3_BN);
                 const uint32_t d_corr = SEP ? tmem_base + (uint32_t)K3_BN : d_tmem;
                 for (int kc = 0; kc < nkc; ++kc) {
+                    if (a_first) ptx::mbar_wait(&afull[kc], afph);  // the new query block's chunk kc is in place
                     ptx::mbar_wait(&full[stage], phase);
                     ptx::tc_fence_after();
                     if (lane == 0) {
-                        const uint32_t sb = ptx::smem_u32(smem + stage * L::STAGE_BYTES);
-                        const uint64_t a_hi = ptx::umma_desc_k_sw128(sb);
+                        const uint32_t sb = ptx::smem_u32(stages + stage * L::STAGE_BYTES);
+                        const uint64_t a_hi = ptx::umma_desc_k_sw128(QS ? ptx::smem_u32(smem + kc * K3_A_BYTES) : sb);
                         const uint64_t a_lo = ptx::umma_desc_k_sw128(sb + K3_A_BYTES);
                         const uint64_t b_hi = ptx::umma_desc_k_sw128(sb + L::OFF_B);
                         const uint64_t b_lo = ptx::umma_desc_k_sw128(sb + L::OFF_B + L::B_BYTES);
@@ -368,11 +440,13 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
                             }
                         }
                         ptx::mma_commit<CG>(&empty[stage]);            // smem slot free once these MMAs retire
+                        if (a_last) ptx::mma_commit<CG>(&aempty[kc]);  // ... and this chunk of the query block, for the next work item
                         if (kc == nkc - 1) ptx::mma_commit<CG>(&tfull[as]);  // accumulator complete
                     }
                     __syncwarp();
                     if (++stage == NS) { stage = 0; phase ^= 1; }
                 }
+                if (a_first) afph ^= 1;
                 if (SEP) { aphase ^= 1; }
                 else { as ^= 1; if (as == 0) aphase ^= 1; }
             }
@@ -407,7 +481,7 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
             return ptx::mbar_try_wait(&sfull[ss], sph);
         };
         auto issue_norms = [&](long long u, float* dst) {
-            const int64_t t = u >> 8;
+            const int64_t t = unit_tile(u);
             for (int j = epi_tid; j < K3_BN; j += EPI_THREADS) {
                 const int64_t r = t * K3_BN + j;
                 if (r < p.n && j < p.tile_cols) ptx::cp_async_4(dst + j, p.norms + r);
@@ -434,7 +508,7 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
             load_state((int)(cur & 255), S);
         }
         while (cur >= 0) {
-            const int64_t t = cur >> 8;  // units arrive as (tile << 8) | query block
+            const int64_t t = unit_tile(cur);  // units arrive as (tile << 8) | query block (| work-item flags)
             const int qb = (int)(cur & 255);
             const int64_t qi = qi_of(qb);
             const bool valid = qi < p.nq && !p.probe;
@@ -476,9 +550,22 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
             // Two register buffers: the tcgen05.ld of the next 32 columns is in flight while this
             // chunk is filtered.
             uint32_t va[32], vb[32], wa[32], wb[32];
+            const uint32_t row_base = (uint32_t)(t * K3_BN) + (uint32_t)(h * HCOLS);
+            // probe levels (measurement only): 1 = the filter runs but nothing passes; 2 = the accumulators are
+            // loaded but not filtered; 3 = the accumulators are handed back untouched (the MMA pipeline alone)
+            if (p.probe < 3) {
             ptx::tmem_ld_32x32(taddr, va);
             if (SEP) ptx::tmem_ld_32x32(taddr + K3_BN, wa);
-            const uint32_t row_base = (uint32_t)(t * K3_BN) + (uint32_t)(h * HCOLS);
+            if (p.probe == 2) {
+#pragma unroll 1
+                for (int c0 = 32; c0 < HCOLS; c0 += 32) {
+                    ptx::tmem_ld_wait();
+                    reg_fence32(va);
+                    ptx::tmem_ld_32x32(taddr + c0, va);
+                }
+                ptx::tmem_ld_wait();
+                reg_fence32(va);
+            } else
 #pragma unroll 1
             for (int c0 = 0; c0 < HCOLS; c0 += 64) {
                 ptx::tmem_ld_wait();
@@ -495,6 +582,7 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
                 reg_fence32(vb);
                 if (SEP) reg_fence32(wb);
                 k3_filter_chunk<SEP, (NH > 1)>(vb, wb, xnh + c0 + 32, t_cmp, qn, tau_eff, kth_eff, row_base + c0 + 32, list, cnt, cnt_s + row);
+            }
             }
             // accumulator drained: hand it back to the MMA warp (of the leader CTA)
             ptx::tc_fence_before();
@@ -604,8 +692,6 @@ __global__ void k3_init_kernel(int64_t nslots, int* cnt, float* tau, u64* kth, i
     if (i < nslots) { cnt[i] = 0; tau[i] = FLT_MAX; kth[i] = (u64)FLT_MAX_BITS << 32; }
     if (gts && i < nq) gts[i] = FLT_MAX_BITS;
 }
-
-__global__ void k3_set_counter_kernel(u64* next_unit, u64 value) { *next_unit = value; }
 
 // ---- K4: per query, merge the lists of every CTA that saw it ---------------------------------
 // One CTA per query.  The lists hold every key under the warm-started shared bound: a few
@@ -737,10 +823,12 @@ __device__ __forceinline__ uint32_t k4_select_dist(const u64* a, int n, int k, u
 template <int K4_P>
 __global__ void __launch_bounds__(K4_THREADS)
 k4_merge_kernel(const K3Params p, int cg, int ncta, int threshold_only, int list_step, float* __restrict__ D,
-                int64_t* __restrict__ I) {
+                int64_t* __restrict__ I, int set_counter, u64 counter_value) {
     extern __shared__ __align__(16) unsigned char k4_smem_raw[];
     K4Smem<K4_P>& sm = *reinterpret_cast<K4Smem<K4_P>*>(k4_smem_raw);
     const int tid = threadIdx.x;
+    // a bound refresh between two segments of the pass also rewinds the scheduler's counter for the next one
+    if (set_counter && blockIdx.x == 0 && tid == 0) *p.next_unit = counter_value;
     const int64_t qi = blockIdx.x;
     const int bq = K3_BM * cg;
     const int qb = (int)(qi / bq);
@@ -887,7 +975,7 @@ __global__ void k3_slack_bf16_kernel(int64_t nq, const float* __restrict__ qn, c
 template <int K4_P>
 __global__ void __launch_bounds__(K4_THREADS)
 k6_rerank_kernel(const K3Params p, int cg, int ncta, const float* __restrict__ X, const float* __restrict__ Q,
-                 float* __restrict__ D, int64_t* __restrict__ I) {
+                 float* __restrict__ D, int64_t* __restrict__ I, int refresh_first) {
     extern __shared__ __align__(16) unsigned char k4_smem_raw[];
     K4Smem<K4_P>& sm = *reinterpret_cast<K4Smem<K4_P>*>(k4_smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -897,14 +985,50 @@ k6_rerank_kernel(const K3Params p, int cg, int ncta, const float* __restrict__ X
     const int r = (int)(qi - (int64_t)qb * bq) / K3_BM;
     const int row = (int)(qi % K3_BM);
     const int k = p.k, d = p.d;
-    // gts holds the k-th smallest approximate distance (K4 in threshold mode ran over the full pass)
-    const float bound = __uint_as_float(p.gts[qi]) + p.slack2[qi];
+    // gts holds the k-th smallest approximate distance of the whole pass (K4 in threshold mode ran behind it), or,
+    // with refresh_first, that of the rows scanned up to the last refresh: an upper bound of the final one
+    const float slack = p.slack2[qi];
+    const float bound = __uint_as_float(p.gts[qi]) + slack;
     const u64 kbound = bound < FLT_MAX ? (((u64)__float_as_uint(bound) << 32) | 0xffffffffull)
                                        : (((u64)FLT_MAX_BITS << 32) - 1);
-    const int total = k4_gather(p, cg, ncta, cg, r, qb, row, kbound, sm);
+    int total = k4_gather(p, cg, ncta, cg, r, qb, row, kbound, sm);
+    if (total > K4_P && refresh_first) {
+        // the bound of the last refresh is too loose for one gather: the refresh proper first (keys up to the old
+        // bound, k-th smallest of those), then the keys within the slack of the result
+        const u64 kb0 = ((u64)p.gts[qi] << 32) | 0xffffffffull;
+        total = k4_gather(p, cg, ncta, cg, r, qb, row, kb0, sm);
+        if (total <= K4_P) {
+            float b2 = bound;
+            if (total >= k) b2 = __uint_as_float(k4_select_dist(sm.buf, total, k, reinterpret_cast<uint32_t*>(sm.out), sm.sel)) + slack;
+            const u64 kb2 = b2 < FLT_MAX ? (((u64)__float_as_uint(b2) << 32) | 0xffffffffull) : (((u64)FLT_MAX_BITS << 32) - 1);
+            total = k4_gather(p, cg, ncta, cg, r, qb, row, kb2, sm);
+        }
+        refresh_first = 0;
+    }
     if (total > K4_P) {  // more rows inside the slack than the buffer holds: the host reruns exactly
         if (tid == 0) atomicExch(p.overflow, 1u);
         return;
+    }
+    if (refresh_first && total >= k) {
+        // The last bound refresh folded in: what was gathered is a superset of the k smallest approximate
+        // distances, so its k-th smallest IS the final k-th; keep the keys within the slack of that.
+        const uint32_t dk = k4_select_dist(sm.buf, total, k, reinterpret_cast<uint32_t*>(sm.out), sm.sel);
+        const float b2 = __uint_as_float(dk) + slack;
+        constexpr int PER = K4_P / K4_THREADS;
+        u64 mine[PER];
+#pragma unroll
+        for (int j = 0; j < PER; ++j) {
+            const int i = tid + j * K4_THREADS;
+            mine[j] = i < total ? sm.buf[i] : KEY_EMPTY;
+        }
+        __syncthreads();
+        if (tid == 0) sm.cnt2 = 0;
+        __syncthreads();
+#pragma unroll
+        for (int j = 0; j < PER; ++j)
+            if (mine[j] != KEY_EMPTY && key_dist(mine[j]) <= b2) sm.buf[atomicAdd(&sm.cnt2, 1)] = mine[j];
+        __syncthreads();
+        total = sm.cnt2;
     }
     // exact distances: one warp per candidate (two candidates in flight per warp), 128-bit loads,
     // fixed summation order
@@ -972,6 +1096,7 @@ struct K3State {
     unsigned int* ext_flag = nullptr;  // caller-owned overflow word (deferred screening check)
     int epi_halves = 0;  // 0 auto (2 where available), 1 four epilogue warps, 2 eight
     int segments = 1;  // cut the main pass into segments with a bound refresh in between (0 = one launch)
+    int qs = 0;        // query-stationary schedule where it applies (option "tensor_query_stationary"; measured: no gain)
     int probe = 0;     // dense-rate probe (option "tensor_probe"): the pass runs with the filter shut, results are padding
 };
 
@@ -1076,7 +1201,8 @@ void k3_set_sep_mode(K3State* s, int m) { s->sep_mode = m; }
 void k3_set_segments(K3State* s, int on) { s->segments = on; }
 void k3_set_epi_halves(K3State* s, int nh) { s->epi_halves = nh; }
 void k3_set_ext_flag(K3State* s, unsigned int* flag) { s->ext_flag = flag; }
-void k3_set_probe(K3State* s, int on) { s->probe = on != 0; }
+void k3_set_probe(K3State* s, int on) { s->probe = on < 0 ? 0 : (on > 3 ? 3 : on); }
+void k3_set_query_stationary(K3State* s, int on) { s->qs = on != 0; }
 int k3_last_mode(const K3State* s) { return s->last_mode; }
 
 int k3_last_kernel_ms(K3State* s, float* ms) {
@@ -1101,11 +1227,14 @@ static int make_map(K3State* s, CUtensorMap* m, const void* base, int64_t rows, 
     return B2K_OK;
 }
 
-template <int CG, int NS, int MODE, int NH>
+static constexpr size_t K3_SMEM_LIMIT = 227 * 1024;
+
+template <int CG, int NS, int MODE, int NH, bool QS = false>
 static int launch_k3(const CUtensorMap& mq, const CUtensorMap& mql, const CUtensorMap& mx, const CUtensorMap& mxl,
                      const K3Params& p, int ncta, cudaStream_t st) {
-    size_t smem = K3Smem<CG, NS, MODE>::bytes(p.P);
-    B2K_CUDA(cudaFuncSetAttribute(k3_tf32x3_topk_kernel<CG, NS, MODE, NH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int nkc = (p.d + (MODE == 3 ? 64 : 32) - 1) / (MODE == 3 ? 64 : 32);
+    size_t smem = K3Smem<CG, NS, MODE, QS>::bytes(p.P, nkc);
+    B2K_CUDA(cudaFuncSetAttribute(k3_tf32x3_topk_kernel<CG, NS, MODE, NH, QS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(ncta);
     cfg.blockDim = dim3(k3_threads(NH));
@@ -1118,7 +1247,7 @@ static int launch_k3(const CUtensorMap& mq, const CUtensorMap& mql, const CUtens
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    B2K_CUDA(cudaLaunchKernelEx(&cfg, k3_tf32x3_topk_kernel<CG, NS, MODE, NH>, mq, mql, mx, mxl, p));
+    B2K_CUDA(cudaLaunchKernelEx(&cfg, k3_tf32x3_topk_kernel<CG, NS, MODE, NH, QS>, mq, mql, mx, mxl, p));
     count_launch();
     return B2K_OK;
 }
@@ -1157,9 +1286,39 @@ static int launch_k3_any(int cg, int P, int mode, int nh, const CUtensorMap& mq,
     return B2K_EINVAL;
 }
 
+// Query-stationary kernels: CTA pairs, eight epilogue warps, lists of <= 512 keys; nsb = operand stages that fit
+// next to the resident query block (6 up to d = 384 in bf16, 4 up to d = 512).
+static int k3_qs_stages(int mode, int d, int P) {
+    if (mode != 2 && mode != 3) return 0;
+    const int bke = mode == 3 ? 64 : 32;
+    const int nkc = (d + bke - 1) / bke;
+    if (nkc > K3_QS_NA || P > 512) return 0;
+    if (K3Smem<2, 6, 3, true>::bytes(P, nkc) <= K3_SMEM_LIMIT) return 6;
+    if (K3Smem<2, 4, 3, true>::bytes(P, nkc) <= K3_SMEM_LIMIT) return 4;
+    return 0;
+}
+
+static int launch_k3_qs(int mode, int nsb, const CUtensorMap& mq, const CUtensorMap& mql, const CUtensorMap& mx,
+                        const CUtensorMap& mxl, const K3Params& p, int ncta, cudaStream_t st) {
+    if (mode == 3 && nsb == 6) return launch_k3<2, 6, 3, 2, true>(mq, mql, mx, mxl, p, ncta, st);
+    if (mode == 3 && nsb == 4) return launch_k3<2, 4, 3, 2, true>(mq, mql, mx, mxl, p, ncta, st);
+    if (mode == 2 && nsb == 6) return launch_k3<2, 6, 2, 2, true>(mq, mql, mx, mxl, p, ncta, st);
+    if (mode == 2 && nsb == 4) return launch_k3<2, 4, 2, 2, true>(mq, mql, mx, mxl, p, ncta, st);
+    set_error("tensor kernel: no query-stationary variant for mode %d with %d stages", mode, nsb);
+    return B2K_EINVAL;
+}
+
 static void launch_k4(int64_t nq, cudaStream_t st, const K3Params& p, int cg, int ncta, int threshold_only,
-                      int list_step, float* D, int64_t* I) {
-    k4_merge_kernel<4096><<<(unsigned)nq, K4_THREADS, sizeof(K4Smem<4096>), st>>>(p, cg, ncta, threshold_only, list_step, D, I);
+                      int list_step, float* D, int64_t* I, int set_counter = 0, u64 counter_value = 0) {
+    // bound refreshes of short lists (k <= 256) use half the key buffer: 28 KB instead of 52 KB of shared memory per
+    // block, so that all nq blocks of a 1024-query batch are resident at once (the kernel is latency-bound on its
+    // gather); a query with more live keys than the buffer takes the sample-and-regather path, exact for any size
+    if (threshold_only && p.k <= 256)
+        k4_merge_kernel<2048><<<(unsigned)nq, K4_THREADS, sizeof(K4Smem<2048>), st>>>(p, cg, ncta, threshold_only, list_step, D, I,
+                                                                                      set_counter, counter_value);
+    else
+        k4_merge_kernel<4096><<<(unsigned)nq, K4_THREADS, sizeof(K4Smem<4096>), st>>>(p, cg, ncta, threshold_only, list_step, D, I,
+                                                                                      set_counter, counter_value);
 }
 
 int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, const float* norms,
@@ -1196,6 +1355,7 @@ int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, con
     p.static_tile0 = 0;
     p.tile_cols = K3_BN;
     p.probe = s->probe;
+    p.qs_t0 = p.qs_tA = p.qs_t1 = 0; p.qs_itemsA = 0; p.qs_T1 = p.qs_T2 = 1;
 
     // queries: norms (+ TF32 residual rows for the exact mode; K1 reused), screening slack, list state reset
     int rc = launch_row_prep(q, nq, d, const_cast<float*>(p.qn), onep ? nullptr : qlo, nullptr, st);
@@ -1324,6 +1484,7 @@ int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, con
             // a boundary that would come too early is moved out, never dropped: dropping it leaves the next
             // segment r times more permissive (measured: 2.0 instead of 0.94 ms on a 1.25M-row shard)
             if (end < prev + min_step) end = prev + min_step;
+            end = (end + L.nqb - 1) / L.nqb * L.nqb;  // whole tiles
             if (end + min_step > p.nunits) break;
             seg_end[nseg++] = end;
             prev = end;
@@ -1331,17 +1492,37 @@ int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, con
         }
     }
     seg_end[nseg++] = p.nunits;
+    // Query-stationary schedule (one-product modes, CTA pairs, d small enough for a CTA's 128 query rows to
+    // stay in shared memory): a pair keeps its query block resident over a run of consecutive tiles and only
+    // streams the rows, which halves the operand traffic from L2 -- the stated bound of the streaming form.
+    const int qs_nsb = (s->qs && L.cg == 2 && nh == 2 && true) ? k3_qs_stages(sep, d, L.P) : 0;
+    const bool qs = qs_nsb > 0 && L.nqb >= 2;
     if (s->timing) B2K_CUDA(cudaEventRecord(s->ev0, st));
     for (int sg = 0; sg < nseg; ++sg) {
         K3Params ps = p;
         ps.nunits = seg_end[sg];
+        const long long u0 = sg > 0 ? seg_end[sg - 1] : 0;
+        if (qs) {
+            // segment boundaries are whole tiles (seg_end is a multiple of nqb); the counter restarts at 0
+            ps.qs_t0 = u0 / L.nqb;
+            ps.qs_t1 = seg_end[sg] / L.nqb;
+            const long long nt = ps.qs_t1 - ps.qs_t0;
+            const long long groups = nclusters / L.nqb > 0 ? nclusters / L.nqb : 1;  // pairs per query block
+            long long T1 = nt / (groups * 4);                                       // >= 4 items per pair and segment
+            T1 = T1 < 1 ? 1 : (T1 > 16 ? 16 : T1);
+            long long T2 = T1 / 4 < 1 ? 1 : T1 / 4;                                  // the last eighth in short runs: a balanced tail
+            long long nA = ((nt - nt / 8) / T1) * T1;
+            ps.qs_T1 = (int)T1; ps.qs_T2 = (int)T2;
+            ps.qs_tA = ps.qs_t0 + nA;
+            ps.qs_itemsA = (nA / T1) * L.nqb;
+        }
         if (sg > 0) {
-            launch_k4(nq, st, p, L.cg, L.ncta, 1, 1, nullptr, nullptr);
-            k3_set_counter_kernel<<<1, 1, 0, st>>>(p.next_unit, (u64)seg_end[sg - 1]);
-            count_launch(2);
+            launch_k4(nq, st, p, L.cg, L.ncta, 1, 1, nullptr, nullptr, 1, qs ? 0ull : (u64)u0);
+            count_launch();
             B2K_CUDA(cudaGetLastError());
         }
-        rc = launch_k3_any(L.cg, L.P, sep, nh, mq, mql, mx, mxl, ps, L.ncta, st);
+        rc = qs ? launch_k3_qs(sep, qs_nsb, mq, mql, mx, mxl, ps, L.ncta, st)
+                : launch_k3_any(L.cg, L.P, sep, nh, mq, mql, mx, mxl, ps, L.ncta, st);
         if (rc) return rc;
     }
     if (s->timing) { B2K_CUDA(cudaEventRecord(s->ev1, st)); s->timed = true; }
@@ -1355,9 +1536,13 @@ int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, con
     // screening: the exact k-th smallest approximate distance per query, then the exact re-rank of
     // everything within the slack of it
     B2K_CUDA(cudaFuncSetAttribute(k6_rerank_kernel<4096>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(K4Smem<4096>)));
-    launch_k4(nq, st, p, L.cg, L.ncta, 1, 1, nullptr, nullptr);
-    k6_rerank_kernel<4096><<<(unsigned)nq, K4_THREADS, sizeof(K4Smem<4096>), st>>>(p, L.cg, L.ncta, x, q, D, I);
-    count_launch(2);
+    // with a refreshed bound from late in the pass (segments) and short lists, the last refresh happens inside the re-rank kernel
+    // (and few enough keys under that bound: ~k / (fraction scanned at the last refresh), plus the slack zone)
+    const double g_last = nseg >= 2 ? (double)seg_end[nseg - 2] / (double)p.nunits : 0.0;
+    const int fold = (nseg >= 2 && k <= 256 && (double)k <= 1500.0 * g_last) ? 1 : 0;
+    if (!fold) { launch_k4(nq, st, p, L.cg, L.ncta, 1, 1, nullptr, nullptr); count_launch(); }
+    k6_rerank_kernel<4096><<<(unsigned)nq, K4_THREADS, sizeof(K4Smem<4096>), st>>>(p, L.cg, L.ncta, x, q, D, I, fold);
+    count_launch();
     B2K_CUDA(cudaGetLastError());
     // a list or the re-rank buffer could not hold every row inside the slack (masses of near-
     // duplicates around the k-th neighbour): the caller repeats the search in the exact mode
