@@ -22,25 +22,21 @@ def ev():
 
 
 rows = []
+from b200knn import merge_shards
 for i in range(25):
     torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
     t0 = time.perf_counter()
+    nk, words, send, recv = idx._buffers(nq, k)
+    I_loc = send[:nk].view(nq, k); D_loc = send[nk:words].view(torch.float32)[:nk].view(nq, k)
     e0 = ev()
-    D, I = idx.local.search(qq, k)
+    send[words:].zero_()
+    idx.local.search(qq, k, D=D_loc, I=I_loc)
     e1 = ev()
-    nk = nq * k
-    words = nk + (nk + 1) // 2
-    send = torch.empty(words, dtype=torch.int64, device=qq.device)
-    send[:nk].view(nq, k).copy_(idx._to_global(torch.as_tensor(I)))
-    send[nk:].view(torch.float32)[:nk].view(nq, k).copy_(torch.as_tensor(D))
     e2 = ev()
-    recv = torch.empty(W * words, dtype=torch.int64, device=qq.device)
     dist.all_gather_into_tensor(recv, send)
     e3 = ev()
-    recv = recv.view(W, words)
-    Icat = recv[:, :nk].reshape(W, nq, k)
-    Dcat = recv[:, nk:].contiguous().view(torch.float32)[:, :nk].reshape(W, nq, k)
-    Dm, Im = b200knn.merge_topk(Dcat, Icat)
+    Dm = torch.empty((nq, k), dtype=torch.float32, device=qq.device); Im = torch.empty((nq, k), dtype=torch.int64, device=qq.device)
+    merge_shards(recv.data_ptr() + 8 * nk, 2 * (words + 1), recv.data_ptr(), words + 1, W, nq, k, Dm, Im, cyclic_block=idx.block)
     e4 = ev()
     torch.cuda.synchronize(); t1 = time.perf_counter()
     if i >= 5:
