@@ -43,7 +43,7 @@ void set_error(const char* fmt, ...) {
 RowStore::~RowStore() {
     DeviceGuard g(device);
     cudaDeviceSynchronize();  // kernels of handles that shared this store may still be reading it
-    cudaFree(x); cudaFree(norms); cudaFree(xlo); cudaFree(xbf); cudaFree(stat);
+    cudaFree(x); cudaFree(norms); cudaFree(xlo); cudaFree(xbf); cudaFree(xnb); cudaFree(stat);
     if (ev_rows) cudaEventDestroy(ev_rows);
 }
 
@@ -137,7 +137,7 @@ int grow(RowStore* rs, int64_t need_rows, cudaStream_t st) {
     if (cap < 1024) cap = 1024;
     if (cap > MAX_ROWS) cap = MAX_ROWS;
     float *nx = nullptr, *nn = nullptr, *nl = nullptr;
-    void* nb = nullptr;
+    void *nb = nullptr, *nnb = nullptr;
     size_t row_bytes = (size_t)rs->d * sizeof(float);
     cudaError_t e = cudaMalloc(&nx, (size_t)cap * row_bytes);
     if (e != cudaSuccess && cap > need_rows) {  // doubling did not fit: take exactly what is needed
@@ -147,16 +147,18 @@ int grow(RowStore* rs, int64_t need_rows, cudaStream_t st) {
     }
     if (e == cudaSuccess) e = cudaMalloc(&nn, (size_t)cap * sizeof(float));
     if (e == cudaSuccess && rs->lo_enabled) e = cudaMalloc(&nl, (size_t)cap * row_bytes);
-    if (e == cudaSuccess && rs->bf_enabled && cudaMalloc(&nb, (size_t)cap * row_bytes / 2) != cudaSuccess) {
+    if (e == cudaSuccess && rs->bf_enabled &&
+        (cudaMalloc(&nb, (size_t)cap * row_bytes / 2) != cudaSuccess || cudaMalloc(&nnb, (size_t)cap * 32) != cudaSuccess)) {
         // no room for the bf16 copies next to the grown rows: drop them, TF32 screening needs none
         cudaGetLastError();
+        cudaFree(nb);
         nb = nullptr;
         rs->bf_enabled = false;
         rs->bf_nomem = true;
     }
     if (e != cudaSuccess) {
         cudaGetLastError();
-        cudaFree(nx); cudaFree(nn); cudaFree(nl); cudaFree(nb);
+        cudaFree(nx); cudaFree(nn); cudaFree(nl); cudaFree(nb); cudaFree(nnb);
         set_error("cudaMalloc for %lld rows x %d failed: %s", (long long)cap, rs->d, cudaGetErrorString(e));
         return B2K_ENOMEM;
     }
@@ -167,12 +169,13 @@ int grow(RowStore* rs, int64_t need_rows, cudaStream_t st) {
         B2K_CUDA(cudaMemcpyAsync(nn, rs->norms, (size_t)rs->filled * sizeof(float), cudaMemcpyDeviceToDevice, st));
         if (nl) B2K_CUDA(cudaMemcpyAsync(nl, rs->xlo, (size_t)rs->filled * row_bytes, cudaMemcpyDeviceToDevice, st));
         if (nb) B2K_CUDA(cudaMemcpyAsync(nb, rs->xbf, (size_t)rs->filled * row_bytes / 2, cudaMemcpyDeviceToDevice, st));
+        if (nnb) B2K_CUDA(cudaMemcpyAsync(nnb, rs->xnb, (size_t)rs->filled * 32, cudaMemcpyDeviceToDevice, st));
         B2K_CUDA(cudaStreamSynchronize(st));
     }
     // cudaFree waits for everything already enqueued on the device, including searches of other
     // handles that read the old buffers (they enqueued under the shared lock, before this point)
-    cudaFree(rs->x); cudaFree(rs->norms); cudaFree(rs->xlo); cudaFree(rs->xbf);
-    rs->x = nx; rs->norms = nn; rs->xlo = nl; rs->xbf = nb; rs->capacity = cap;
+    cudaFree(rs->x); cudaFree(rs->norms); cudaFree(rs->xlo); cudaFree(rs->xbf); cudaFree(rs->xnb);
+    rs->x = nx; rs->norms = nn; rs->xlo = nl; rs->xbf = nb; rs->xnb = nnb; rs->capacity = cap;
     return B2K_OK;
 }
 
@@ -183,6 +186,7 @@ int prep_new_rows(RowStore* rs, int64_t first, int64_t n, cudaStream_t st) {
     if (!rc && rs->bf_enabled)
         rc = launch_row_bf16(rs->x + first * (int64_t)rs->d, n, rs->d,
                              static_cast<unsigned short*>(rs->xbf) + first * (int64_t)rs->d, nullptr, rs->stat + MAX_ERR_SLOT, st);
+    if (!rc && rs->bf_enabled) rc = launch_norm_split(rs->norms + first, n, static_cast<unsigned char*>(rs->xnb) + first * 32, st);
     return rc;
 }
 
@@ -214,12 +218,20 @@ int enable_bf(RowStore* rs, cudaStream_t st) {
     if (rs->bf_nomem) { set_error("no room for the bf16 copies"); return B2K_ENOMEM; }
     if (rs->capacity > 0) {
         cudaError_t e = cudaMalloc(&rs->xbf, (size_t)rs->capacity * rs->d * 2);
-        if (e != cudaSuccess) { cudaGetLastError(); rs->xbf = nullptr; rs->bf_nomem = true; set_error("cudaMalloc for bf16 rows failed: %s", cudaGetErrorString(e)); return B2K_ENOMEM; }
+        if (e == cudaSuccess) e = cudaMalloc(&rs->xnb, (size_t)rs->capacity * 32);
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            cudaFree(rs->xbf);
+            rs->xbf = nullptr; rs->xnb = nullptr; rs->bf_nomem = true;
+            set_error("cudaMalloc for bf16 rows failed: %s", cudaGetErrorString(e));
+            return B2K_ENOMEM;
+        }
     }
     int rc = B2K_OK;
     if (rs->filled > 0) {
         B2K_CUDA(cudaStreamWaitEvent(st, rs->ev_rows, 0));
         rc = launch_row_bf16(rs->x, rs->filled, rs->d, rs->xbf, nullptr, rs->stat + MAX_ERR_SLOT, st);
+        if (!rc) rc = launch_norm_split(rs->norms, rs->filled, rs->xnb, st);
         if (!rc) B2K_CUDA(cudaEventRecord(rs->ev_rows, st));
     }
     if (!rc) rs->bf_enabled = true;
@@ -770,7 +782,7 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
             int overflowed = 0;
             {
                 std::shared_lock<std::shared_mutex> sl(rs->mu);
-                rc = k3_search(h->k3, rs->x, rs->xlo, rs->xbf, rs->norms, rs->stat + MAX_NORM_SLOT, rs->stat + MAX_ERR_SLOT, h->ntotal,
+                rc = k3_search(h->k3, rs->x, rs->xlo, rs->xbf, rs->xnb, rs->norms, rs->stat + MAX_NORM_SLOT, rs->stat + MAX_ERR_SLOT, h->ntotal,
                                h->d, qc, nqc, kk, Dd + q0 * kk, Id + q0 * kk, ws_tail, st, mode, &overflowed);
             }
             if (!rc && overflowed && mode != 4) {
@@ -781,7 +793,7 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
                 ++h->stat_screen_fallbacks;
                 if (enable_lo(rs, st) == B2K_OK) {  // (no room for the residual rows: straight to the scan, overflowed stays set)
                     std::shared_lock<std::shared_mutex> sl(rs->mu);
-                    rc = k3_search(h->k3, rs->x, rs->xlo, rs->xbf, rs->norms, rs->stat + MAX_NORM_SLOT, rs->stat + MAX_ERR_SLOT,
+                    rc = k3_search(h->k3, rs->x, rs->xlo, rs->xbf, rs->xnb, rs->norms, rs->stat + MAX_NORM_SLOT, rs->stat + MAX_ERR_SLOT,
                                    h->ntotal, h->d, qc, nqc, kk, Dd + q0 * kk, Id + q0 * kk, ws_tail, st, 4, &overflowed);
                 }
             }

@@ -27,6 +27,7 @@ struct RowStore {
     float* norms = nullptr;            // [capacity]    ||x||^2, K1 at add()          (K3 epilogue)
     float* xlo = nullptr;              // [capacity][d] TF32 residual rows, once a 3xTF32 mode has run
     void* xbf = nullptr;               // [capacity][d] bf16 copies, once a screening pass / bf16 scan has run
+    void* xnb = nullptr;               // [capacity][16] bf16: -||x||^2/2 as three bf16 terms, next to xbf (K3 adds it by MMA)
     bool lo_enabled = false, bf_enabled = false, bf_nomem = false;
     unsigned int* stat = nullptr;      // device words: [0] bits of max ||x||^2, [1] bits of max ||x - bf16(x)||^2
     cudaEvent_t ev_rows = nullptr;     // last write to any of the buffers above

@@ -153,6 +153,34 @@ int launch_row_bf16(const float* X, int64_t n, int d, void* xb, float* err2, uns
     return B2K_OK;
 }
 
+// ---- -||x||^2 / 2 as three bf16 terms, one 32-byte record per row -----------------------------
+// The bf16 screening pass lets the tensor core add the row norms: one more K = 16 MMA per tile with a
+// block of ones on the query side and this record on the row side puts  q~.x~ - ||x||^2/2  in the
+// accumulator, so the epilogue compares instead of computing.  h1 + h2 + h3 reproduces ||x||^2/2 to
+// 2^-24 relative (three 8-bit mantissas); a non-finite norm gives -inf / NaN, which never passes.
+__global__ void __launch_bounds__(256)
+norm_split_kernel(const float* __restrict__ norms, int64_t n, uint4* __restrict__ out) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float h = 0.5f * norms[i];
+    const __nv_bfloat16 b1 = __float2bfloat16_rn(h);
+    const float r1 = h - __bfloat162float(b1);
+    const __nv_bfloat16 b2 = __float2bfloat16_rn(r1);
+    const float r2 = r1 - __bfloat162float(b2);
+    const __nv_bfloat16 b3 = __float2bfloat16_rn(r2);
+    const uint32_t u1 = __bfloat16_as_ushort(__hneg(b1)), u2 = __bfloat16_as_ushort(__hneg(b2)), u3 = __bfloat16_as_ushort(__hneg(b3));
+    out[2 * i] = make_uint4(u1 | (u2 << 16), u3, 0u, 0u);
+    out[2 * i + 1] = make_uint4(0u, 0u, 0u, 0u);
+}
+
+int launch_norm_split(const float* norms, int64_t n, void* out, cudaStream_t st) {
+    if (n <= 0) return B2K_OK;
+    norm_split_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(norms, n, static_cast<uint4*>(out));
+    count_launch();
+    B2K_CUDA(cudaGetLastError());
+    return B2K_OK;
+}
+
 // ---- synthetic rows (must stay bit-identical to oracle/flat_l2_oracle.c orc_synth_value) ----
 __host__ __device__ __forceinline__ uint64_t mix64(uint64_t z) {
     z ^= z >> 30; z *= 0xBF58476D1CE4E5B9ull;

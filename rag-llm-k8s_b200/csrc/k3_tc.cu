@@ -111,9 +111,16 @@ struct K3Smem {
     static constexpr int NPART = (MODE == 2 || MODE == 3) ? 1 : 2;  // one operand pair (one-product screening), or hi + lo (3xTF32)
     static constexpr int OFF_B = QS ? 0 : NPART * K3_A_BYTES;
     static constexpr int STAGE_BYTES = QS ? B_BYTES : NPART * (K3_A_BYTES + B_BYTES);
-    static constexpr int REL_XN = 0;                            // float[2][256]
-    static constexpr int REL_BAR = REL_XN + 2 * K3_BN * 4;      // full[NS] empty[NS] tfull[2] tempty[2] sfull[4] sempty[4] (afull[8] aempty[8])
-    static constexpr int NBAR = 2 * NS + 4 + 2 * K3_NSCHED + (QS ? 2 * K3_QS_NA : 0);
+    // norm fold (bf16 screening with CTA pairs): two buffers of 32-byte norm records for the rows of a tile
+    // and one block of "ones" rows for the queries, operands of one extra K = 16 MMA per tile
+    static constexpr bool NF = (MODE == 3 && CG == 2);
+    static constexpr int NREC_BYTES = B_ROWS * 32;
+    static constexpr int ONES_BYTES = K3_BM * 32;
+    static constexpr int REL_NREC = 0;
+    static constexpr int REL_ONES = 2 * NREC_BYTES;
+    static constexpr int REL_XN = NF ? 2 * NREC_BYTES + ONES_BYTES : 0;  // float[2][256] (unused with NF)
+    static constexpr int REL_BAR = REL_XN + 2 * K3_BN * 4;      // full[NS] empty[NS] tfull[2] tempty[2] sfull[4] sempty[4] (afull[8] aempty[8]) (nfull[2] nempty[2] onefull)
+    static constexpr int NBAR = 2 * NS + 4 + 2 * K3_NSCHED + (QS ? 2 * K3_QS_NA : 0) + (NF ? 5 : 0);
     static constexpr int REL_SCHED = REL_BAR + NBAR * 8;        // long long[K3_NSCHED]
     static constexpr int REL_TMEM = REL_SCHED + K3_NSCHED * 8;
     static constexpr int REL_CNT = (REL_TMEM + 16 + 15) & ~15;  // int[128]: list lengths of the unit in flight (NH = 2)
@@ -221,6 +228,52 @@ __device__ __forceinline__ void k3_filter_chunk(const uint32_t (&v)[32], const u
     }
 }
 
+// The same for the norm-folded accumulator a = q~.x~ - ||x||^2/2 (bf16 screening with CTA pairs): a row passes
+// iff a >= thr, so the dense part is a running maximum (3-input FMNMX: half an instruction per element, no norm
+// loads); the approximate distance of a survivor is ||q||^2 - 2a.  ncols: columns of this chunk that are real rows.
+template <bool SHCNT>
+__device__ __forceinline__ void k3_filter_chunk_nf(const uint32_t (&v)[32], float thr, float qn, float tau_eff, u64 kth,
+                                                   uint32_t row0, int ncols, u64* list, int& cnt, int* cnt_s) {
+    float m[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) m[j] = __uint_as_float(v[j]);
+#pragma unroll
+    for (int c = 4; c < 32; c += 8) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) m[j] = fmaxf(fmaxf(m[j], __uint_as_float(v[c + j])), __uint_as_float(v[c + 4 + j]));
+    }
+    if (fmaxf(fmaxf(m[0], m[1]), fmaxf(m[2], m[3])) >= thr) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            if (m[j] >= thr) {
+                uint32_t mask = 0;
+                float a[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    a[i] = __uint_as_float(v[4 * i + j]);
+                    mask |= (a[i] >= thr) ? (1u << i) : 0u;
+                }
+                while (mask) {
+                    const int i = __ffs(mask) - 1;
+                    mask &= mask - 1;
+                    const int c = 4 * i + j;
+                    if (c < ncols) {
+                        float dist = fmaf(-2.f, reg_select<0, 8, 8>(a, i), qn);
+                        dist = dist < 0.f ? 0.f : dist;
+                        if (dist <= tau_eff) {
+                            const u64 key = make_key(dist, row0 + c);
+                            if (key < kth) {
+                                if constexpr (SHCNT) { list[atomicAdd(cnt_s, 1)] = key; }
+                                else { list[cnt] = key; ++cnt; }
+                            }
+                        }
+                    }
+                }
+            }
+        }
+    }
+}
+
 // SEP = true keeps the two small cross products (Q_lo*X_hi + Q_hi*X_lo) in their own TMEM
 // accumulator (columns 256..511) and adds it to the main one in the epilogue.  The tensor core
 // truncates on every accumulate (measured ~0.8 ulp of the accumulator per MMA, biased towards
@@ -233,6 +286,7 @@ template <int CG, int NS, int MODE, int NH, bool QS>
 __global__ void __launch_bounds__(k3_threads(NH), 1)
 k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_ql,
                       const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_xl,
+                      const __grid_constant__ CUtensorMap tm_n, const __grid_constant__ CUtensorMap tm_one,
                       const K3Params p) {
     // MODE: 0 3xTF32, one accumulator | 1 3xTF32, separate cross-term accumulator | 2 one TF32 product, screening
     //       3 one bf16 product, screening | 4 3xTF32 (as 1) used as a screen: second line of defence when the
@@ -244,6 +298,7 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
     constexpr int BKE = BF16 ? 64 : 32;                 // elements per k-chunk: one 128-byte swizzle row either way
     static_assert(!QS || ONEP, "the query-stationary schedule is for the one-product modes");
     using L = K3Smem<CG, NS, MODE, QS>;
+    constexpr bool NF = L::NF;  // the tensor core also adds -||x||^2/2 (one more MMA per tile): the epilogue only compares
     // No integer round-trip on this pointer: the compiler must keep seeing shared memory here, or
     // every access through it becomes a generic LD/ST (that cost 2k cycles per 32 accumulator
     // columns in the epilogue).  The kernel has no static shared memory, so the dynamic window
@@ -265,6 +320,11 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
     uint64_t* sempty = sfull + K3_NSCHED;
     uint64_t* afull = sempty + K3_NSCHED;   // QS only: chunk kc of the resident query block has landed
     uint64_t* aempty = afull + K3_QS_NA;    //          ... has been read by the last MMA of its work item
+    uint64_t* nfull = sempty + K3_NSCHED + (QS ? 2 * K3_QS_NA : 0);  // NF only: the tile's norm records have landed
+    uint64_t* nempty = nfull + 2;           //          ... have been read by the tile's norm MMA
+    uint64_t* onefull = nempty + 2;         //          the block of ones has landed (once per kernel)
+    unsigned char* nrec = tail + L::REL_NREC;
+    unsigned char* ones = tail + L::REL_ONES;
     long long* sched_u = reinterpret_cast<long long*>(tail + L::REL_SCHED);
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tail + L::REL_TMEM);
     u64* scratch = reinterpret_cast<u64*>(tail + L::REL_SCRATCH);
@@ -276,6 +336,11 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
         for (int s = 0; s < 2; ++s) { ptx::mbar_init(&tfull[s], 1); ptx::mbar_init(&tempty[s], 4 * NH * CG); }
         for (int s = 0; s < K3_NSCHED; ++s) { ptx::mbar_init(&sfull[s], 1); ptx::mbar_init(&sempty[s], (1 + 4 * NH) * CG); }
         if (QS) for (int s = 0; s < K3_QS_NA; ++s) { ptx::mbar_init(&afull[s], CG); ptx::mbar_init(&aempty[s], 1); }
+        if (NF) {
+            for (int s = 0; s < 2; ++s) { ptx::mbar_init(&nfull[s], CG); ptx::mbar_init(&nempty[s], 1); }
+            ptx::mbar_init(onefull, CG);
+            ptx::prefetch_tmap(&tm_n); ptx::prefetch_tmap(&tm_one);
+        }
         ptx::fence_barrier_init();
     }
     if (warp == 1) {
@@ -295,6 +360,13 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
             uint32_t phase = 0, sph = 0, aph = 0;
             long long item_tile = 0, item_end = 0;  // QS: tiles left of the current work item
             int item_qb = 0;
+            int nb = 0;
+            uint32_t nph = 0;
+            if constexpr (NF) {
+                if (rank == 0) ptx::mbar_arrive_expect_tx(onefull, 2 * L::ONES_BYTES);
+                else ptx::mbar_arrive_cluster(onefull, 0);
+                ptx::tma_load_2d_pair(ones, &tm_one, onefull, 0, 0);
+            }
             for (;;) {
                 long long u;
                 if (rank == 0) {
@@ -366,6 +438,15 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
                 const bool load_a = QS && (u & K3_U_FIRST) != 0;
                 const int qrow0 = qb * (K3_BM * CG) + (int)rank * K3_BM;
                 const int64_t xrow0 = t * K3_BN + (int64_t)rank * L::B_ROWS;
+                if constexpr (NF) {
+                    // this tile's norm records, into the buffer that goes with the tile's accumulator
+                    ptx::mbar_wait(&nempty[nb], nph ^ 1);
+                    if (rank == 0) ptx::mbar_arrive_expect_tx(&nfull[nb], 2 * L::NREC_BYTES);
+                    else ptx::mbar_arrive_cluster(&nfull[nb], 0);
+                    ptx::tma_load_2d_pair(nrec + nb * L::NREC_BYTES, &tm_n, &nfull[nb], 0, (int)xrow0);
+                    nb ^= 1;
+                    if (nb == 0) nph ^= 1;
+                }
                 for (int kc = 0; kc < nkc; ++kc) {
                     if (load_a) {
                         // chunk kc of the new query block replaces the old one as soon as the last MMA that read it has retired
@@ -407,6 +488,7 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
             constexpr uint32_t idesc = BF16 ? ptx::umma_idesc_bf16(K3_BM * CG, K3_BN) : ptx::umma_idesc_tf32(K3_BM * CG, K3_BN);
             int stage = 0, as = 0, ss = 0;
             uint32_t phase = 0, aphase = 0, sph = 0, afph = 0;
+            if constexpr (NF) ptx::mbar_wait(onefull, 0);
             for (;;) {
                 const long long u = sched_take_warp<CG>(sfull, sempty, sched_u, ss, sph, rank, lane);
                 if (++ss == K3_NSCHED) { ss = 0; sph ^= 1; }
@@ -441,10 +523,22 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
                         }
                         ptx::mma_commit<CG>(&empty[stage]);            // smem slot free once these MMAs retire
                         if (a_last) ptx::mma_commit<CG>(&aempty[kc]);  // ... and this chunk of the query block, for the next work item
-                        if (kc == nkc - 1) ptx::mma_commit<CG>(&tfull[as]);  // accumulator complete
+                        if (!NF && kc == nkc - 1) ptx::mma_commit<CG>(&tfull[as]);  // accumulator complete
                     }
                     __syncwarp();
                     if (++stage == NS) { stage = 0; phase ^= 1; }
+                }
+                if constexpr (NF) {
+                    // last, so that the large term meets the accumulator once: acc = q~.x~ - (h1 + h2 + h3)
+                    ptx::mbar_wait(&nfull[as], aphase);
+                    ptx::tc_fence_after();
+                    if (lane == 0) {
+                        ptx::mma_bf16<CG>(d_tmem, ptx::umma_desc_k_sw32(ptx::smem_u32(ones)),
+                                          ptx::umma_desc_k_sw32(ptx::smem_u32(nrec + as * L::NREC_BYTES)), idesc, 1u);
+                        ptx::mma_commit<CG>(&nempty[as]);
+                        ptx::mma_commit<CG>(&tfull[as]);
+                    }
+                    __syncwarp();
                 }
                 if (a_first) afph ^= 1;
                 if (SEP) { aphase ^= 1; }
@@ -481,6 +575,7 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
             return ptx::mbar_try_wait(&sfull[ss], sph);
         };
         auto issue_norms = [&](long long u, float* dst) {
+            if constexpr (NF) return;
             const int64_t t = unit_tile(u);
             for (int j = epi_tid; j < K3_BN; j += EPI_THREADS) {
                 const int64_t r = t * K3_BN + j;
@@ -524,6 +619,12 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
             // filter threshold on s = ||x||^2 - 2 ip, widened by a few ulps so it never rejects a
             // candidate the exact test below would accept
             const float t_cmp = valid ? (tau_eff - qn) + 2e-6f * (fabsf(tau_eff) + qn) : -INF;
+            // norm fold: a = q~.x~ - ||x||^2/2 passes iff ||q||^2 - 2a <= tau_eff, i.e. a >= (||q||^2 - tau_eff)/2, widened likewise
+            const float thr0 = 0.5f * (qn - tau_eff);
+            const float thr = valid ? thr0 - 1e-6f * (fabsf(thr0) + qn) : INF;
+            // columns of this tile that are real rows (the last tile is ragged; the warm-start pass looks at fewer)
+            const int64_t rows_left = p.n - t * K3_BN;
+            const int ncols_tile = (int)(rows_left < p.tile_cols ? rows_left : p.tile_cols) - h * HCOLS;
             float* xn = xn_s + xb * K3_BN;
             if (NH > 1 && h == 0) cnt_s[row] = cnt;
             ptx::cp_async_wait_all();
@@ -573,6 +674,8 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
                 if (SEP) ptx::tmem_ld_32x32(taddr + K3_BN + c0 + 32, wb);
                 reg_fence32(va);
                 if (SEP) reg_fence32(wa);
+                if constexpr (NF) { if (ncols_tile > c0) k3_filter_chunk_nf<(NH > 1)>(va, thr, qn, tau_eff, kth_eff, row_base + c0, ncols_tile - c0, list, cnt, cnt_s + row); }
+                else
                 k3_filter_chunk<SEP, (NH > 1)>(va, wa, xnh + c0, t_cmp, qn, tau_eff, kth_eff, row_base + c0, list, cnt, cnt_s + row);
                 ptx::tmem_ld_wait();
                 if (c0 + 64 < HCOLS) {
@@ -581,6 +684,8 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
                 }
                 reg_fence32(vb);
                 if (SEP) reg_fence32(wb);
+                if constexpr (NF) { if (ncols_tile > c0 + 32) k3_filter_chunk_nf<(NH > 1)>(vb, thr, qn, tau_eff, kth_eff, row_base + c0 + 32, ncols_tile - c0 - 32, list, cnt, cnt_s + row); }
+                else
                 k3_filter_chunk<SEP, (NH > 1)>(vb, wb, xnh + c0 + 32, t_cmp, qn, tau_eff, kth_eff, row_base + c0 + 32, list, cnt, cnt_s + row);
             }
             }
@@ -686,8 +791,9 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
 
 // ---- state initialisation -------------------------------------------------------------------
 __global__ void k3_init_kernel(int64_t nslots, int* cnt, float* tau, u64* kth, int64_t nq, unsigned int* gts,
-                               u64* next_unit, unsigned int* overflow) {
+                               u64* next_unit, unsigned int* overflow, unsigned short* ones) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (ones && i < K3_BM * 16) ones[i] = (i & 15) < 3 ? 0x3F80 : 0;  // bf16 1.0 in the three columns that meet the norm terms
     if (i == 0) { *next_unit = 0; if (overflow) *overflow = 0; }
     if (i < nslots) { cnt[i] = 0; tau[i] = FLT_MAX; kth[i] = (u64)FLT_MAX_BITS << 32; }
     if (gts && i < nq) gts[i] = FLT_MAX_BITS;
@@ -1126,7 +1232,7 @@ void k3_set_cta_group(K3State* s, int cg);
 
 struct K3Layout {
     int cg, ncta, nqb, qpc, P;
-    size_t off_qlo, off_qn, off_gts, off_slack, off_next, off_cnt, off_tau, off_kth, off_cand, total;
+    size_t off_qlo, off_qn, off_gts, off_slack, off_next, off_ones, off_cnt, off_tau, off_kth, off_cand, total;
 };
 
 static K3Layout k3_layout(int sm_count, int d, int64_t nq, int k, int want_cg, bool screen, int64_t n) {
@@ -1145,6 +1251,7 @@ static K3Layout k3_layout(int sm_count, int d, int64_t nq, int k, int want_cg, b
     L.off_gts = o; o += al((size_t)nq * 4);
     L.off_slack = o; o += al((size_t)nq * 4);
     L.off_next = o; o += 256;  // [0] scheduler counter (u64), [16] overflow flag
+    L.off_ones = o; o += K3_BM * 32;  // the block of ones of the norm fold: [128][16] bf16, columns 0..2 = 1
     size_t slots = (size_t)L.ncta * L.qpc;
     L.off_cnt = o; o += al(slots * 4);
     L.off_tau = o; o += al(slots * 4);
@@ -1212,14 +1319,16 @@ int k3_last_kernel_ms(K3State* s, float* ms) {
     return B2K_OK;
 }
 
-static int make_map(K3State* s, CUtensorMap* m, const void* base, int64_t rows, int d, int box_rows, bool bf16 = false) {
+// rec32: the tensor is [rows][16] bf16 (32-byte records: norm terms / the ones block), boxes are whole records, 32-byte swizzle
+static int make_map(K3State* s, CUtensorMap* m, const void* base, int64_t rows, int d, int box_rows, bool bf16 = false,
+                    bool rec32 = false) {
     cuuint64_t gdim[2] = {(cuuint64_t)d, (cuuint64_t)rows};
     cuuint64_t gstr[1] = {(cuuint64_t)d * (bf16 ? 2 : 4)};
-    cuuint32_t box[2] = {(cuuint32_t)(bf16 ? 64 : K3_BK), (cuuint32_t)box_rows};  // 128 bytes wide either way
+    cuuint32_t box[2] = {(cuuint32_t)(rec32 ? 16 : bf16 ? 64 : K3_BK), (cuuint32_t)box_rows};  // 128 bytes wide (32 for records)
     cuuint32_t estr[2] = {1, 1};
     CUresult r = s->encode(m, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), gdim, gstr, box, estr,
-                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, rec32 ? CU_TENSOR_MAP_SWIZZLE_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                           CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
         set_error("cuTensorMapEncodeTiled failed (%d) for %lld x %d", (int)r, (long long)rows, d);
         return B2K_ECUDA;
@@ -1228,9 +1337,10 @@ static int make_map(K3State* s, CUtensorMap* m, const void* base, int64_t rows, 
 }
 
 static constexpr size_t K3_SMEM_LIMIT = 227 * 1024;
+struct K3Maps { CUtensorMap q, ql, x, xl, n, one; };
 
 template <int CG, int NS, int MODE, int NH, bool QS = false>
-static int launch_k3(const CUtensorMap& mq, const CUtensorMap& mql, const CUtensorMap& mx, const CUtensorMap& mxl,
+static int launch_k3(const K3Maps& mm,
                      const K3Params& p, int ncta, cudaStream_t st) {
     const int nkc = (p.d + (MODE == 3 ? 64 : 32) - 1) / (MODE == 3 ? 64 : 32);
     size_t smem = K3Smem<CG, NS, MODE, QS>::bytes(p.P, nkc);
@@ -1247,19 +1357,18 @@ static int launch_k3(const CUtensorMap& mq, const CUtensorMap& mql, const CUtens
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    B2K_CUDA(cudaLaunchKernelEx(&cfg, k3_tf32x3_topk_kernel<CG, NS, MODE, NH, QS>, mq, mql, mx, mxl, p));
+    B2K_CUDA(cudaLaunchKernelEx(&cfg, k3_tf32x3_topk_kernel<CG, NS, MODE, NH, QS>, mm.q, mm.ql, mm.x, mm.xl, mm.n, mm.one, p));
     count_launch();
     return B2K_OK;
 }
 
 // nh: 1 = four epilogue warps, 2 = eight (two per scheduler; screening modes with one CTA per tile)
-static int launch_k3_any(int cg, int P, int mode, int nh, const CUtensorMap& mq, const CUtensorMap& mql, const CUtensorMap& mx,
-                         const CUtensorMap& mxl, const K3Params& p, int ncta, cudaStream_t st) {
+static int launch_k3_any(int cg, int P, int mode, int nh, const K3Maps& mm, const K3Params& p, int ncta, cudaStream_t st) {
 #define B2K_K3_CASE(MODE_)                                                                        \
     case MODE_:                                                                                   \
-        if (cg == 1) return launch_k3<1, 2, MODE_, 1>(mq, mql, mx, mxl, p, ncta, st);             \
-        if (P <= 512) return launch_k3<2, 3, MODE_, 1>(mq, mql, mx, mxl, p, ncta, st);            \
-        return launch_k3<2, 2, MODE_, 1>(mq, mql, mx, mxl, p, ncta, st);
+        if (cg == 1) return launch_k3<1, 2, MODE_, 1>(mm, p, ncta, st);             \
+        if (P <= 512) return launch_k3<2, 3, MODE_, 1>(mm, p, ncta, st);            \
+        return launch_k3<2, 2, MODE_, 1>(mm, p, ncta, st);
     switch (mode) {
         B2K_K3_CASE(0)
         B2K_K3_CASE(1)
@@ -1271,11 +1380,11 @@ static int launch_k3_any(int cg, int P, int mode, int nh, const CUtensorMap& mq,
 #define B2K_K3_SCREEN(MODE_, NH_)                                                                  \
     if (mode == MODE_ && nh == NH_) {                                                              \
         if (cg == 1) {                                                                             \
-            if (P <= 512) return launch_k3<1, 4, MODE_, NH_>(mq, mql, mx, mxl, p, ncta, st);       \
-            return launch_k3<1, 2, MODE_, NH_>(mq, mql, mx, mxl, p, ncta, st);                     \
+            if (P <= 512) return launch_k3<1, 4, MODE_, NH_>(mm, p, ncta, st);       \
+            return launch_k3<1, 2, MODE_, NH_>(mm, p, ncta, st);                     \
         }                                                                                          \
-        if (P <= 512) return launch_k3<2, 6, MODE_, NH_>(mq, mql, mx, mxl, p, ncta, st);           \
-        return launch_k3<2, 4, MODE_, NH_>(mq, mql, mx, mxl, p, ncta, st);                         \
+        if (P <= 512) return launch_k3<2, 6, MODE_, NH_>(mm, p, ncta, st);           \
+        return launch_k3<2, 4, MODE_, NH_>(mm, p, ncta, st);                         \
     }
     B2K_K3_SCREEN(2, 1)
     B2K_K3_SCREEN(2, 2)
@@ -1298,12 +1407,11 @@ static int k3_qs_stages(int mode, int d, int P) {
     return 0;
 }
 
-static int launch_k3_qs(int mode, int nsb, const CUtensorMap& mq, const CUtensorMap& mql, const CUtensorMap& mx,
-                        const CUtensorMap& mxl, const K3Params& p, int ncta, cudaStream_t st) {
-    if (mode == 3 && nsb == 6) return launch_k3<2, 6, 3, 2, true>(mq, mql, mx, mxl, p, ncta, st);
-    if (mode == 3 && nsb == 4) return launch_k3<2, 4, 3, 2, true>(mq, mql, mx, mxl, p, ncta, st);
-    if (mode == 2 && nsb == 6) return launch_k3<2, 6, 2, 2, true>(mq, mql, mx, mxl, p, ncta, st);
-    if (mode == 2 && nsb == 4) return launch_k3<2, 4, 2, 2, true>(mq, mql, mx, mxl, p, ncta, st);
+static int launch_k3_qs(int mode, int nsb, const K3Maps& mm, const K3Params& p, int ncta, cudaStream_t st) {
+    if (mode == 3 && nsb == 6) return launch_k3<2, 6, 3, 2, true>(mm, p, ncta, st);
+    if (mode == 3 && nsb == 4) return launch_k3<2, 4, 3, 2, true>(mm, p, ncta, st);
+    if (mode == 2 && nsb == 6) return launch_k3<2, 6, 2, 2, true>(mm, p, ncta, st);
+    if (mode == 2 && nsb == 4) return launch_k3<2, 4, 2, 2, true>(mm, p, ncta, st);
     set_error("tensor kernel: no query-stationary variant for mode %d with %d stages", mode, nsb);
     return B2K_EINVAL;
 }
@@ -1321,7 +1429,7 @@ static void launch_k4(int64_t nq, cudaStream_t st, const K3Params& p, int cg, in
                                                                                       set_counter, counter_value);
 }
 
-int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, const float* norms,
+int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, const void* xnb, const float* norms,
               const unsigned int* max_norm_bits, const unsigned int* max_err_bits, int64_t n, int d, const float* q,
               int64_t nq, int k, float* D, int64_t* I, unsigned char* scratch, cudaStream_t st, int mode,
               int* overflowed) {
@@ -1329,7 +1437,7 @@ int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, con
     const bool onep = mode == 2 || mode == 3;  // one product per k-step (no residual operands)
     const bool bf16 = mode == 3;
     if (mode < 1 || mode > 4) { set_error("tensor kernel: bad mode %d", mode); return B2K_EINVAL; }
-    if (bf16 && (d % 8 != 0 || !xbf || !max_err_bits)) { set_error("tensor kernel: bf16 screening needs d %% 8 == 0 and the bf16 rows"); return B2K_EINVAL; }
+    if (bf16 && (d % 8 != 0 || !xbf || !xnb || !max_err_bits)) { set_error("tensor kernel: bf16 screening needs d %% 8 == 0 and the bf16 rows"); return B2K_EINVAL; }
     if (overflowed) *overflowed = 0;
     s->last_mode = mode;
     K3Layout L = k3_layout(s->sm_count, d, nq, k, s->cg, onep, n);
@@ -1395,8 +1503,9 @@ int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, con
     }
     const int64_t nslots = (int64_t)L.ncta * L.qpc;
     const int64_t ninit = nslots > nq ? nslots : nq;
-    k3_init_kernel<<<(unsigned)((ninit + 255) / 256), 256, 0, st>>>(nslots, p.cnt, p.tau, p.kth, nq, p.gts, p.next_unit,
-                                                                    s->ext_flag ? nullptr : p.overflow);
+    unsigned short* ones_dev = reinterpret_cast<unsigned short*>(scratch + L.off_ones);
+    k3_init_kernel<<<(unsigned)(((ninit > K3_BM * 16 ? ninit : K3_BM * 16) + 255) / 256), 256, 0, st>>>(
+        nslots, p.cnt, p.tau, p.kth, nq, p.gts, p.next_unit, s->ext_flag ? nullptr : p.overflow, bf16 ? ones_dev : nullptr);
     count_launch();
     B2K_CUDA(cudaGetLastError());
 
@@ -1404,12 +1513,16 @@ int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, con
     // K4 did not get faster, it was bound by its sort, not by residency, and the smaller re-rank buffer
     // made the 3xTF32 screen overflow on data it otherwise handles)
     B2K_CUDA(cudaFuncSetAttribute(k4_merge_kernel<4096>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(K4Smem<4096>)));
-    CUtensorMap mq, mql, mx, mxl;
+    CUtensorMap mq, mql, mx, mxl, mn, mone;
     if (bf16) {
         if ((rc = make_map(s, &mq, qlo, nq_pad, d, K3_BM, true))) return rc;
         if ((rc = make_map(s, &mx, xbf, n, d, K3_BN / L.cg, true))) return rc;
         mql = mq;
         mxl = mx;
+        if (L.cg == 2) {  // the norm fold's operands: 32-byte records of the rows, and the block of ones
+            if ((rc = make_map(s, &mn, xnb, n, 16, K3_BN / L.cg, true, true))) return rc;
+            if ((rc = make_map(s, &mone, ones_dev, K3_BM, 16, K3_BM, true, true))) return rc;
+        }
     } else if (mode == 2 && nq_pad > nq) {
         if ((rc = make_map(s, &mq, qlo, nq_pad, d, K3_BM))) return rc;
         if ((rc = make_map(s, &mx, x, n, d, K3_BN / L.cg))) return rc;
@@ -1421,6 +1534,9 @@ int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, con
         if ((rc = make_map(s, &mx, x, n, d, K3_BN / L.cg))) return rc;
         if ((rc = make_map(s, &mxl, onep ? x : xlo, n, d, K3_BN / L.cg))) return rc;
     }
+
+    if (!(bf16 && L.cg == 2)) { mn = mx; mone = mq; }  // unused by the other kernels
+    const K3Maps mm{mq, mql, mx, mxl, mn, mone};
 
     // Warm start: the first 64 rows of one tile per CTA (pair) with open thresholds -- every key is
     // kept, so the pass is kept small; per query the k-th smallest distance of that sample becomes
@@ -1450,10 +1566,10 @@ int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, con
         pre.static_qb_mod = G;
         pre.nunits = (int64_t)nclusters * L.nqb;
         pre.n = (int64_t)nclusters * K3_BN;
-        rc = launch_k3_any(L.cg, L.P, sep, nh, mq, mql, mx, mxl, pre, L.ncta, st);
+        rc = launch_k3_any(L.cg, L.P, sep, nh, mm, pre, L.ncta, st);
         if (rc) return rc;
         launch_k4(nq, st, pre, L.cg, L.ncta, 1, 1, nullptr, nullptr);
-        k3_init_kernel<<<(unsigned)((nslots + 255) / 256), 256, 0, st>>>(nslots, p.cnt, p.tau, p.kth, nq, nullptr, p.next_unit, nullptr);
+        k3_init_kernel<<<(unsigned)((nslots + 255) / 256), 256, 0, st>>>(nslots, p.cnt, p.tau, p.kth, nq, nullptr, p.next_unit, nullptr, nullptr);
         count_launch(2);
         B2K_CUDA(cudaGetLastError());
         warm_rows = (int64_t)nclusters * cols_a / G;
@@ -1521,8 +1637,8 @@ int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, con
             count_launch();
             B2K_CUDA(cudaGetLastError());
         }
-        rc = qs ? launch_k3_qs(sep, qs_nsb, mq, mql, mx, mxl, ps, L.ncta, st)
-                : launch_k3_any(L.cg, L.P, sep, nh, mq, mql, mx, mxl, ps, L.ncta, st);
+        rc = qs ? launch_k3_qs(sep, qs_nsb, mm, ps, L.ncta, st)
+                : launch_k3_any(L.cg, L.P, sep, nh, mm, ps, L.ncta, st);
         if (rc) return rc;
     }
     if (s->timing) { B2K_CUDA(cudaEventRecord(s->ev1, st)); s->timed = true; }

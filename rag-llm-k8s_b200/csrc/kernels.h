@@ -11,6 +11,8 @@ int launch_row_prep(const float* X, int64_t n, int d, float* norms, float* xlo, 
 // bf16 (round-to-nearest) copies of rows [0,n) of X into xb, with the squared rounding-error norm per row
 // (err2, nullable) and its running maximum (max_err_bits, nullable, float bits).  Needs d % 8 == 0.
 int launch_row_bf16(const float* X, int64_t n, int d, void* xb, float* err2, unsigned int* max_err_bits, cudaStream_t st);
+// -||x||^2/2 of rows [0,n) as three bf16 terms in a 32-byte record per row (the bf16 screening pass adds it by MMA)
+int launch_norm_split(const float* norms, int64_t n, void* out, cudaStream_t st);
 int launch_synth(uint64_t seed, int64_t row0, int64_t nrows, int d, float* out, cudaStream_t st);
 
 // K2 (k2_scan.cu)
