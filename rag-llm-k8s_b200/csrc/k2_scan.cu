@@ -558,11 +558,25 @@ scan_rerank_kernel(const float* __restrict__ X, const float* __restrict__ Q, int
         if (id < 0) continue;  // warp-uniform
         const float* xv = X + id * (int64_t)d;
         float acc = 0.f;
-        for (int t = lane * 4; t < d; t += 128) {
-            const float4 a = __ldg(reinterpret_cast<const float4*>(qv + t));
-            const float4 b = ldg_stream(reinterpret_cast<const float4*>(xv + t));
-            const float e0 = a.x - b.x, e1 = a.y - b.y, e2 = a.z - b.z, e3 = a.w - b.w;
-            acc = fmaf(e0, e0, acc); acc = fmaf(e1, e1, acc); acc = fmaf(e2, e2, acc); acc = fmaf(e3, e3, acc);
+        // up to four 512-byte slices of the row are requested before the first is used: the row is a random
+        // HBM read, and one round trip per 512 columns beats one per 128 (same summation order per lane)
+        for (int t0 = lane * 4; t0 < d; t0 += 512) {
+            float4 a[4], b[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int t = t0 + j * 128;
+                if (t < d) {
+                    a[j] = __ldg(reinterpret_cast<const float4*>(qv + t));
+                    b[j] = ldg_stream(reinterpret_cast<const float4*>(xv + t));
+                } else {
+                    a[j] = b[j] = make_float4(0.f, 0.f, 0.f, 0.f);  // adds exact zeros
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float e0 = a[j].x - b[j].x, e1 = a[j].y - b[j].y, e2 = a[j].z - b[j].z, e3 = a[j].w - b[j].w;
+                acc = fmaf(e0, e0, acc); acc = fmaf(e1, e1, acc); acc = fmaf(e2, e2, acc); acc = fmaf(e3, e3, acc);
+            }
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
