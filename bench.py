@@ -98,7 +98,7 @@ class ClockSampler(threading.Thread):
                         self.reasons.add(name)
             except Exception:
                 pass
-            time.sleep(0.02)
+            time.sleep(0.002)
 
     def result(self):
         return {"sm_mhz": statistics.median(self.sm) if self.sm else None, "sm_max_mhz": self.sm_max,
@@ -392,10 +392,7 @@ def run_workload(ctx, name, N, d, nq, k, steps, warmup, extras):
     sampler.stop_flag = True
     sampler.join()
     stats = index.stats() if hasattr(index, "stats") else {}
-    if world > 1:
-        e2e_call = lambda: index.search(q_host, k)            # (the sharded index allocates its own outputs)
-    else:
-        e2e_call = lambda: index.search(q_host, k, D=D_pin, I=I_pin)
+    e2e_call = lambda: index.search(q_host, k, D=D_pin, I=I_pin)
     _, wall_e2e, _ = timed(e2e_call, steps, max(warmup, 1))
 
     # p50 single-query latency on the same index (second half of BASELINE.json's metric):

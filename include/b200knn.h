@@ -144,11 +144,26 @@ B2K_API int b2k_merge_topk(int device, int nlists, int64_t nq, int64_t k, const 
  * distances at Din + l*list_stride_d and its ids at Iin + l*list_stride_i (strides in elements, so
  * the lists may sit inside packed all-gather records), and with cyclic_block = B > 0 the ids are
  * shard-local rows of the block-cyclic layout above (B rows per block, nlists shards) and come out as
- * global rows; B = 0 leaves them as they are. */
+ * global rows; B = 0 leaves them as they are.  Each list must be sorted ascending by (distance, id) with its
+ * padding at the tail -- as b2k_search returns it -- and no id may occur in two lists (shards are disjoint): the
+ * kernel merges by rank instead of sorting. */
 B2K_API int b2k_merge_shards(int device, int nlists, int64_t nq, int64_t k, const float* Din,
                      int64_t list_stride_d, const int64_t* Iin, int64_t list_stride_i,
                      int64_t cyclic_block, float* D, int64_t* I, void* stream);
 #define B2K_CYCLIC_BLOCK 4096  /* rows per block of the multi-GPU layout */
+
+/* The exchange step of the one-process-per-GPU sharded index as a one-shot all-gather over peer memory (no
+ * counterpart in the reference, which is one process).  b2k_exchange_push stores `bytes` of `record` (device memory,
+ * 16-byte aligned and sized) into slot my_rank (slot_bytes apart) of every rank's receive buffer -- dst_ptrs_dev is a
+ * DEVICE array of nranks base addresses, peer-mapped (e.g. torch symmetric memory) -- and then writes seq into word
+ * flag_index of every rank's flag row (flag_ptrs_dev: device array of the rows' base addresses).  done_dev: nranks zeroed words of scratch on this device.  b2k_exchange_wait enqueues a
+ * bounded wait until flags_dev[0..nranks) have all reached seq; if a rank never arrives it sets *err_dev (nonzero)
+ * instead of hanging.  Sequence numbers must grow per flag word; callers alternate two buffer halves so that a rank
+ * one call ahead never overwrites a record still being read. */
+B2K_API int b2k_exchange_push(int device, const void* record, int64_t bytes, const uint64_t* dst_ptrs_dev,
+                      const uint64_t* flag_ptrs_dev, int nranks, int my_rank, int64_t slot_bytes, int flag_index,
+                      uint32_t seq, uint32_t* done_dev, void* stream);
+B2K_API int b2k_exchange_wait(int device, const uint32_t* flags_dev, int nranks, uint32_t seq, uint32_t* err_dev, void* stream);
 
 /* Search without allocating anything.  No counterpart in the reference (llm/rag.py never
  * manages device memory); it exists for callers that cannot call cudaMalloc -- a process

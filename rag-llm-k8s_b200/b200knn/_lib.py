@@ -41,6 +41,9 @@ SIGNATURES = {
                                  C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     "b2k_merge_shards": (C.c_int, [C.c_int, C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64,
                                    C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "b2k_exchange_push": (C.c_int, [C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int64, C.c_int,
+                                    C.c_uint32, C.c_void_p, C.c_void_p]),
+    "b2k_exchange_wait": (C.c_int, [C.c_int, C.c_void_p, C.c_int, C.c_uint32, C.c_void_p, C.c_void_p]),
     "b2k_search_rows_noalloc": (C.c_int, [C.c_int, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_int64, C.c_int64,
                                           C.c_void_p, C.c_void_p, C.c_void_p]),
     "b2k_set_option": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int64]),

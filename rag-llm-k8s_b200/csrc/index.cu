@@ -907,6 +907,26 @@ int b2k_merge_shards(int device, int nlists, int64_t nq, int64_t k, const float*
     return launch_merge_shards(nlists, nq, (int)k, Din, list_stride_d, Iin, list_stride_i, cyclic_block, D, I, (cudaStream_t)stream);
 }
 
+int b2k_exchange_push(int device, const void* record, int64_t bytes, const uint64_t* dst_ptrs_dev, const uint64_t* flag_ptrs_dev,
+                      int nranks, int my_rank, int64_t slot_bytes, int flag_index, uint32_t seq, uint32_t* done_dev, void* stream) {
+    if (!record || bytes <= 0 || !dst_ptrs_dev || !flag_ptrs_dev || nranks <= 0 || nranks > 64 || my_rank < 0 || my_rank >= nranks || !done_dev) {
+        set_error("b2k_exchange_push: bad argument");
+        return B2K_EINVAL;
+    }
+    int rc = check_device(device, nullptr);
+    if (rc) return rc;
+    DeviceGuard g(device);
+    return launch_push_record(record, bytes, dst_ptrs_dev, flag_ptrs_dev, nranks, my_rank, slot_bytes, flag_index, seq, done_dev, (cudaStream_t)stream);
+}
+
+int b2k_exchange_wait(int device, const uint32_t* flags_dev, int nranks, uint32_t seq, uint32_t* err_dev, void* stream) {
+    if (!flags_dev || nranks <= 0 || nranks > 64 || !err_dev) { set_error("b2k_exchange_wait: bad argument"); return B2K_EINVAL; }
+    int rc = check_device(device, nullptr);
+    if (rc) return rc;
+    DeviceGuard g(device);
+    return launch_wait_flags(flags_dev, nranks, seq, err_dev, (cudaStream_t)stream);
+}
+
 // ---- IxF2 persistence ------------------------------------------------------------------
 // Layout (little-endian, packed) [faiss-upstream index_write.cpp, SURVEY.md 8a-a5]:
 //   "IxF2" | d int32 | ntotal int64 | 1<<20 int64 | 1<<20 int64 | is_trained u8 (1) |

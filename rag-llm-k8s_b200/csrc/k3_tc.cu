@@ -926,6 +926,79 @@ __device__ __forceinline__ uint32_t k4_select_dist(const u64* a, int n, int k, u
     return prefix;
 }
 
+// An UPPER BOUND of the k-th smallest distance (1 <= k <= n) among the n keys of `a` that is itself one of the
+// distances: a 2048-bin histogram over [min, max] of the keys, the bin in which the running count reaches k, and
+// the largest key in the bins up to there.  The bound refreshes of the pass only prune with the number, so
+// "k-th smallest or a hair above" is as good as exact, and it costs one histogram pass instead of three
+// (9 block barriers instead of 15).  hist: 2048 words.  Block-wide; every thread returns the result.
+__device__ __forceinline__ uint32_t k4_bound_linear(const u64* a, int n, int k, uint32_t* hist, int* scratch2) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    __shared__ float s_lo[K4_THREADS / 32], s_hi[K4_THREADS / 32];
+    __shared__ int s_ws[K4_THREADS / 32];
+    float lo = __int_as_float(0x7f800000), hi = 0.f;
+    for (int i = tid; i < n; i += K4_THREADS) {
+        const float dv = key_dist(a[i]);
+        lo = fminf(lo, dv); hi = fmaxf(hi, dv);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+        hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+    }
+    if (lane == 0) { s_lo[warp] = lo; s_hi[warp] = hi; }
+    for (int b = tid; b < 2048; b += K4_THREADS) hist[b] = 0;
+    __syncthreads();
+#pragma unroll
+    for (int w = 0; w < K4_THREADS / 32; ++w) { lo = fminf(lo, s_lo[w]); hi = fmaxf(hi, s_hi[w]); }
+    if (!(hi > lo) || !(hi < FLT_MAX)) return __float_as_uint(hi);  // all keys equal (block-uniform exit)
+    const float scale = 2047.f / (hi - lo);
+    for (int i = tid; i < n; i += K4_THREADS) {
+        int b = (int)((key_dist(a[i]) - lo) * scale);
+        b = b < 0 ? 0 : (b > 2047 ? 2047 : b);
+        atomicAdd(&hist[b], 1u);
+    }
+    __syncthreads();
+    int mine = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) mine += (int)hist[tid * 8 + j];
+    int incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+    }
+    if (lane == 31) s_ws[warp] = incl;
+    __syncthreads();
+    int before = incl - mine;
+    for (int w = 0; w < warp; ++w) before += s_ws[w];
+    if (before < k && k <= before + mine) {  // exactly one thread: the k-th key is in its bins
+        int c = before;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int hcount = (int)hist[tid * 8 + j];
+            if (c < k && k <= c + hcount) scratch2[0] = tid * 8 + j;
+            c += hcount;
+        }
+    }
+    __syncthreads();
+    const int bsel = scratch2[0];
+    float best = 0.f;  // largest key in bins 0..bsel (same bin arithmetic as above, so it covers at least k keys)
+    for (int i = tid; i < n; i += K4_THREADS) {
+        const float dv = key_dist(a[i]);
+        int b = (int)((dv - lo) * scale);
+        b = b < 0 ? 0 : (b > 2047 ? 2047 : b);
+        if (b <= bsel) best = fmaxf(best, dv);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) best = fmaxf(best, __shfl_xor_sync(0xffffffffu, best, o));
+    __syncthreads();  // s_hi is reused
+    if (lane == 0) s_hi[warp] = best;
+    __syncthreads();
+#pragma unroll
+    for (int w = 0; w < K4_THREADS / 32; ++w) best = fmaxf(best, s_hi[w]);
+    return __float_as_uint(best);
+}
+
 template <int K4_P>
 __global__ void __launch_bounds__(K4_THREADS)
 k4_merge_kernel(const K3Params p, int cg, int ncta, int threshold_only, int list_step, float* __restrict__ D,
@@ -952,7 +1025,7 @@ k4_merge_kernel(const K3Params p, int cg, int ncta, int threshold_only, int list
         if (threshold_only && attempt == 0 && total <= K4_P) {
             // bound refresh: only the k-th smallest distance is wanted, no order
             if (total >= k) {
-                const uint32_t dk = k4_select_dist(sm.buf, total, k, reinterpret_cast<uint32_t*>(sm.out), sm.sel);
+                const uint32_t dk = k4_bound_linear(sm.buf, total, k, reinterpret_cast<uint32_t*>(sm.out), sm.sel);
                 if (tid == 0) atomicMin(p.gts + qi, dk);
             }
             return;

@@ -37,4 +37,11 @@ int launch_merge_lists(int nlists, int64_t nq, int k, const float* Din, const in
 int launch_merge_shards(int nlists, int64_t nq, int k, const float* Din, int64_t stride_d, const int64_t* Iin,
                         int64_t stride_i, int64_t cyc_block, float* D, int64_t* I, cudaStream_t st);
 
+// one-shot all-gather over peer memory: store `bytes` of src into slot my_rank of every rank's receive buffer
+// (dst_ptrs_dev: device array of nranks base addresses), then publish seq in word flag_index of every rank's flag row
+int launch_push_record(const void* src, int64_t bytes, const uint64_t* dst_ptrs_dev, const uint64_t* flag_ptrs_dev, int nranks,
+                       int my_rank, int64_t slot_bytes, int flag_index, unsigned int seq, unsigned int* done_dev, cudaStream_t st);
+// bounded wait for flags[0..n) >= seq; raises *err (1 + index of the missing rank) on time-out
+int launch_wait_flags(const unsigned int* flags, int n, unsigned int seq, unsigned int* err, cudaStream_t st);
+
 }  // namespace b2k

@@ -26,17 +26,18 @@ from b200knn import merge_shards
 for i in range(25):
     torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
     t0 = time.perf_counter()
-    nk, words, send, recv = idx._buffers(nq, k)
+    nk, words, (send, recv, slot, p2p) = idx._buffers(nq, k)
     I_loc = send[:nk].view(nq, k); D_loc = send[nk:words].view(torch.float32)[:nk].view(nq, k)
     e0 = ev()
     send[words:].zero_()
     idx.local.search(qq, k, D=D_loc, I=I_loc)
     e1 = ev()
     e2 = ev()
-    dist.all_gather_into_tensor(recv, send)
+    rnccl = torch.empty(W * slot, dtype=torch.int64, device=qq.device) if i == 0 else rnccl
+    dist.all_gather_into_tensor(rnccl, send)          # (the NCCL form of the exchange, timed for comparison)
     e3 = ev()
     Dm = torch.empty((nq, k), dtype=torch.float32, device=qq.device); Im = torch.empty((nq, k), dtype=torch.int64, device=qq.device)
-    merge_shards(recv.data_ptr() + 8 * nk, 2 * (words + 1), recv.data_ptr(), words + 1, W, nq, k, Dm, Im, cyclic_block=idx.block)
+    merge_shards(rnccl.data_ptr() + 8 * nk, 2 * slot, rnccl.data_ptr(), slot, W, nq, k, Dm, Im, cyclic_block=idx.block)
     e4 = ev()
     torch.cuda.synchronize(); t1 = time.perf_counter()
     if i >= 5:
@@ -50,6 +51,6 @@ for i in range(15):
     if i >= 5: tot.append(e0.elapsed_time(e1))
 if dist.get_rank() == 0:
     med = [statistics.median(c) for c in zip(*rows)]
-    print("N=%d nq=%d k=%d d=%d world=%d: local search %.3f (main pass %.3f) | pack %.3f | all_gather %.3f | merge %.3f | wall %.3f ms ; public search() %.3f ms"
+    print(("N=%d nq=%d k=%d d=%d world=%d exchange=" + ("p2p" if idx._p2p is not None else "nccl") + ": local search %.3f (main pass %.3f) | pack %.3f | NCCL all_gather %.3f | merge %.3f | wall %.3f ms ; public search() %.3f ms")
           % (N, nq, k, d, W, med[0], med[5], med[1], med[2], med[3], med[4], statistics.median(tot)), flush=True)
 dist.destroy_process_group()

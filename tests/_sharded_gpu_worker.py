@@ -59,8 +59,14 @@ def main():
     assert idx.stats()["tensor_mode"] == "bf16screen+rerank"
     assert_knn_matches(D2, I2, xs, q, 10, expanded=True, what="sharded synthetic again")
     dist.barrier()
+    # numpy in, page-locked outputs: filled in place, one synchronisation
+    Dp = torch.empty((40, 10), dtype=torch.float32, pin_memory=True).numpy()
+    Ip = torch.empty((40, 10), dtype=torch.int64, pin_memory=True).numpy()
+    D3, I3 = idx.search(q, 10, D=Dp, I=Ip)
+    assert D3 is Dp and I3 is Ip and np.array_equal(Ip, I2) and np.array_equal(Dp, D2)
+    dist.barrier()
     if rank == 0:
-        print("SHARDED-GPU-OK world=%d" % world)
+        print("SHARDED-GPU-OK world=%d exchange=%s" % (world, "p2p" if idx._p2p is not None else "nccl"))
     dist.destroy_process_group()
 
 
