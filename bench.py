@@ -200,7 +200,7 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     ctx = dict(np=np, torch=torch, b200knn=b200knn, dist=dist, rank=rank, world=world, local_rank=local_rank, args=args)
 
-    res = run_workload(ctx, args.workload, N, d, nq, k, args.steps, args.warmup, extras=True)
+    res = run_workload(ctx, args.workload, N, d, nq, k, args.steps, args.warmup, extras=True, config=config)
     c4 = None
     if (world == 8 and args.workload == "c3" and not args.rows) or args.c4_rows:
         # BASELINE.json configs[3] needs all eight GPUs: measured here, where the driver's scaling run looks
@@ -328,7 +328,8 @@ def tf32_peaks(ctx, index, q_dev, k):
     return out
 
 
-def run_workload(ctx, name, N, d, nq, k, steps, warmup, extras):
+def run_workload(ctx, name, N, d, nq, k, steps, warmup, extras, config=None):
+    config = config if config is not None else {}
     np, torch, b200knn, dist = ctx["np"], ctx["torch"], ctx["b200knn"], ctx["dist"]
     rank, world, local_rank = ctx["rank"], ctx["world"], ctx["local_rank"]
     args = ctx["args"]
@@ -345,6 +346,8 @@ def run_workload(ctx, name, N, d, nq, k, steps, warmup, extras):
         index.add_synthetic(N, SEED_DB, 0)
         n_local = N
     index.set_option("timing", 1)
+    if world > 1:
+        config["exchange"] = "one-shot all-gather over peer memory (b2k_exchange_push)" if index._p2p is not None else "NCCL all_gather_into_tensor"
     if args.tensor_mode:
         index.set_option("tensor_mode", args.tensor_mode)
     q_dev = b200knn.synth(SEED_Q, 0, nq, d, device=local_rank)

@@ -205,6 +205,9 @@ B2K_API int b2k_search_rows_noalloc(int device, const float* x_dev, int64_t n, i
  * "tensor_query_stationary" (1: in the one-product screening modes a CTA pair keeps its query block resident in
  * shared memory over a run of row tiles when it fits -- d <= 512 in bf16 --; 0, the default: both operands stream.
  * Same results either way; measured equally fast),
+ * "prepare_copies" (1: build the bf16 copies of the rows now -- +50% of the row bytes, one conversion pass -- instead
+ * of inside the first search that profits from them; a start-up call for servers that reserve HBM afterwards or
+ * capture their searches),
  * "multi_peer_writes" (multi-GPU handles: 0 = shards keep their results locally and a peer memcpy moves
  * them to devices[0]; 1 = direct peer stores where the GPUs allow it, the default).
  * Unknown key -> B2K_EINVAL. */

@@ -192,6 +192,11 @@ class IndexFlatL2:
     def reserve(self, nrows):
         _lib.check(_lib.lib().b2k_reserve(self._h, int(nrows)))
 
+    def prepare(self):
+        """Build the bf16 copies the search kernels screen on (+50 % of the row bytes) now rather than inside the
+        first search that would profit from them; later adds keep them current."""
+        self.set_option("prepare_copies", 1)
+
     def reconstruct_n(self, i0=0, n=-1):
         if n < 0:
             n = self.ntotal - i0

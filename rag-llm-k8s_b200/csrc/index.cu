@@ -537,6 +537,15 @@ int b2k_set_option(b2k_index* h, const char* key, int64_t value) {
     } else if (!strcmp(key, "scan_rows")) {
         if (value < 0 || value > 2) { set_error("option scan_rows must be 0 (auto), 1 (fp32 rows) or 2 (bf16 copies + exact re-rank)"); return B2K_EINVAL; }
         h->opt_scan_rows = (int)value;
+    } else if (!strcmp(key, "prepare_copies")) {
+        // build the bf16 copies now (start-up) instead of inside the first search that profits from them:
+        // that search would otherwise allocate +50% of the row bytes and pay one conversion pass
+        if (value && h->d % 8 == 0) {
+            DeviceGuard g(h->device);
+            int rc = enable_bf(h->rs.get(), h->stream);
+            if (rc) return rc;
+            B2K_CUDA(cudaStreamSynchronize(h->stream));
+        }
     } else if (!strcmp(key, "tensor_query_stationary")) {
         h->opt_qs = value != 0;
         if (h->k3) k3_set_query_stationary(h->k3, h->opt_qs);

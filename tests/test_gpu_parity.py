@@ -932,3 +932,21 @@ def test_zero_and_far_queries_on_the_screening_path(faiss):
         d64 = O.dist_f64(x, q, I)
         assert np.all(np.abs(d64 - Dt) <= 1e-5 * np.maximum(Dt, 1e-30) + 1e-30), "mode %d: a nearer row was missed" % mode
         assert_knn_matches(D, I, x, q, k, expanded=True, what="zero/far queries, mode %d" % mode)
+
+
+def test_prepare_builds_the_copies_before_the_first_search(faiss):
+    import torch
+    d, n = 128, 1_000_000
+    idx = faiss.IndexFlatL2(d)
+    x = O.synth(8, 0, n, d)
+    idx.add(x)
+    torch.cuda.synchronize()
+    free0 = torch.cuda.mem_get_info(0)[0]
+    idx.prepare()
+    free1 = torch.cuda.mem_get_info(0)[0]
+    assert free0 - free1 >= n * d * 2 * 0.9            # the bf16 copies (+ 32 bytes of norm record per row) exist now
+    q = O.synth(9, 0, 64, d)
+    D, I = idx.search(q, 10)
+    free2 = torch.cuda.mem_get_info(0)[0]
+    assert free1 - free2 < n * d                        # the search allocated its workspace only (~100 MB of candidate lists)
+    assert_knn_matches(D, I, x, q, 10, expanded=True, what="after prepare")
