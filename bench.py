@@ -83,26 +83,39 @@ class ClockSampler(threading.Thread):
         if not self.nv:
             return
         nv = self.nv
-        names = {
-            getattr(nv, "nvmlClocksThrottleReasonHwSlowdown", 0x8): "hw_slowdown",
-            getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
-            getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
-            getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0x4): "sw_power_cap",
-        }
+        names = {0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x10: "sync_boost",
+                 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown", 0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting"}
+        self.power, self.mask = [], 0
+        try:
+            self.power_limit = nv.nvmlDeviceGetEnforcedPowerLimit(self.h) / 1000.0
+        except Exception:
+            self.power_limit = None
         while not self.stop_flag:
             try:
                 self.sm.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
                 r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                self.mask |= int(r)
                 for bit, name in names.items():
-                    if r & bit:
+                    if (r & bit) and name != "gpu_idle":
                         self.reasons.add(name)
+                self.power.append(nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0)
             except Exception:
                 pass
             time.sleep(0.002)
 
     def result(self):
-        return {"sm_mhz": statistics.median(self.sm) if self.sm else None, "sm_max_mhz": self.sm_max,
-                "reasons": sorted(self.reasons), "samples": len(self.sm)}
+        out = {"sm_mhz": statistics.median(self.sm) if self.sm else None, "sm_max_mhz": self.sm_max,
+               "reasons": sorted(self.reasons), "samples": len(self.sm)}
+        if self.nv:
+            out["reasons_mask"] = "0x%x" % getattr(self, "mask", 0)
+            pw = getattr(self, "power", [])
+            out["power_w"] = statistics.median(pw) if pw else None
+            out["power_limit_w"] = getattr(self, "power_limit", None)
+            if self.sm and not self.reasons and out["sm_mhz"] < 0.9 * (self.sm_max or 0):
+                out["note"] = ("SM clock below its maximum under load with no throttle reason flagged: the board's power management "
+                               "under sustained tensor-core load (MEASURED_PEAKS.json records the same for cuBLAS: "
+                               "clocks_under_load.sm_mhz_median well below sm_max_mhz, throttled false); no clock lock was set")
+        return out
 
 
 def cpu_reference(N, d, nq, k, steps, warmup, budget_s=15.0):
