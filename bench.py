@@ -517,6 +517,7 @@ def run_workload(ctx, name, N, d, nq, k, steps, warmup, extras, config=None):
             # north_star: ">= 60% of the 3xTF32 tensor-core roofline at nq = 1024": the contraction with three
             # TF32 products per k-step (tensor_mode = 1), against the TF32 dense rate measured on this box
             tp = tf32_peaks(ctx, index, q_dev, k) if rank == 0 else {}
+            barrier()          # rank 0 has just spent seconds on its own: the ranks go on together
             for pm, key, nprod in ((2, "own_dense_pass", 1), (1, "own_dense_pass_3products", 3)):
                 probe_ms = None
                 try:

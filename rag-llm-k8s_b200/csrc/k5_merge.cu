@@ -222,15 +222,20 @@ push_record_kernel(const uint4* __restrict__ src, int64_t n16, const uint64_t* _
 }
 
 // Waits until every rank's record of call `seq` has landed here (flags[i] >= seq for i < n).  The wait is
-// bounded: a peer that never shows up (it died, or the ranks' calls went out of step) raises *err instead of
-// hanging the GPU; the host then fails the search.
+// bounded by wall time -- two minutes, far beyond any skew between ranks that are alive (one of them may be
+// busy on its host for seconds) --: a peer that never shows up (it died, or the ranks' calls went out of step)
+// raises *err instead of hanging the GPU; the host then fails the search.
 __global__ void wait_flags_kernel(const unsigned int* flags, int n, unsigned int seq, unsigned int* err) {
     const int i = threadIdx.x;
     if (i >= n) return;
     const volatile unsigned int* f = flags + i;
-    for (long long spin = 0; spin < (1ll << 22); ++spin) {  // a few seconds
+    unsigned long long t0, t1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    for (;;) {
         if ((int)(*f - seq) >= 0) { __threadfence_system(); return; }
-        __nanosleep(64);
+        __nanosleep(128);
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+        if (t1 - t0 > 120ull * 1000000000ull) break;
     }
     atomicExch(err, 1u + (unsigned)i);
 }
