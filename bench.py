@@ -224,6 +224,7 @@ def main():
             c4 = {"workload": "c4: IndexFlatL2 %dx%d fp32 row-sharded x%d, nq=%d, k=%d" % (Nc, dc, world, nqc, kc),
                   "qps": r4["qps"], "ms_per_step": r4["ms_step"], "e2e": r4["e2e"], "roofline": r4["roofline"],
                   "parity_check": r4["parity_check"], "p50_nq1_ms": r4["p50_nq1_ms"], "roofline_nq1": r4["roofline_nq1"],
+                  "clocks": r4["clocks"], "gpu_launches": r4["launches"],
                   "note": "per-GPU shard %d x 768; shard_main_pass_qps = nq / roofline.launch_ms is what one GPU's main pass "
                           "alone would allow for the whole batch" % (Nc // world),
                   "shard_main_pass_qps": nqc / (r4["roofline"]["launch_ms"] * 1e-3) if r4["roofline"].get("launch_ms") else None}
@@ -405,11 +406,11 @@ def run_workload(ctx, name, N, d, nq, k, steps, warmup, extras, config=None):
     sampler = ClockSampler(local_rank)
     sampler.start()
     ms_dev, _, launches = timed(lambda: index.search(q_dev, k), steps, warmup)
-    sampler.stop_flag = True
-    sampler.join()
     stats = index.stats() if hasattr(index, "stats") else {}
     e2e_call = lambda: index.search(q_host, k, D=D_pin, I=I_pin)
     _, wall_e2e, _ = timed(e2e_call, steps, max(warmup, 1))
+    sampler.stop_flag = True          # (sampled through both timed regions: they are tens of milliseconds long)
+    sampler.join()
 
     # p50 single-query latency on the same index (second half of BASELINE.json's metric):
     # CUDA events around the public call (includes the host's submission gap) and the scan
