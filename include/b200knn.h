@@ -205,6 +205,8 @@ B2K_API int b2k_search_rows_noalloc(int device, const float* x_dev, int64_t n, i
  * "tensor_query_stationary" (1: in the one-product screening modes a CTA pair keeps its query block resident in
  * shared memory over a run of row tiles when it fits -- d <= 512 in bf16 --; 0, the default: both operands stream.
  * Same results either way; measured equally fast),
+ * "tensor_prefetch_tiles" (n > 0: the batched pass asks L2 for the row tile n tiles ahead of its scheduler; 0, the
+ * default: off -- measured no faster at any distance, see profiles/r02_notes.md),
  * "prepare_copies" (1: build the bf16 copies of the rows now -- +50% of the row bytes, one conversion pass -- instead
  * of inside the first search that profits from them; a start-up call for servers that reserve HBM afterwards or
  * capture their searches),

@@ -549,6 +549,10 @@ int b2k_set_option(b2k_index* h, const char* key, int64_t value) {
     } else if (!strcmp(key, "tensor_query_stationary")) {
         h->opt_qs = value != 0;
         if (h->k3) k3_set_query_stationary(h->k3, h->opt_qs);
+    } else if (!strcmp(key, "tensor_prefetch_tiles")) {
+        if (value < 0 || value > 4096) { set_error("option tensor_prefetch_tiles must be 0..4096"); return B2K_EINVAL; }
+        h->opt_pf = (int)value;
+        if (h->k3) k3_set_prefetch_tiles(h->k3, h->opt_pf);
     } else if (!strcmp(key, "tensor_probe")) {
         h->opt_probe = (int)(value < 0 ? 0 : (value > 3 ? 3 : value));
         if (h->k3) k3_set_probe(h->k3, h->opt_probe);
@@ -781,6 +785,7 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
             if (!rc) k3_set_ext_flag(h->k3, h->opt_flag_ptr);
             if (!rc) k3_set_probe(h->k3, h->opt_probe);
             if (!rc) k3_set_query_stationary(h->k3, h->opt_qs);
+            if (!rc) k3_set_prefetch_tiles(h->k3, h->opt_pf);
         }
         if (!rc) h->last_path = 2;
         // like faiss (query blocks of 4096), long batches go through in chunks: the candidate-list

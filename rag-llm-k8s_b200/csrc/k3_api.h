@@ -37,6 +37,7 @@ void k3_set_ext_flag(K3State* s, unsigned int* flag);
 // key ever passes, so its time is the kernel's ceiling for that product kind; results are all padding
 void k3_set_probe(K3State* s, int on);
 void k3_set_query_stationary(K3State* s, int on);  // 1: resident query blocks where they fit; 0 (default): both operands stream
+void k3_set_prefetch_tiles(K3State* s, int n);      // L2 prefetch of the row tiles n tiles ahead of the scheduler (0 = off)
 int k3_last_kernel_ms(K3State* s, float* ms);
 int k3_last_mode(const K3State* s);  // 1 = 3xTF32, 2 = TF32 screening + exact re-rank, 3 = bf16 screening + exact re-rank
 

@@ -89,6 +89,7 @@ struct K3Params {
     long long qs_t0, qs_tA, qs_t1;
     long long qs_itemsA;  // items of the first region = ceil((qs_tA - qs_t0) / qs_T1) * nqb
     int qs_T1, qs_T2;
+    int pf_tiles;         // > 0: the CTA (pair) that takes query block 0 of tile t asks L2 for the rows of tile t + pf_tiles
 };
 
 // A unit as it travels through the ring: (tile << 8) | query block, plus, for the query-stationary
@@ -438,6 +439,17 @@ k3_tf32x3_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
                 const bool load_a = QS && (u & K3_U_FIRST) != 0;
                 const int qrow0 = qb * (K3_BM * CG) + (int)rank * K3_BM;
                 const int64_t xrow0 = t * K3_BN + (int64_t)rank * L::B_ROWS;
+                if (p.pf_tiles > 0 && qb == 0 && !p.static_mode) {
+                    // Every row tile is read by nqb CTA pairs at about the same time, and the first of them waits for
+                    // HBM.  One of them asks L2 for a tile a few dozen units ahead, so that by the time the scheduler
+                    // hands that tile out its rows are an L2 hit for everybody.
+                    const int64_t tp = t + p.pf_tiles;
+                    if (tp * K3_BN < p.n) {
+                        const int prow0 = (int)(tp * K3_BN + (int64_t)rank * L::B_ROWS);
+                        for (int kc = 0; kc < nkc; ++kc) ptx::tma_prefetch_l2_2d(&tm_x, kc * BKE, prow0);
+                        if (NF) ptx::tma_prefetch_l2_2d(&tm_n, 0, prow0);
+                    }
+                }
                 if constexpr (NF) {
                     // this tile's norm records, into the buffer that goes with the tile's accumulator
                     ptx::mbar_wait(&nempty[nb], nph ^ 1);
@@ -1290,6 +1302,7 @@ struct K3State {
     unsigned int* ext_flag = nullptr;  // caller-owned overflow word (deferred screening check)
     int epi_halves = 0;  // 0 auto (2 where available), 1 four epilogue warps, 2 eight
     int segments = 1;  // cut the main pass into segments with a bound refresh in between (0 = one launch)
+    int pf_tiles = 0;  // L2 prefetch distance in row tiles (option "tensor_prefetch_tiles"; 0 = off)
     int qs = 0;        // query-stationary schedule where it applies (option "tensor_query_stationary"; measured: no gain)
     int probe = 0;     // dense-rate probe (option "tensor_probe"): the pass runs with the filter shut, results are padding
 };
@@ -1398,6 +1411,7 @@ void k3_set_epi_halves(K3State* s, int nh) { s->epi_halves = nh; }
 void k3_set_ext_flag(K3State* s, unsigned int* flag) { s->ext_flag = flag; }
 void k3_set_probe(K3State* s, int on) { s->probe = on < 0 ? 0 : (on > 3 ? 3 : on); }
 void k3_set_query_stationary(K3State* s, int on) { s->qs = on != 0; }
+void k3_set_prefetch_tiles(K3State* s, int n) { s->pf_tiles = n < 0 ? 0 : n; }
 int k3_last_mode(const K3State* s) { return s->last_mode; }
 
 int k3_last_kernel_ms(K3State* s, float* ms) {
@@ -1551,6 +1565,7 @@ int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, con
     p.static_tile0 = 0;
     p.tile_cols = K3_BN;
     p.probe = s->probe;
+    p.pf_tiles = s->pf_tiles;
     p.qs_t0 = p.qs_tA = p.qs_t1 = 0; p.qs_itemsA = 0; p.qs_T1 = p.qs_T2 = 1;
 
     // queries: norms (+ TF32 residual rows for the exact mode; K1 reused), screening slack, list state reset
