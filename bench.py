@@ -410,12 +410,17 @@ def run_workload(ctx, name, N, d, nq, k, steps, warmup, extras, config=None):
     e2e_call = lambda: index.search(q_host, k, D=D_pin, I=I_pin)
     _, wall_e2e, _ = timed(e2e_call, steps, max(warmup, 1))
     sampler_extended = False
-    if len(sampler.sm) < 5:
+    few = 1 if len(sampler.sm) < 5 else 0
+    if dist is not None:             # the sharded search is collective: every rank must take the same decision
+        t = torch.tensor([few], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        few = int(t.item())
+    if few:
         # the timed regions are tens of milliseconds and an NVML query can take as long when several ranks ask at
-        # once: keep the same load running (untimed) until the sampler has a handful of readings under load
+        # once: keep the same load running (untimed, ~0.3 s, the same count on every rank) so that the sampler
+        # gets a handful of readings under load
         sampler_extended = True
-        t_end = time.perf_counter() + 0.5
-        while time.perf_counter() < t_end and len(sampler.sm) < 8:
+        for _ in range(int(min(400, max(10, 300.0 / (ms_dev / steps))))):
             index.search(q_dev, k)
         torch.cuda.synchronize()
     sampler.stop_flag = True          # (sampled through both timed regions: they are tens of milliseconds long)
