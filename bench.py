@@ -510,7 +510,7 @@ def run_workload(ctx, name, N, d, nq, k, steps, warmup, extras, config=None):
 
     clocks = sampler.result()
     if sampler_extended:
-        clocks["extended"] = "the same searches ran on, untimed, for up to 0.5 s so that NVML could be read under load"
+        clocks["extended"] = "the same searches ran on, untimed, for ~0.3 s so that NVML could be read under load"
     out = {"qps": qps, "ms_step": ms_step, "launches": launches, "clocks": clocks, "roofline": roof,
            "parity_check": pc, "p50_nq1_ms": p50_nq1, "roofline_nq1": roof_nq1,
            "e2e": {"value": qps_e2e, "unit": "queries/s", "h2d_bytes_per_step": nq * d * 4, "d2h_bytes_per_step": nq * k * 12}}

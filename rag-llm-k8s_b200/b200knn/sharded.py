@@ -223,11 +223,16 @@ class ShardedIndexFlatL2:
         slot = (words + 2) & ~1         # record + flag word, padded to 16 bytes (the peer exchange copies 16 bytes at a time)
         b = self._bufs.get((nq, k))
         if b is None:
-            if len(self._bufs) >= 8 and not (self._cuda and self._p2p):
-                self._bufs.clear()
+            # symmetric-memory receive buffers are collective allocations and are never freed: at most 8 shapes get
+            # one (every rank makes the same sequence of calls, so every rank decides alike); further shapes, and
+            # everything when the peer exchange is off, use ordinary buffers for the NCCL exchange, recycled
+            n_symm = sum(1 for v in self._bufs.values() if v[3] is not None)
+            if len(self._bufs) - n_symm >= 8:
+                for key in [key for key, v in self._bufs.items() if v[3] is None]:
+                    del self._bufs[key]
             send = torch.zeros(slot, dtype=torch.int64, device=self._tdev)
             b = None
-            if self._cuda and self._p2p is not None:
+            if self._cuda and self._p2p is not None and n_symm < 8:
                 # receive buffer in symmetric memory: two halves (calls alternate) of `world` slots; a collective
                 # allocation, made by every rank at its first search of this shape
                 try:
