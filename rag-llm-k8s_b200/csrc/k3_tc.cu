@@ -1478,7 +1478,9 @@ static int launch_k3_any(int cg, int P, int mode, int nh, const K3Maps& mm, cons
     }
 #undef B2K_K3_CASE
     // screening (2 = TF32, 3 = bf16): one operand pair per stage (32 KB per CTA, or 48 KB without a
-    // partner), so the rings are deeper; the 2048-key compaction scratch of long lists needs the room
+    // partner), so the rings are deeper -- as deep as the compaction scratch of the list length leaves room for
+    // (6 / 5 / 4 stages for lists of 512 / 1024 / 2048 keys: the pipeline alone loses a quarter of its rate
+    // between 6 and 4 stages, scripts/stage_depth.py)
 #define B2K_K3_SCREEN(MODE_, NH_)                                                                  \
     if (mode == MODE_ && nh == NH_) {                                                              \
         if (cg == 1) {                                                                             \
@@ -1486,6 +1488,7 @@ static int launch_k3_any(int cg, int P, int mode, int nh, const K3Maps& mm, cons
             return launch_k3<1, 2, MODE_, NH_>(mm, p, ncta, st);                     \
         }                                                                                          \
         if (P <= 512) return launch_k3<2, 6, MODE_, NH_>(mm, p, ncta, st);           \
+        if (P <= 1024) return launch_k3<2, 5, MODE_, NH_>(mm, p, ncta, st);          \
         return launch_k3<2, 4, MODE_, NH_>(mm, p, ncta, st);                         \
     }
     B2K_K3_SCREEN(2, 1)

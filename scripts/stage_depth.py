@@ -1,4 +1,4 @@
-"""Sensitivity of the batched pass to the depth of its operand ring: k <= 256 runs 6 stages, k > 256 runs 4 (room for
+"""Sensitivity of the batched pass to the depth of its operand ring: k <= 256 runs 6 stages, 257..768 run 5, longer lists 4 (room for
 longer lists); with the epilogue off (tensor_probe 3) the difference is the pipeline's alone."""
 import os, sys, statistics
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -16,4 +16,4 @@ for rep in range(2):
                 idx.search(q, k); torch.cuda.synchronize()
                 if i >= 3: main.append(idx.stats()["main_kernel_ms"])
             ms = statistics.median(main)
-            print("k=%d (%d stages) probe=%d: main pass %.3f ms = %.0f TFLOP/s" % (k, 6 if k <= 256 else 4, probe, ms, 2.0 * nq * N * d / (ms * 1e-3) / 1e12), flush=True)
+            print("k=%d (%d stages) probe=%d: main pass %.3f ms = %.0f TFLOP/s" % (k, 6 if k <= 256 else 5 if k <= 768 else 4, probe, ms, 2.0 * nq * N * d / (ms * 1e-3) / 1e12), flush=True)
