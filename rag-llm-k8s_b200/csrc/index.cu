@@ -43,7 +43,7 @@ void set_error(const char* fmt, ...) {
 RowStore::~RowStore() {
     DeviceGuard g(device);
     cudaDeviceSynchronize();  // kernels of handles that shared this store may still be reading it
-    cudaFree(x); cudaFree(norms); cudaFree(xlo); cudaFree(xbf); cudaFree(xnb); cudaFree(stat);
+    cudaFree(x); cudaFree(norms); cudaFree(xlo); cudaFree(xbf); cudaFree(xnb); cudaFree(stat); cudaFree(outl); cudaFree(outl_hist);
     if (ev_rows) cudaEventDestroy(ev_rows);
 }
 
@@ -122,6 +122,9 @@ int new_store(int d, int device, std::shared_ptr<RowStore>* out) {
     rs->d = d; rs->device = device;
     cudaError_t e = cudaMalloc(&rs->stat, 256);
     if (e == cudaSuccess) e = cudaMemset(rs->stat, 0, 256);
+    if (e == cudaSuccess) e = cudaMalloc(&rs->outl, B2K_OUTL_WORDS * sizeof(unsigned int));
+    if (e == cudaSuccess) e = cudaMemset(rs->outl, 0, B2K_OUTL_WORDS * sizeof(unsigned int));
+    if (e == cudaSuccess) e = cudaMalloc(&rs->outl_hist, B2K_OUTL_HIST_WORDS * sizeof(unsigned int));
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&rs->ev_rows, cudaEventDisableTiming);
     if (e != cudaSuccess) { cudaGetLastError(); set_error("row store: %s", cudaGetErrorString(e)); return B2K_ECUDA; }
     *out = rs;
@@ -181,6 +184,7 @@ int grow(RowStore* rs, int64_t need_rows, cudaStream_t st) {
 
 // Rows [first, first+n) of rs->x are in place: compute their norms (and the derived copies that exist).
 int prep_new_rows(RowStore* rs, int64_t first, int64_t n, cudaStream_t st) {
+    rs->outl_dirty = true;
     int rc = launch_row_prep(rs->x + first * (int64_t)rs->d, n, rs->d, rs->norms + first,
                              rs->lo_enabled ? rs->xlo + first * (int64_t)rs->d : nullptr, rs->stat + MAX_NORM_SLOT, st);
     if (!rc && rs->bf_enabled)
@@ -232,10 +236,29 @@ int enable_bf(RowStore* rs, cudaStream_t st) {
         B2K_CUDA(cudaStreamWaitEvent(st, rs->ev_rows, 0));
         rc = launch_row_bf16(rs->x, rs->filled, rs->d, rs->xbf, nullptr, rs->stat + MAX_ERR_SLOT, st);
         if (!rc) rc = launch_norm_split(rs->norms, rs->filled, rs->xnb, st);
+        if (!rc) B2K_CUDA(cudaMemsetAsync(rs->outl, 0, B2K_OUTL_WORDS * sizeof(unsigned int), st));  // fresh records: no row is out
+        rs->outl_dirty = true;
         if (!rc) B2K_CUDA(cudaEventRecord(rs->ev_rows, st));
     }
     if (!rc) rs->bf_enabled = true;
     return rc;
+}
+
+// Outlier rows for the norm-folded screen (see launch_outlier_pass): recomputed after the rows changed, under the
+// exclusive lock and with the device idle -- the pass rewrites a few norm records that searches of other handles on
+// this store may be reading.
+int ensure_outliers(RowStore* rs, cudaStream_t st) {
+    if (!rs->outl_dirty || !rs->bf_enabled) return B2K_OK;
+    std::unique_lock<std::shared_mutex> lk(rs->mu);
+    if (!rs->outl_dirty) return B2K_OK;
+    B2K_CUDA(cudaDeviceSynchronize());
+    B2K_CUDA(cudaStreamWaitEvent(st, rs->ev_rows, 0));
+    int rc = launch_outlier_pass(rs->norms, rs->filled, rs->xnb, rs->stat + MAX_NORM_SLOT, rs->stat + MAX_ERR_SLOT, rs->outl,
+                                 rs->outl_hist, st);
+    if (rc) return rc;
+    B2K_CUDA(cudaEventRecord(rs->ev_rows, st));
+    rs->outl_dirty = false;
+    return B2K_OK;
 }
 
 // Candidates the bf16 scan selects for a request of k (0: the bf16 scan cannot serve this k).
@@ -771,6 +794,7 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
         if ((mode == 2 || mode == 3) && h->opt_tensor_mode == 0 && h->screen_fail_streak >= 2 && (++h->screen_skipped & 63) != 0) mode = 4;
         // (the derived copies are created before the shared lock is taken: creating them needs it exclusively)
         if (mode == 3 && enable_bf(rs, st) != B2K_OK) mode = 2;
+        if (mode == 3) rc = ensure_outliers(rs, st);
         if (mode == 4 && h->opt_tensor_mode == 0 && enable_lo(rs, st) != B2K_OK) mode = 2;  // no room for the residual rows: cheap screen, then the scan
         if (mode == 1 || mode == 4) rc = enable_lo(rs, st);
         const bool cheap = mode == 2 || mode == 3;
@@ -796,7 +820,7 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
             int overflowed = 0;
             {
                 std::shared_lock<std::shared_mutex> sl(rs->mu);
-                rc = k3_search(h->k3, rs->x, rs->xlo, rs->xbf, rs->xnb, rs->norms, rs->stat + MAX_NORM_SLOT, rs->stat + MAX_ERR_SLOT, h->ntotal,
+                rc = k3_search(h->k3, rs->x, rs->xlo, rs->xbf, rs->xnb, rs->outl, rs->norms, rs->stat + MAX_NORM_SLOT, rs->stat + MAX_ERR_SLOT, h->ntotal,
                                h->d, qc, nqc, kk, Dd + q0 * kk, Id + q0 * kk, ws_tail, st, mode, &overflowed);
             }
             if (!rc && overflowed && mode != 4) {
@@ -807,7 +831,7 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
                 ++h->stat_screen_fallbacks;
                 if (enable_lo(rs, st) == B2K_OK) {  // (no room for the residual rows: straight to the scan, overflowed stays set)
                     std::shared_lock<std::shared_mutex> sl(rs->mu);
-                    rc = k3_search(h->k3, rs->x, rs->xlo, rs->xbf, rs->xnb, rs->norms, rs->stat + MAX_NORM_SLOT, rs->stat + MAX_ERR_SLOT,
+                    rc = k3_search(h->k3, rs->x, rs->xlo, rs->xbf, rs->xnb, rs->outl, rs->norms, rs->stat + MAX_NORM_SLOT, rs->stat + MAX_ERR_SLOT,
                                    h->ntotal, h->d, qc, nqc, kk, Dd + q0 * kk, Id + q0 * kk, ws_tail, st, 4, &overflowed);
                 }
             }

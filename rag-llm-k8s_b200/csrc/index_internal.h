@@ -30,6 +30,11 @@ struct RowStore {
     void* xnb = nullptr;               // [capacity][16] bf16: -||x||^2/2 as three bf16 terms, next to xbf (K3 adds it by MMA)
     bool lo_enabled = false, bf_enabled = false, bf_nomem = false;
     unsigned int* stat = nullptr;      // device words: [0] bits of max ||x||^2, [1] bits of max ||x - bf16(x)||^2
+    // outlier rows (k1_prep.cu: launch_outlier_pass): [0] count, [1] / [2] the norm / rounding-error caps the norm-folded
+    // screen uses once those rows are out of it, [8..72) their ids; recomputed lazily after the rows changed
+    unsigned int* outl = nullptr;
+    unsigned int* outl_hist = nullptr;
+    bool outl_dirty = true;
     cudaEvent_t ev_rows = nullptr;     // last write to any of the buffers above
     // shared: enqueueing work that reads the buffers; exclusive: add / grow / creating derived copies
     std::shared_mutex mu;

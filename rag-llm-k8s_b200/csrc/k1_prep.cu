@@ -181,6 +181,109 @@ int launch_norm_split(const float* norms, int64_t n, void* out, cudaStream_t st)
     return B2K_OK;
 }
 
+// ---- outlier rows: a norm cap for the screening slack ------------------------------------------
+// The screening slack is proportional to the largest row norm, so a handful of rows with 30 times the typical
+// norm would widen every query's zone 30-fold (and push every batched search down the fallback chain).  This
+// pass finds the few largest rows: if leaving out at most OUTL_MAX of them lowers the largest squared norm by
+// OUTL_GAIN or more, those rows are taken out of the screen -- their norm records become +inf, so the
+// norm-folded accumulator is -inf and they never pass -- and the re-rank kernel computes their exact distance
+// for every query instead; the slack then uses the cap.  Otherwise nothing changes (count = 0, cap = max).
+// `o` (device words): [0] count, [1] bits of the squared-norm cap, [2] bits of the squared rounding-error cap,
+// [3] chosen histogram bin, [8 .. 8+OUTL_MAX) row ids.  hist: OUTL_BINS words.  Bins: float bits >> 19 (sixteen
+// bins per octave), so the order of the bins is the order of the norms.
+static constexpr int OUTL_MAX = 64;
+static constexpr int OUTL_BINS = 4096;
+static constexpr float OUTL_GAIN = 1.5f;
+
+__global__ void outl_restore_kernel(unsigned int* o, const float* __restrict__ norms, uint4* __restrict__ rec, int64_t n) {
+    // rows that were outliers get their finite norm record back (they may not be outliers any more)
+    const int i = threadIdx.x;
+    if (i < (int)o[0] && i < OUTL_MAX) {
+        const int64_t r = o[8 + i];
+        if (r < n) {
+            const float h = 0.5f * norms[r];
+            const __nv_bfloat16 b1 = __float2bfloat16_rn(h);
+            const float r1 = h - __bfloat162float(b1);
+            const __nv_bfloat16 b2 = __float2bfloat16_rn(r1);
+            const __nv_bfloat16 b3 = __float2bfloat16_rn(r1 - __bfloat162float(b2));
+            const uint32_t u1 = __bfloat16_as_ushort(__hneg(b1)), u2 = __bfloat16_as_ushort(__hneg(b2)), u3 = __bfloat16_as_ushort(__hneg(b3));
+            rec[2 * r] = make_uint4(u1 | (u2 << 16), u3, 0u, 0u);
+        }
+    }
+    __syncthreads();
+    if (i == 0) o[0] = 0;
+}
+
+__global__ void __launch_bounds__(256)
+outl_hist_kernel(const float* __restrict__ norms, int64_t n, unsigned int* __restrict__ hist) {
+    __shared__ unsigned int sh[OUTL_BINS];
+    for (int b = threadIdx.x; b < OUTL_BINS; b += 256) sh[b] = 0;
+    __syncthreads();
+    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (int64_t)gridDim.x * 256) {
+        const float v = norms[i];
+        if (v <= FLT_MAX && v >= 0.f) atomicAdd(&sh[__float_as_uint(v) >> 19], 1u);  // non-finite rows never match anyway
+    }
+    __syncthreads();
+    for (int b = threadIdx.x; b < OUTL_BINS; b += 256) if (sh[b]) atomicAdd(&hist[b], sh[b]);
+}
+
+__global__ void outl_pick_kernel(const unsigned int* __restrict__ hist, const unsigned int* __restrict__ max_norm_bits,
+                                 const unsigned int* __restrict__ max_err_bits, unsigned int* o) {
+    if (threadIdx.x != 0) return;
+    // from the top: the lowest bin such that the rows in the bins ABOVE it number at most OUTL_MAX
+    unsigned int above = 0;
+    int b = OUTL_BINS - 1;
+    while (b > 0 && above + hist[b] <= OUTL_MAX) { above += hist[b]; --b; }
+    const float vmax = __uint_as_float(*max_norm_bits);
+    const float cap = __uint_as_float(((unsigned int)(b + 1)) << 19);  // every row in the bins up to b has a squared norm below this
+    if (above > 0 && cap > 0.f && vmax >= OUTL_GAIN * cap) {
+        o[1] = __float_as_uint(cap);
+        // bf16 (8 significant bits) rounds every element to within 2^-8 of its magnitude, so |x - x~| <= 2^-8 |x| for
+        // the rows that stay; the measured maximum, where smaller, is kept
+        const float ecap = cap * (1.0f / 65536.f) * 1.002f;
+        o[2] = __float_as_uint(fminf(ecap, __uint_as_float(*max_err_bits)));
+        o[3] = (unsigned int)b;
+    } else {
+        o[1] = *max_norm_bits;
+        o[2] = *max_err_bits;
+        o[3] = OUTL_BINS;  // nothing lies above this bin: no row is taken out
+    }
+}
+
+__global__ void __launch_bounds__(256)
+outl_collect_kernel(const float* __restrict__ norms, int64_t n, uint4* __restrict__ rec, unsigned int* o) {
+    const unsigned int bsel = o[3];
+    if (bsel >= OUTL_BINS) return;
+    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (int64_t)gridDim.x * 256) {
+        const float v = norms[i];
+        if (v <= FLT_MAX && v >= 0.f && (__float_as_uint(v) >> 19) > bsel) {
+            const unsigned int pos = atomicAdd(&o[0], 1u);
+            if (pos < OUTL_MAX) {
+                o[8 + pos] = (unsigned int)i;
+                rec[2 * i] = make_uint4(0xFF80FF80u, 0xFF80u, 0u, 0u);  // -h = -inf in all three terms: the accumulator becomes -inf
+            }
+        }
+    }
+}
+
+int launch_outlier_pass(const float* norms, int64_t n, void* rec, const unsigned int* max_norm_bits,
+                        const unsigned int* max_err_bits, unsigned int* o, unsigned int* hist, cudaStream_t st) {
+    outl_restore_kernel<<<1, OUTL_MAX, 0, st>>>(o, norms, static_cast<uint4*>(rec), n);
+    B2K_CUDA(cudaMemsetAsync(hist, 0, OUTL_BINS * sizeof(unsigned int), st));
+    if (n > 0) {
+        int64_t blocks = (n + 256 * 16 - 1) / (256 * 16);
+        blocks = blocks < 1 ? 1 : (blocks > 148 * 8 ? 148 * 8 : blocks);
+        outl_hist_kernel<<<(unsigned)blocks, 256, 0, st>>>(norms, n, hist);
+        outl_pick_kernel<<<1, 32, 0, st>>>(hist, max_norm_bits, max_err_bits, o);
+        outl_collect_kernel<<<(unsigned)blocks, 256, 0, st>>>(norms, n, static_cast<uint4*>(rec), o);
+        count_launch(4);
+    } else {
+        count_launch(1);
+    }
+    B2K_CUDA(cudaGetLastError());
+    return B2K_OK;
+}
+
 // ---- synthetic rows (must stay bit-identical to oracle/flat_l2_oracle.c orc_synth_value) ----
 __host__ __device__ __forceinline__ uint64_t mix64(uint64_t z) {
     z ^= z >> 30; z *= 0xBF58476D1CE4E5B9ull;

@@ -15,11 +15,12 @@ void k3_destroy(K3State* s);
 // mode 1: 3xTF32 (needs xlo).  mode 2: TF32 screening + exact fp32 re-rank (max_norm_bits = float
 // bits of the largest squared row norm).  mode 3: bf16 screening + exact re-rank (needs xbf, the
 // bf16 copies of the rows, max_err_bits = float bits of the largest squared rounding-error norm
-// of a row, xnb = the 32-byte norm records that go with xbf, and d % 8 == 0).  mode 4: the 3xTF32 product (needs xlo) used as a screen, ~10^4 times
+// of a row, xnb = the 32-byte norm records that go with xbf, outl = the outlier words of launch_outlier_pass, and d % 8 == 0).  mode 4: the 3xTF32 product (needs xlo) used as a screen, ~10^4 times
 // narrower slack than 2 / 3, + exact re-rank.  The screening modes synchronise the stream and set *overflowed when
 // the slack zone did not fit, in which case the caller must rerun with mode 4 and, failing that,
 // with the exact scan kernel.
-int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, const void* xnb, const float* norms,
+int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, const void* xnb, const unsigned int* outl,
+              const float* norms,
               const unsigned int* max_norm_bits, const unsigned int* max_err_bits, int64_t n, int d, const float* q,
               int64_t nq, int k, float* D, int64_t* I, unsigned char* scratch, cudaStream_t st, int mode,
               int* overflowed);

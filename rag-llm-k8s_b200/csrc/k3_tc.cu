@@ -89,6 +89,7 @@ struct K3Params {
     long long qs_t0, qs_tA, qs_t1;
     long long qs_itemsA;  // items of the first region = ceil((qs_tA - qs_t0) / qs_T1) * nqb
     int qs_T1, qs_T2;
+    const unsigned int* outl;  // norm-folded screen: [0] number of outlier rows kept out of the screen, [8..) their ids (else null)
     int pf_tiles;         // > 0: the CTA (pair) that takes query block 0 of tile t asks L2 for the rows of tile t + pf_tiles
 };
 
@@ -1221,6 +1222,24 @@ k6_rerank_kernel(const K3Params p, int cg, int ncta, const float* __restrict__ X
         __syncthreads();
         total = sm.cnt2;
     }
+    if (p.outl) {
+        // rows the screen never sees (their norms would have blown up every query's slack, k1_prep.cu): each of them
+        // gets its exact distance for every query, like any other candidate
+        const int nout = (int)p.outl[0] < 64 ? (int)p.outl[0] : 64;
+        if (total + nout > K4_P) {
+            if (tid == 0) atomicExch(p.overflow, 1u);
+            return;
+        }
+        __syncthreads();
+        if (tid == 0) sm.cnt2 = 0;
+        __syncthreads();
+        if (tid < nout) {
+            const unsigned int id = p.outl[8 + tid];
+            if ((int64_t)id < p.n) sm.buf[total + atomicAdd(&sm.cnt2, 1)] = make_key(0.f, id);
+        }
+        __syncthreads();
+        total += sm.cnt2;
+    }
     // exact distances: one warp per candidate (two candidates in flight per warp), 128-bit loads,
     // fixed summation order
     const float* qv = Q + qi * (int64_t)d;
@@ -1534,7 +1553,8 @@ static void launch_k4(int64_t nq, cudaStream_t st, const K3Params& p, int cg, in
                                                                                       set_counter, counter_value);
 }
 
-int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, const void* xnb, const float* norms,
+int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, const void* xnb, const unsigned int* outl,
+              const float* norms,
               const unsigned int* max_norm_bits, const unsigned int* max_err_bits, int64_t n, int d, const float* q,
               int64_t nq, int k, float* D, int64_t* I, unsigned char* scratch, cudaStream_t st, int mode,
               int* overflowed) {
@@ -1569,6 +1589,9 @@ int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, con
     p.tile_cols = K3_BN;
     p.probe = s->probe;
     p.pf_tiles = s->pf_tiles;
+    // the norm-folded kernels (bf16 screen, CTA pairs) run with the outlier rows out of the screen and the capped slack
+    const bool nf = bf16 && L.cg == 2 && outl != nullptr;
+    p.outl = nf ? outl : nullptr;
     p.qs_t0 = p.qs_tA = p.qs_t1 = 0; p.qs_itemsA = 0; p.qs_T1 = p.qs_T2 = 1;
 
     // queries: norms (+ TF32 residual rows for the exact mode; K1 reused), screening slack, list state reset
@@ -1584,7 +1607,8 @@ int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, con
         if (nq_pad > nq)
             B2K_CUDA(cudaMemsetAsync(reinterpret_cast<unsigned short*>(qlo) + nq * (int64_t)d, 0, (size_t)(nq_pad - nq) * d * 2, st));
         const float acc_coef = 8e-6f * (float)d / 256.f;
-        k3_slack_bf16_kernel<<<(unsigned)((nq + 255) / 256), 256, 0, st>>>(nq, p.qn, max_norm_bits, max_err_bits, acc_coef,
+        k3_slack_bf16_kernel<<<(unsigned)((nq + 255) / 256), 256, 0, st>>>(nq, p.qn, nf ? outl + 1 : max_norm_bits,
+                                                                           nf ? outl + 2 : max_err_bits, acc_coef,
                                                                            const_cast<float*>(p.slack2));
         count_launch();
         B2K_CUDA(cudaGetLastError());

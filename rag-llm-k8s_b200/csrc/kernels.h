@@ -13,6 +13,12 @@ int launch_row_prep(const float* X, int64_t n, int d, float* norms, float* xlo, 
 int launch_row_bf16(const float* X, int64_t n, int d, void* xb, float* err2, unsigned int* max_err_bits, cudaStream_t st);
 // -||x||^2/2 of rows [0,n) as three bf16 terms in a 32-byte record per row (the bf16 screening pass adds it by MMA)
 int launch_norm_split(const float* norms, int64_t n, void* out, cudaStream_t st);
+// outlier rows (k1_prep.cu): o = device words [0] count, [1] squared-norm cap bits, [2] squared rounding-error cap bits,
+// [8..72) row ids; hist = 4096 words of scratch.  Rewrites the norm records of the rows it takes out of the screen.
+static constexpr int B2K_OUTL_WORDS = 80;
+static constexpr int B2K_OUTL_HIST_WORDS = 4096;
+int launch_outlier_pass(const float* norms, int64_t n, void* rec, const unsigned int* max_norm_bits,
+                        const unsigned int* max_err_bits, unsigned int* o, unsigned int* hist, cudaStream_t st);
 int launch_synth(uint64_t seed, int64_t row0, int64_t nrows, int d, float* out, cudaStream_t st);
 
 // K2 (k2_scan.cu)

@@ -950,3 +950,56 @@ def test_prepare_builds_the_copies_before_the_first_search(faiss):
     free2 = torch.cuda.mem_get_info(0)[0]
     assert free1 - free2 < n * d                        # the search allocated its workspace only (~100 MB of candidate lists)
     assert_knn_matches(D, I, x, q, 10, expanded=True, what="after prepare")
+
+
+def test_a_few_huge_rows_do_not_widen_every_querys_slack(faiss):
+    """A handful of rows with 30 times the typical norm (and a later add that brings more): the batched search keeps
+    its bf16 screen -- the rows are taken out of the screen and re-ranked exactly for every query -- and stays exact,
+    also for queries that sit on or next to such a row."""
+    rng = np.random.default_rng(11)
+    n, d, nq, k = 700_000, 64, 512, 10
+    x = rng.standard_normal((n, d)).astype(np.float32)
+    big = rng.choice(n, 20, replace=False)
+    x[big] *= 30.0
+    q = rng.standard_normal((nq, d)).astype(np.float32)
+    q[0] = x[big[0]]                                   # a query ON an outlier row
+    q[1] = x[big[1]] + 0.5 * rng.standard_normal(d).astype(np.float32)
+    q[2] = 25.0 * rng.standard_normal(d).astype(np.float32)   # a far-out query: the outliers are its neighbours
+    idx = _build(faiss, x)
+    D, I = idx.search(q, k)
+    st = idx.stats()
+    assert st["path"] == "tensor" and st["tensor_mode"] == "bf16screen+rerank" and st["screen_fallbacks"] == 0, st
+    assert I[0, 0] == big[0] and D[0, 0] == 0.0
+    Dt, It = O.truth_f64(x, q[:48], k)          # (float64 brute force: a sample of the batch, the special queries included)
+    d64 = O.dist_f64(x, q[:48], I[:48])
+    # (the float64 truth uses the norm expansion: a self-match comes out as ~1e-11, hence the absolute term)
+    assert np.all(np.abs(d64 - Dt) <= 1e-5 * Dt + 1e-6), "a nearer row was missed"
+    assert_knn_matches(D, I, x, q, k, expanded=True, what="outlier rows")
+    # more rows, among them new outliers (and the old ones stay): the set is recomputed after the add
+    y = rng.standard_normal((5000, d)).astype(np.float32)
+    y[::500] *= 40.0
+    idx.add(y)
+    xa = np.concatenate([x, y])
+    q[3] = y[500]
+    D, I = idx.search(q, k)
+    st = idx.stats()
+    assert st["tensor_mode"] == "bf16screen+rerank" and st["screen_fallbacks"] == 0, st
+    assert I[3, 0] == n + 500 and D[3, 0] == 0.0
+    Dt, It = O.truth_f64(xa, q[:48], k)
+    d64 = O.dist_f64(xa, q[:48], I[:48])
+    assert np.all(np.abs(d64 - Dt) <= 1e-5 * Dt + 1e-6), "a nearer row was missed after the add"
+    assert_knn_matches(D, I, xa, q, k, expanded=True, what="outlier rows after the add")
+    # too many large rows to take out (more than 64): nothing is taken out, the search is still exact (by whatever path)
+    z = rng.standard_normal((300_000, d)).astype(np.float32)
+    z[::1000] *= 30.0
+    idx2 = _build(faiss, z)
+    qz = rng.standard_normal((300, d)).astype(np.float32)
+    D, I = idx2.search(qz, k)
+    assert_knn_matches(D, I, z, qz, k, expanded=True, what="many large rows")
+    # a view that ends before some outlier rows must not return them
+    v = idx._view()
+    idx.add(40.0 * rng.standard_normal((3, d)).astype(np.float32))
+    D, I = idx.search(q[:200], k)
+    Dv, Iv = v.search(q[:200], k)
+    assert Iv.max() < n + 5000 and I.max() < n + 5003
+    assert_knn_matches(Dv, Iv, xa, q[:200], k, expanded=True, what="view below later outliers")
