@@ -207,6 +207,8 @@ B2K_API int b2k_search_rows_noalloc(int device, const float* x_dev, int64_t n, i
  * Same results either way; measured equally fast),
  * "tensor_prefetch_tiles" (n > 0: the batched pass asks L2 for the row tile n tiles ahead of its scheduler; 0, the
  * default: off -- measured no faster at any distance, see profiles/r02_notes.md),
+ * "tensor_warm_keys" (2..64, default 12: size of the warm-start sample per query in multiples of k; measured flat
+ * between 12 and 64, worse at 6),
  * "prepare_copies" (1: build the bf16 copies of the rows now -- +50% of the row bytes, one conversion pass -- instead
  * of inside the first search that profits from them; a start-up call for servers that reserve HBM afterwards or
  * capture their searches),

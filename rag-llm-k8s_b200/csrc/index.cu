@@ -576,6 +576,10 @@ int b2k_set_option(b2k_index* h, const char* key, int64_t value) {
         if (value < 0 || value > 4096) { set_error("option tensor_prefetch_tiles must be 0..4096"); return B2K_EINVAL; }
         h->opt_pf = (int)value;
         if (h->k3) k3_set_prefetch_tiles(h->k3, h->opt_pf);
+    } else if (!strcmp(key, "tensor_warm_keys")) {
+        if (value < 2 || value > 64) { set_error("option tensor_warm_keys must be 2..64"); return B2K_EINVAL; }
+        h->opt_warm = (int)value;
+        if (h->k3) k3_set_warm_keys(h->k3, h->opt_warm);
     } else if (!strcmp(key, "tensor_probe")) {
         h->opt_probe = (int)(value < 0 ? 0 : (value > 3 ? 3 : value));
         if (h->k3) k3_set_probe(h->k3, h->opt_probe);
@@ -810,6 +814,7 @@ int b2k_search(b2k_index* h, int64_t nq, const float* xq, int64_t k, float* D, i
             if (!rc) k3_set_probe(h->k3, h->opt_probe);
             if (!rc) k3_set_query_stationary(h->k3, h->opt_qs);
             if (!rc) k3_set_prefetch_tiles(h->k3, h->opt_pf);
+            if (!rc) k3_set_warm_keys(h->k3, h->opt_warm);
         }
         if (!rc) h->last_path = 2;
         // like faiss (query blocks of 4096), long batches go through in chunks: the candidate-list

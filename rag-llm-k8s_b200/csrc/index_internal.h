@@ -70,6 +70,7 @@ struct b2k_index {
     int opt_probe = 0;
     int opt_qs = 0;
     int opt_pf = 0;
+    int opt_warm = 12;
     int opt_tensor_mode = 0;  // 0 auto (bf16 screening + exact re-rank where d % 8 == 0 and memory allows, else TF32 screening), 1 3xTF32, 2 TF32 screening, 3 bf16 screening, 4 3xTF32 screening
     int64_t stat_screen_fallbacks = 0;
     int screen_fail_streak = 0;      // consecutive searches whose cheap screen overflowed

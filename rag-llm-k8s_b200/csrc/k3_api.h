@@ -39,6 +39,7 @@ void k3_set_ext_flag(K3State* s, unsigned int* flag);
 void k3_set_probe(K3State* s, int on);
 void k3_set_query_stationary(K3State* s, int on);  // 1: resident query blocks where they fit; 0 (default): both operands stream
 void k3_set_prefetch_tiles(K3State* s, int n);      // L2 prefetch of the row tiles n tiles ahead of the scheduler (0 = off)
+void k3_set_warm_keys(K3State* s, int n);           // warm-start sample per query in multiples of k (default 12)
 int k3_last_kernel_ms(K3State* s, float* ms);
 int k3_last_mode(const K3State* s);  // 1 = 3xTF32, 2 = TF32 screening + exact re-rank, 3 = bf16 screening + exact re-rank
 

@@ -1321,6 +1321,7 @@ struct K3State {
     unsigned int* ext_flag = nullptr;  // caller-owned overflow word (deferred screening check)
     int epi_halves = 0;  // 0 auto (2 where available), 1 four epilogue warps, 2 eight
     int segments = 1;  // cut the main pass into segments with a bound refresh in between (0 = one launch)
+    int warm_keys = 12;  // warm-start sample per query, in multiples of k (option "tensor_warm_keys")
     int pf_tiles = 0;  // L2 prefetch distance in row tiles (option "tensor_prefetch_tiles"; 0 = off)
     int qs = 0;        // query-stationary schedule where it applies (option "tensor_query_stationary"; measured: no gain)
     int probe = 0;     // dense-rate probe (option "tensor_probe"): the pass runs with the filter shut, results are padding
@@ -1431,6 +1432,7 @@ void k3_set_ext_flag(K3State* s, unsigned int* flag) { s->ext_flag = flag; }
 void k3_set_probe(K3State* s, int on) { s->probe = on < 0 ? 0 : (on > 3 ? 3 : on); }
 void k3_set_query_stationary(K3State* s, int on) { s->qs = on != 0; }
 void k3_set_prefetch_tiles(K3State* s, int n) { s->pf_tiles = n < 0 ? 0 : n; }
+void k3_set_warm_keys(K3State* s, int n) { s->warm_keys = n < 2 ? 2 : (n > 64 ? 64 : n); }
 int k3_last_mode(const K3State* s) { return s->last_mode; }
 
 int k3_last_kernel_ms(K3State* s, float* ms) {
@@ -1685,11 +1687,12 @@ int k3_search(K3State* s, const float* x, const float* xlo, const void* xbf, con
         pre.static_tile0 = 0;
         pre.tile_cols = cols_a;
         // each CTA (pair) only serves every G-th query block, leaving nclusters / G lists of 64 keys per query
-        int G = (int)(((int64_t)nclusters * cols_a) / (12 * (int64_t)k));
+        const int64_t wk = s->warm_keys;  // sample size per query, in multiples of k
+        int G = (int)(((int64_t)nclusters * cols_a) / (wk * (int64_t)k));
         G = G < 1 ? 1 : (G > L.nqb ? L.nqb : G);
         // ... and of fewer than 64 columns when that is still more than the ~12k keys per query a usable
         // bound needs (few query blocks, small k): the pass keeps every key, so it costs what it keeps
-        int want_cols = (int)((12 * (int64_t)k * G + nclusters - 1) / nclusters);
+        int want_cols = (int)((wk * (int64_t)k * G + nclusters - 1) / nclusters);
         want_cols = (want_cols + 7) & ~7;
         cols_a = want_cols < 8 ? 8 : (want_cols > 64 ? 64 : want_cols);
         pre.tile_cols = cols_a;
