@@ -96,9 +96,48 @@ bool is_pinned_host(const void* p) {
 
 namespace {
 
+// Spare buffers.  llm/rag.py builds a fresh index object per request (read_index, rag.py:153), i.e. a fresh view
+// here, and a view's first search needs a workspace and a pinned staging buffer: cudaMalloc + cudaMallocHost cost
+// ~2.5 ms, ten times the search itself at the reference's sizes.  A destroyed handle therefore leaves its (small)
+// buffers in a per-device pool and the next handle picks them up.
+struct Spare { void* p; size_t bytes; };
+struct SparePool {
+    std::mutex mu;
+    std::vector<Spare> ws[64], pin[64];
+};
+SparePool g_spares;
+constexpr size_t SPARE_MAX_BYTES = (size_t)64 << 20;  // larger buffers are not hoarded
+constexpr size_t SPARE_MAX_COUNT = 8;
+
+bool take_spare(std::vector<Spare>& v, size_t need, Spare* out) {
+    std::lock_guard<std::mutex> lk(g_spares.mu);
+    int best = -1;
+    for (int i = 0; i < (int)v.size(); ++i)
+        if (v[i].bytes >= need && (best < 0 || v[i].bytes < v[best].bytes)) best = i;
+    if (best < 0) return false;
+    *out = v[best];
+    v.erase(v.begin() + best);
+    return true;
+}
+
+// true if the pool took the buffer (the caller must have made sure no work still uses it)
+bool give_spare(std::vector<Spare>& v, void* p, size_t bytes) {
+    if (!p || bytes > SPARE_MAX_BYTES) return false;
+    std::lock_guard<std::mutex> lk(g_spares.mu);
+    if (v.size() >= SPARE_MAX_COUNT) return false;
+    v.push_back(Spare{p, bytes});
+    return true;
+}
+
 int ensure_ws(b2k_index* h, size_t bytes) {
     if (bytes <= h->ws_bytes) return B2K_OK;
-    if (h->ws) { B2K_CUDA(cudaFree(h->ws)); h->ws = nullptr; h->ws_bytes = 0; }  // cudaFree synchronises
+    if (h->ws) {
+        B2K_CUDA(cudaEventSynchronize(h->ev_ws));  // the last user of the old workspace is done
+        if (!give_spare(g_spares.ws[h->device & 63], h->ws, h->ws_bytes)) B2K_CUDA(cudaFree(h->ws));
+        h->ws = nullptr; h->ws_bytes = 0;
+    }
+    Spare sp;
+    if (take_spare(g_spares.ws[h->device & 63], bytes, &sp)) { h->ws = sp.p; h->ws_bytes = sp.bytes; return B2K_OK; }
     size_t want = bytes + bytes / 4 + 4096;
     cudaError_t e = cudaMalloc(&h->ws, want);
     if (e != cudaSuccess) { cudaGetLastError(); set_error("workspace cudaMalloc(%zu) failed: %s", want, cudaGetErrorString(e)); return B2K_ENOMEM; }
@@ -108,7 +147,13 @@ int ensure_ws(b2k_index* h, size_t bytes) {
 
 int ensure_pin(b2k_index* h, size_t bytes) {
     if (bytes <= h->pin_bytes) return B2K_OK;
-    if (h->pin) { B2K_CUDA(cudaStreamSynchronize(h->stream)); B2K_CUDA(cudaFreeHost(h->pin)); h->pin = nullptr; h->pin_bytes = 0; }
+    if (h->pin) {
+        B2K_CUDA(cudaStreamSynchronize(h->stream));
+        if (!give_spare(g_spares.pin[h->device & 63], h->pin, h->pin_bytes)) B2K_CUDA(cudaFreeHost(h->pin));
+        h->pin = nullptr; h->pin_bytes = 0;
+    }
+    Spare sp;
+    if (take_spare(g_spares.pin[h->device & 63], bytes, &sp)) { h->pin = sp.p; h->pin_bytes = sp.bytes; return B2K_OK; }
     size_t want = bytes + bytes / 4 + 4096;
     cudaError_t e = cudaMallocHost(&h->pin, want);
     if (e != cudaSuccess) { cudaGetLastError(); set_error("cudaMallocHost(%zu) failed: %s", want, cudaGetErrorString(e)); return B2K_ENOMEM; }
@@ -507,8 +552,9 @@ int b2k_destroy(b2k_index* h) {
     if (h->stream) cudaStreamSynchronize(h->stream);
     if (h->ev_ws) cudaEventSynchronize(h->ev_ws);
     if (h->k3) k3_destroy(h->k3);
-    cudaFree(h->ws); cudaFree(h->done);
-    if (h->pin) cudaFreeHost(h->pin);
+    if (!give_spare(g_spares.ws[h->device & 63], h->ws, h->ws_bytes)) cudaFree(h->ws);  // (all of this handle's work is done: synchronised above)
+    cudaFree(h->done);
+    if (h->pin && !give_spare(g_spares.pin[h->device & 63], h->pin, h->pin_bytes)) cudaFreeHost(h->pin);
     if (h->ev_ws) cudaEventDestroy(h->ev_ws);
     if (h->ev_t0) cudaEventDestroy(h->ev_t0);
     if (h->ev_t1) cudaEventDestroy(h->ev_t1);
