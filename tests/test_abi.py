@@ -93,3 +93,15 @@ def test_default_device_env(monkeypatch):
     assert b200knn.default_device() == 3
     monkeypatch.setenv("B200KNN_DEVICE", "1")
     assert b200knn.default_device() == 1
+
+
+def test_every_option_and_stat_key_is_documented_in_the_header():
+    """b2k_set_option / b2k_get_stat take string keys: each key the library accepts must be described in include/b200knn.h."""
+    hdr = open(os.path.join(ROOT, "include", "b200knn.h")).read()
+    csrc = os.path.join(ROOT, "rag-llm-k8s_b200", "csrc")
+    keys = set()
+    for f in ("index.cu", "multi.cu"):
+        keys |= set(re.findall(r'!strcmp\(key, "(\w+)"\)', open(os.path.join(csrc, f)).read()))
+    assert len(keys) >= 20
+    missing = sorted(k for k in keys if '"%s"' % k not in hdr)
+    assert not missing, "undocumented option / stat keys: %s" % missing
